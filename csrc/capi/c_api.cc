@@ -1,0 +1,290 @@
+// extern "C" surface over the host core (include/mp4j.h). The GPU half lives in csrc/gpu/gpu_api.cu.
+#include <stdlib.h>
+#include <string.h>
+
+#include "../../include/mp4j.h"
+#include "../control/control.h"
+#include "../host/process_comm.h"
+#include "../host/thread_group.h"
+#include "capi_util.h"
+
+using namespace mp4j;
+
+namespace mp4j {
+thread_local std::string g_last_error;
+}
+
+struct mp4j_master {
+  Master* m;
+};
+struct mp4j_tgroup {
+  ThreadGroup* g;
+};
+
+extern "C" {
+
+const char* mp4j_last_error(void) { return g_last_error.c_str(); }
+const char* mp4j_version(void) { return "mp4j-b200 0.1.0 (sm_100a)"; }
+void mp4j_free(void* p) { free(p); }
+
+static char* dup_bytes(const std::string& s) {
+  char* p = (char*)malloc(s.size() + 1);
+  if (!p) throw Error("out of memory");
+  memcpy(p, s.data(), s.size());
+  p[s.size()] = 0;
+  return p;
+}
+
+// ---------------------------------------------------------------- master
+int mp4j_master_create(int nslaves, int port, int connect_timeout_s, int heartbeat_timeout_s,
+                       int exchange_timeout_s, int watchdog_period_ms, const char* log_dir,
+                       const char* work_dir, int quiet, mp4j_master** out) {
+  MP4J_API_BEGIN
+  MasterOptions o;
+  if (connect_timeout_s > 0) o.connect_timeout_s = connect_timeout_s;
+  if (heartbeat_timeout_s > 0) o.heartbeat_timeout_s = heartbeat_timeout_s;
+  if (exchange_timeout_s > 0) o.exchange_timeout_s = exchange_timeout_s;
+  if (watchdog_period_ms > 0) o.watchdog_period_ms = watchdog_period_ms;
+  if (log_dir) o.log_dir = log_dir;
+  if (work_dir && *work_dir) o.work_dir = work_dir;
+  o.quiet = quiet != 0;
+  *out = new mp4j_master{new Master(nslaves, port, o)};
+  MP4J_API_END
+}
+int mp4j_master_start(mp4j_master* m) {
+  MP4J_API_BEGIN
+  m->m->start();
+  MP4J_API_END
+}
+int mp4j_master_port(mp4j_master* m) { return m->m->port(); }
+int mp4j_master_wait(mp4j_master* m, int timeout_ms, int* code) {
+  try {
+    if (timeout_ms < 0) {
+      int c = m->m->wait();
+      if (code) *code = c;
+      return 0;
+    }
+    return m->m->wait_for(timeout_ms, code) ? 0 : 1;
+  } catch (const std::exception& e) {
+    g_last_error = e.what();
+    return MP4J_ERR;
+  }
+}
+int mp4j_master_shutdown(mp4j_master* m) {
+  MP4J_API_BEGIN
+  m->m->shutdown();
+  MP4J_API_END
+}
+int mp4j_master_logs(mp4j_master* m, char** out, size_t* len) {
+  MP4J_API_BEGIN
+  std::string all;
+  for (auto& l : m->m->logs()) {
+    all += l;
+    all += '\n';
+  }
+  *out = dup_bytes(all);
+  *len = all.size();
+  MP4J_API_END
+}
+void mp4j_master_destroy(mp4j_master* m) {
+  if (!m) return;
+  delete m->m;
+  delete m;
+}
+
+// ---------------------------------------------------------------- communicator
+int mp4j_comm_create(const char* login, const char* master_host, int master_port, int rank_hint,
+                     const char* my_host, mp4j_comm** out) {
+  MP4J_API_BEGIN
+  auto* c = new mp4j_comm();
+  try {
+    c->pc = new ProcessComm(login ? login : "", master_host, master_port, rank_hint, my_host ? my_host : "");
+  } catch (...) {
+    delete c;
+    throw;
+  }
+  *out = c;
+  MP4J_API_END
+}
+void mp4j_comm_destroy(mp4j_comm* c) {
+  if (!c) return;
+  if (c->gpu_dtor) c->gpu_dtor(c);
+  delete c->pc;
+  delete c;
+}
+int mp4j_comm_rank(mp4j_comm* c) { return c->pc->rank(); }
+int mp4j_comm_size(mp4j_comm* c) { return c->pc->size(); }
+int mp4j_comm_barrier(mp4j_comm* c) {
+  MP4J_API_BEGIN
+  c->pc->barrier();
+  MP4J_API_END
+}
+int mp4j_comm_log(mp4j_comm* c, int level, const char* msg) {
+  MP4J_API_BEGIN
+  c->pc->log((LogLevel)level, msg);
+  MP4J_API_END
+}
+int mp4j_comm_close(mp4j_comm* c, int code) {
+  MP4J_API_BEGIN
+  c->pc->close(code);
+  MP4J_API_END
+}
+int mp4j_comm_exchange(mp4j_comm* c, int* other) {
+  MP4J_API_BEGIN
+  *other = c->pc->master().exchange(c->pc->rank());
+  MP4J_API_END
+}
+int mp4j_comm_write_file(mp4j_comm* c, const char* content, const char* fname) {
+  MP4J_API_BEGIN
+  c->pc->master().write_file(content, fname);
+  MP4J_API_END
+}
+int mp4j_comm_shutdown_master(mp4j_comm* c) {
+  MP4J_API_BEGIN
+  c->pc->master().shutdown_master();
+  MP4J_API_END
+}
+int mp4j_comm_gather_all(mp4j_comm* c, const void* data, size_t n, char** out, size_t* out_len) {
+  MP4J_API_BEGIN
+  auto parts = c->pc->master().gather_all(c->pc->rank(), data, n);
+  std::string all;
+  for (auto& p : parts) {
+    uint64_t len = p.size();
+    all.append((const char*)&len, 8);
+    all += p;
+  }
+  *out = dup_bytes(all);
+  *out_len = all.size();
+  MP4J_API_END
+}
+
+int mp4j_host_reduce_scatter(mp4j_comm* c, void* arr, int dtype, int op, int64_t from,
+                             const int64_t* counts) {
+  MP4J_API_BEGIN
+  c->pc->reduce_scatter(arr, dtype, op, from, counts);
+  MP4J_API_END
+}
+int mp4j_host_allgather(mp4j_comm* c, void* arr, int dtype, const int64_t* froms, const int64_t* tos) {
+  MP4J_API_BEGIN
+  c->pc->allgather(arr, dtype, froms, tos);
+  MP4J_API_END
+}
+int mp4j_host_gather(mp4j_comm* c, void* arr, int dtype, const int64_t* froms, const int64_t* tos,
+                     int root) {
+  MP4J_API_BEGIN
+  c->pc->gather(arr, dtype, froms, tos, root);
+  MP4J_API_END
+}
+int mp4j_host_scatter(mp4j_comm* c, void* arr, int dtype, const int64_t* froms, const int64_t* tos,
+                      int root) {
+  MP4J_API_BEGIN
+  c->pc->scatter(arr, dtype, froms, tos, root);
+  MP4J_API_END
+}
+int mp4j_host_broadcast(mp4j_comm* c, void* arr, int dtype, int64_t from, int64_t to, int root) {
+  MP4J_API_BEGIN
+  c->pc->broadcast(arr, dtype, from, to, root);
+  MP4J_API_END
+}
+int mp4j_host_reduce(mp4j_comm* c, void* arr, int dtype, int op, int64_t from, int64_t to, int root) {
+  MP4J_API_BEGIN
+  c->pc->reduce(arr, dtype, op, from, to, root);
+  MP4J_API_END
+}
+int mp4j_host_allreduce(mp4j_comm* c, void* arr, int dtype, int op, int64_t from, int64_t to) {
+  MP4J_API_BEGIN
+  c->pc->allreduce(arr, dtype, op, from, to);
+  MP4J_API_END
+}
+int mp4j_host_allreduce_rpc(mp4j_comm* c, void* arr, int dtype, int op, int64_t n) {
+  MP4J_API_BEGIN
+  c->pc->allreduce_rpc(arr, dtype, op, n);
+  MP4J_API_END
+}
+int mp4j_host_reduce_into(int dtype, int op, void* dst, const void* src, int64_t n) {
+  MP4J_API_BEGIN
+  host_reduce_into(dtype, op, dst, src, (size_t)n);
+  MP4J_API_END
+}
+
+int mp4j_comm_send_bytes(mp4j_comm* c, int dest, const void* data, size_t n) {
+  MP4J_API_BEGIN
+  c->pc->send_bytes(dest, data, n);
+  MP4J_API_END
+}
+int mp4j_comm_recv_bytes(mp4j_comm* c, int src, char** out, size_t* out_len) {
+  MP4J_API_BEGIN
+  std::string s = c->pc->recv_bytes(src);
+  *out = dup_bytes(s);
+  *out_len = s.size();
+  MP4J_API_END
+}
+int mp4j_comm_sendrecv_bytes(mp4j_comm* c, int dest, const void* data, size_t n, int src, char** out,
+                             size_t* out_len) {
+  MP4J_API_BEGIN
+  std::string s = c->pc->sendrecv_bytes(dest, data, n, src);
+  *out = dup_bytes(s);
+  *out_len = s.size();
+  MP4J_API_END
+}
+
+// ---------------------------------------------------------------- thread group
+int mp4j_tgroup_create(int nthreads, mp4j_tgroup** out) {
+  MP4J_API_BEGIN
+  if (nthreads < 1) throw Error("threadNum must be >= 1");
+  *out = new mp4j_tgroup{new ThreadGroup(nthreads)};
+  MP4J_API_END
+}
+void mp4j_tgroup_destroy(mp4j_tgroup* g) {
+  if (!g) return;
+  delete g->g;
+  delete g;
+}
+int mp4j_tgroup_barrier(mp4j_tgroup* g) {
+  MP4J_API_BEGIN
+  g->g->barrier();
+  MP4J_API_END
+}
+int mp4j_tgroup_set_slot(mp4j_tgroup* g, int tid, int which, uint64_t v) {
+  MP4J_API_BEGIN
+  if (tid < 0 || tid >= g->g->size() || which < 0 || which >= ThreadGroup::kSlots) throw Error("bad slot");
+  g->g->set_slot(tid, which, v);
+  MP4J_API_END
+}
+uint64_t mp4j_tgroup_get_slot(mp4j_tgroup* g, int tid, int which) { return g->g->get_slot(tid, which); }
+
+// ---------------------------------------------------------------- helpers
+double mp4j_composite_double(float val, int32_t loc) { return composite_double(val, loc); }
+float mp4j_composite_double_val(double c) { return composite_double_val(c); }
+int32_t mp4j_composite_double_loc(double c) { return composite_double_loc(c); }
+int64_t mp4j_composite_long(int32_t val, int32_t loc) { return composite_long(val, loc); }
+int32_t mp4j_composite_long_val(int64_t c) { return composite_long_val(c); }
+int32_t mp4j_composite_long_loc(int64_t c) { return composite_long_loc(c); }
+
+int32_t mp4j_java_string_hash(const char* s, size_t n) {
+  // decode UTF-8 into UTF-16 code units on the fly; h = 31*h + unit (32-bit wrap)
+  uint32_t h = 0;
+  size_t i = 0;
+  while (i < n) {
+    uint32_t cp;
+    unsigned char b = (unsigned char)s[i];
+    if (b < 0x80) { cp = b; i += 1; }
+    else if ((b >> 5) == 6 && i + 1 < n) { cp = ((b & 0x1f) << 6) | (s[i + 1] & 0x3f); i += 2; }
+    else if ((b >> 4) == 14 && i + 2 < n) {
+      cp = ((b & 0x0f) << 12) | ((s[i + 1] & 0x3f) << 6) | (s[i + 2] & 0x3f); i += 3;
+    } else if ((b >> 3) == 30 && i + 3 < n) {
+      cp = ((b & 0x07) << 18) | ((s[i + 1] & 0x3f) << 12) | ((s[i + 2] & 0x3f) << 6) | (s[i + 3] & 0x3f);
+      i += 4;
+    } else { cp = b; i += 1; }
+    if (cp >= 0x10000) {
+      cp -= 0x10000;
+      h = 31 * h + (0xD800 + (cp >> 10));
+      h = 31 * h + (0xDC00 + (cp & 0x3ff));
+    } else {
+      h = 31 * h + cp;
+    }
+  }
+  return (int32_t)h;
+}
+
+}  // extern "C"

@@ -1,0 +1,289 @@
+#include "process_comm.h"
+
+#include <stdlib.h>
+#include <unistd.h>
+
+#include <algorithm>
+
+namespace mp4j {
+
+namespace {
+constexpr size_t kChunk = 1 << 20;  // pipeline granularity of reduce-on-receive
+
+int env_int(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return v && *v ? atoi(v) : dflt;
+}
+}  // namespace
+
+ProcessComm::ProcessComm(const std::string& login, const std::string& master_host, int master_port,
+                         int rank_hint, const std::string& my_host) {
+  master_.reset(new MasterClient(master_host, master_port));
+  listen_fd_ = net::tcp_listen(0, &listen_port_);
+  std::string host = my_host.empty() ? (getenv("MP4J_HOST") ? getenv("MP4J_HOST") : net::local_hostname())
+                                     : my_host;
+  std::string me = host + kAddrDelim + std::to_string(listen_port_);
+  rank_ = master_->rendezvous(me, rank_hint, &addrs_);
+  n_ = (int)addrs_.size();
+  for (auto& a : addrs_) {
+    size_t k = a.rfind(kAddrDelim);
+    hosts_.push_back(a.substr(0, k));
+    ports_.push_back(atoi(a.c_str() + k + 3));
+  }
+  out_fds_.assign(n_, -1);
+  in_fds_.assign(n_, -1);
+  accept_thr_ = std::thread([this] { accept_loop(); });
+  // kill script line: ssh login@host "kill -9 pid" (PCS:178-183)
+  master_->kill_me(rank_, "ssh " + login + "@" + host + " \"kill -9 " + std::to_string((int)getpid()) + "\"");
+  int period = env_int("MP4J_HEARTBEAT_MS", 15000);
+  master_->start_heartbeat(rank_, std::min(period, 5000), period, 4, nullptr, nullptr);
+}
+
+ProcessComm::~ProcessComm() {
+  master_->stop_heartbeat();
+  if (listen_fd_ >= 0) {
+    net::shutdown_fd(listen_fd_);
+    net::close_fd(listen_fd_);
+    listen_fd_ = -1;
+  }
+  if (accept_thr_.joinable()) accept_thr_.join();
+  for (int fd : out_fds_) net::close_fd(fd);
+  for (int fd : in_fds_) net::close_fd(fd);
+}
+
+void ProcessComm::accept_loop() {
+  for (;;) {
+    int fd = net::tcp_accept(listen_fd_);
+    if (fd < 0) return;
+    int32_t src = -1;
+    try {
+      if (!net::recv_all(fd, &src, 4) || src < 0 || src >= n_) {
+        net::close_fd(fd);
+        continue;
+      }
+    } catch (const std::exception&) {
+      net::close_fd(fd);
+      continue;
+    }
+    std::lock_guard<std::mutex> lk(mesh_mu_);
+    in_fds_[src] = fd;
+    mesh_cv_.notify_all();
+  }
+}
+
+int ProcessComm::out_fd(int dest) {
+  {
+    std::lock_guard<std::mutex> lk(mesh_mu_);
+    if (out_fds_[dest] >= 0) return out_fds_[dest];
+  }
+  int fd = net::tcp_connect(hosts_[dest], ports_[dest], 200, 30);
+  int32_t me = rank_;
+  net::send_all(fd, &me, 4);
+  std::lock_guard<std::mutex> lk(mesh_mu_);
+  out_fds_[dest] = fd;
+  return fd;
+}
+
+int ProcessComm::in_fd(int src) {
+  std::unique_lock<std::mutex> lk(mesh_mu_);
+  int tmo = env_int("MP4J_PEER_TIMEOUT_S", 600);
+  if (!mesh_cv_.wait_for(lk, std::chrono::seconds(tmo), [&] { return in_fds_[src] >= 0; }))
+    throw Error("timeout waiting for a data connection from rank " + std::to_string(src));
+  return in_fds_[src];
+}
+
+void ProcessComm::barrier() {
+  if (n_ == 1) return;
+  master_->barrier();
+}
+
+void ProcessComm::log(LogLevel lvl, const std::string& msg) { master_->log(lvl, msg); }
+
+void ProcessComm::close(int code) {
+  if (closed_) return;
+  closed_ = true;
+  master_->stop_heartbeat();
+  master_->close(rank_, code);
+}
+
+// ------------------------------------------------------------------ host collectives
+
+void ProcessComm::reduce_scatter(void* arr, int dtype, int op, int64_t from, const int64_t* counts) {
+  check_from_counts(from, counts, n_);
+  if (n_ == 1) return;  // PCS:1179
+  if (!op_valid_for(dtype, op) || op == MP4J_COPY) throw Error("invalid operator for dtype");
+  std::lock_guard<std::mutex> lk(op_mu_);
+  const size_t es = dtype_size(dtype);
+  std::vector<int64_t> froms(n_), tos(n_);
+  froms_tos_from_counts(from, counts, n_, froms.data(), tos.data());
+  int next = (rank_ + 1) % n_, prev = (rank_ - 1 + n_) % n_;
+  int sfd = out_fd(next), rfd = in_fd(prev);
+  char* base = (char*)arr;
+  if (scratch_.size() < kChunk) scratch_.resize(kChunk);
+  for (int s = 0; s < n_ - 1; ++s) {
+    int sseg = ((rank_ - 1 - s) % n_ + n_) % n_;
+    int rseg = ((rank_ - 2 - s) % n_ + n_) % n_;
+    size_t sbytes = (size_t)(tos[sseg] - froms[sseg]) * es, rbytes = (size_t)(tos[rseg] - froms[rseg]) * es;
+    char* sp = base + froms[sseg] * es;
+    char* rp = base + froms[rseg] * es;
+    size_t so = 0, ro = 0;
+    const size_t chunk = kChunk / es * es;
+    while (so < sbytes || ro < rbytes) {
+      size_t sl = std::min(chunk, sbytes - so), rl = std::min(chunk, rbytes - ro);
+      net::sendrecv(sfd, sp + so, sl, rfd, scratch_.data(), rl);
+      if (rl) host_reduce_into(dtype, op, rp + ro, scratch_.data(), rl / es);  // op(local, incoming) DOP:196
+      so += sl;
+      ro += rl;
+    }
+  }
+}
+
+void ProcessComm::allgather(void* arr, int dtype, const int64_t* froms, const int64_t* tos) {
+  check_froms_tos(froms, tos, n_);
+  if (n_ == 1) return;  // PCS:630
+  std::lock_guard<std::mutex> lk(op_mu_);
+  const size_t es = dtype_size(dtype);
+  int next = (rank_ + 1) % n_, prev = (rank_ - 1 + n_) % n_;
+  int sfd = out_fd(next), rfd = in_fd(prev);
+  char* base = (char*)arr;
+  for (int s = 0; s < n_ - 1; ++s) {
+    int sseg = ((rank_ - s) % n_ + n_) % n_;
+    int rseg = ((rank_ - 1 - s) % n_ + n_) % n_;
+    net::sendrecv(sfd, base + froms[sseg] * es, (size_t)(tos[sseg] - froms[sseg]) * es, rfd,
+                  base + froms[rseg] * es, (size_t)(tos[rseg] - froms[rseg]) * es);
+  }
+}
+
+void ProcessComm::gather(void* arr, int dtype, const int64_t* froms, const int64_t* tos, int root) {
+  check_froms_tos(froms, tos, n_);
+  if (root < 0 || root >= n_) throw Error("root rank out of range");
+  if (n_ == 1) return;  // PCS:545
+  std::lock_guard<std::mutex> lk(op_mu_);
+  const size_t es = dtype_size(dtype);
+  char* base = (char*)arr;
+  int vr = (rank_ - root + n_) % n_;
+  auto real = [&](int v) { return (v + root) % n_; };
+  for (int m = 1; m < n_; m <<= 1) {
+    if (vr & m) {  // hand everything accumulated so far to the parent
+      int fd = out_fd(real(vr - m));
+      for (int v = vr; v < std::min(vr + m, n_); ++v) {
+        int q = real(v);
+        net::send_all(fd, base + froms[q] * es, (size_t)(tos[q] - froms[q]) * es);
+      }
+      break;
+    } else if (vr + m < n_) {
+      int fd = in_fd(real(vr + m));
+      for (int v = vr + m; v < std::min(vr + 2 * m, n_); ++v) {
+        int q = real(v);
+        size_t nb = (size_t)(tos[q] - froms[q]) * es;
+        if (nb && !net::recv_all(fd, base + froms[q] * es, nb)) throw Error("peer closed during gather");
+      }
+    }
+  }
+}
+
+void ProcessComm::scatter(void* arr, int dtype, const int64_t* froms, const int64_t* tos, int root) {
+  check_froms_tos(froms, tos, n_);
+  if (root < 0 || root >= n_) throw Error("root rank out of range");
+  if (n_ == 1) return;
+  std::lock_guard<std::mutex> lk(op_mu_);
+  const size_t es = dtype_size(dtype);
+  char* base = (char*)arr;
+  int vr = (rank_ - root + n_) % n_;
+  auto real = [&](int v) { return (v + root) % n_; };
+  int top = 1;
+  while (top < n_) top <<= 1;
+  top >>= 1;
+  int start = top;
+  if (vr != 0) {
+    int lsb = vr & -vr;
+    int fd = in_fd(real(vr - lsb));
+    for (int v = vr; v < std::min(vr + lsb, n_); ++v) {
+      int q = real(v);
+      size_t nb = (size_t)(tos[q] - froms[q]) * es;
+      if (nb && !net::recv_all(fd, base + froms[q] * es, nb)) throw Error("peer closed during scatter");
+    }
+    start = lsb >> 1;
+  }
+  for (int m = start; m >= 1; m >>= 1) {
+    if (vr + m >= n_) continue;
+    int fd = out_fd(real(vr + m));
+    for (int v = vr + m; v < std::min(vr + 2 * m, n_); ++v) {
+      int q = real(v);
+      net::send_all(fd, base + froms[q] * es, (size_t)(tos[q] - froms[q]) * es);
+    }
+  }
+}
+
+void ProcessComm::broadcast(void* arr, int dtype, int64_t from, int64_t to, int root) {
+  check_from_to(from, to);
+  if (n_ == 1) return;  // PCS:751
+  std::vector<int64_t> froms(n_), tos(n_);
+  balanced_split(from, to, n_, froms.data(), tos.data());  // PCS:760-767
+  scatter(arr, dtype, froms.data(), tos.data(), root);
+  allgather(arr, dtype, froms.data(), tos.data());
+}
+
+void ProcessComm::reduce(void* arr, int dtype, int op, int64_t from, int64_t to, int root) {
+  check_from_to(from, to);
+  if (n_ == 1) return;
+  std::vector<int64_t> froms(n_), tos(n_), counts(n_);
+  balanced_split(from, to, n_, froms.data(), tos.data());
+  for (int i = 0; i < n_; ++i) counts[i] = tos[i] - froms[i];
+  reduce_scatter(arr, dtype, op, from, counts.data());
+  gather(arr, dtype, froms.data(), tos.data(), root);
+}
+
+void ProcessComm::allreduce(void* arr, int dtype, int op, int64_t from, int64_t to) {
+  check_from_to(from, to);
+  if (n_ == 1) return;  // PCS:1734
+  std::vector<int64_t> froms(n_), tos(n_), counts(n_);
+  balanced_split(from, to, n_, froms.data(), tos.data());  // PCS:1741-1756
+  for (int i = 0; i < n_; ++i) counts[i] = tos[i] - froms[i];
+  reduce_scatter(arr, dtype, op, from, counts.data());
+  allgather(arr, dtype, froms.data(), tos.data());
+}
+
+void ProcessComm::allreduce_rpc(void* arr, int dtype, int op, int64_t n) {
+  if (n_ == 1) return;
+  if (!op_valid_for(dtype, op) || op == MP4J_COPY) throw Error("invalid operator for dtype");
+  const size_t es = dtype_size(dtype);
+  auto parts = master_->gather_all(rank_, arr, (size_t)n * es);
+  for (auto& p : parts)
+    if (p.size() != (size_t)n * es) throw Error("allreduce_rpc: ranks passed arrays of different length");
+  memcpy(arr, parts[0].data(), (size_t)n * es);  // rank order => identical bits on every rank
+  for (int q = 1; q < n_; ++q) host_reduce_into(dtype, op, arr, parts[q].data(), (size_t)n);
+}
+
+// ------------------------------------------------------------------ byte transport
+
+void ProcessComm::send_bytes(int dest, const void* data, size_t n) {
+  if (dest < 0 || dest >= n_ || dest == rank_) throw Error("send_bytes: bad destination");
+  int fd = out_fd(dest);
+  uint64_t len = n;
+  net::send_all(fd, &len, 8);
+  net::send_all(fd, data, n);
+}
+
+std::string ProcessComm::recv_bytes(int src) {
+  if (src < 0 || src >= n_ || src == rank_) throw Error("recv_bytes: bad source");
+  int fd = in_fd(src);
+  uint64_t len = 0;
+  if (!net::recv_all(fd, &len, 8)) throw Error("peer closed the data connection");
+  std::string out(len, '\0');
+  if (len && !net::recv_all(fd, &out[0], len)) throw Error("peer closed the data connection");
+  return out;
+}
+
+std::string ProcessComm::sendrecv_bytes(int dest, const void* data, size_t n, int src) {
+  if (dest < 0 || dest >= n_ || dest == rank_) throw Error("sendrecv_bytes: bad destination");
+  if (src < 0 || src >= n_ || src == rank_) throw Error("sendrecv_bytes: bad source");
+  int sfd = out_fd(dest), rfd = in_fd(src);
+  uint64_t slen = n, rlen = 0;
+  net::sendrecv(sfd, &slen, 8, rfd, &rlen, 8);
+  std::string out(rlen, '\0');
+  net::sendrecv(sfd, data, n, rfd, rlen ? &out[0] : nullptr, rlen);
+  return out;
+}
+
+}  // namespace mp4j

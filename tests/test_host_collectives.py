@@ -1,0 +1,82 @@
+"""Multi-process CPU tests: control plane + C++ host collectives + generic (String/Object/map)
+path + ThreadCommSlave, on local ranks over loopback TCP (the integration layer the reference
+only tests on a real cluster)."""
+import os
+
+import pytest
+
+import workers
+from ytk_mp4j_b200.parallel.local_cluster import run_cluster
+
+
+@pytest.mark.parametrize("p,dtype,n,root", [
+    (1, "double", 100, 0),
+    (2, "double", 1001, 1),
+    (3, "float", 1000, 2),
+    (4, "long", 103, 3),
+    (4, "int", 4096, 0),
+    (3, "short", 50, 1),
+    (2, "byte", 77, 0),
+    (4, "double", 3, 2),      # fewer elements than ranks: empty segments
+])
+def test_process_arrays(p, dtype, n, root):
+    res, code, _ = run_cluster(p, workers.process_arrays, (dtype, n, root))
+    assert res == [True] * p and code == 0
+
+
+def test_process_arrays_large_pipelined():
+    # > 1 MiB per segment exercises the chunked reduce-on-receive pipeline
+    res, code, _ = run_cluster(2, workers.process_arrays, ("double", 700_001, 1))
+    assert res == [True] * 2 and code == 0
+
+
+def test_loc_operators_end_to_end():
+    res, code, _ = run_cluster(3, workers.process_loc_ops)
+    assert res == [True] * 3 and code == 0
+
+
+@pytest.mark.parametrize("p,root,compress", [(1, 0, False), (2, 1, False), (3, 2, True), (4, 0, False)])
+def test_process_generic(p, root, compress):
+    res, code, _ = run_cluster(p, workers.process_generic, (40, root, compress))
+    assert res == [True] * p and code == 0
+
+
+@pytest.mark.parametrize("p,T,dtype,root,rt", [(1, 1, "double", 0, 0), (1, 3, "float", 0, 2), (2, 2, "double", 1, 1),
+                                               (3, 2, "int", 2, 0), (2, 4, "byte", 0, 3)])
+def test_thread_arrays(p, T, dtype, root, rt):
+    res, code, _ = run_cluster(p, workers.thread_arrays, (dtype, 120, root, rt), threads=T)
+    assert all(all(x) for x in res) and code == 0
+
+
+@pytest.mark.parametrize("p,T,root,rt", [(1, 2, 0, 1), (2, 2, 1, 0), (3, 2, 0, 1)])
+def test_thread_maps(p, T, root, rt):
+    res, code, _ = run_cluster(p, workers.thread_maps, (10, root, rt), threads=T)
+    assert all(all(x) for x in res) and code == 0
+
+
+def test_sorted_address_rank_rule():
+    # no hints: rank = index of "host###port" in the sorted address list (SRV:188,199-206)
+    res, code, _ = run_cluster(3, workers.control_plane, use_hints=False)
+    assert sorted(res) == [0, 1, 2] and code == 0
+
+
+def test_control_plane_logs_and_files(tmp_path):
+    res, code, logs = run_cluster(3, workers.control_plane, master_kwargs={"work_dir": str(tmp_path)})
+    assert res == [0, 1, 2] and code == 0
+    text = "\n".join(logs)
+    for r in range(3):
+        assert "[rank=%d] hello from everyone" % r in text
+    assert text.count("hello from rank0 only") == 1
+    assert "[ERROR] [rank=1] an error line" in text
+    assert (tmp_path / "mp4j_writefile_test.txt").read_text().strip() == "content-3"
+    kills = [f for f in os.listdir(tmp_path) if f.startswith("kill_")]
+    assert len(kills) == 1
+    body = (tmp_path / kills[0]).read_text()
+    assert body.count("kill -9") == 4  # three slaves + the master itself (SRV:331-342)
+
+
+def test_failing_slave_ends_job_with_code_1():
+    res, code, logs = run_cluster(2, workers.failing_slave)
+    assert code == 1
+    text = "\n".join(logs)
+    assert "slave exception:" in text and "boom" in text
