@@ -1,0 +1,259 @@
+#!/usr/bin/env python
+"""Headline benchmark (driver contract: see the task statement / DESIGN.md "bench").
+
+Metric (BASELINE.json: "allreduce bus GB/s"): config "ThreadCommSlave N procs x 8 threads, float SUM
+allreduce 64M elems (thread-level + GPU-level fusion)". Per GPU: T = 8 thread buffers of 64 Mi
+fp32 (256 MiB each, 2 GiB per GPU - far larger than the 126 MB L2, so no flush is needed between
+iterations); one step = ThreadCommSlave.allreduceArray over all N*T participants: ONE fused
+kernel per GPU (T-way register reduce -> inter-GPU reduce-scatter/allgather over NVLink -> fan-out
+to the T buffers).
+
+  busbw_per_rank = (S / t) * 2(P-1)/P,  S = 256 MiB, P = N*T participants     (nccl-tests convention)
+  value          = N * busbw_per_rank   (whole-job aggregate; weak scaling: per-GPU work is fixed)
+  vs_baseline    = value / (N * 0.1028 GB/s)  - the best per-rank allreduce bus bandwidth anywhere in
+                   the reference's published tables (README.md:347, 1 GbE), scaled to N ranks.
+
+`value` is device-timed (CUDA events around each step on the launching stream, summed, max over
+ranks). `e2e` goes through the public API with T Python threads per process and includes, every
+step, the host->device copy of all T inputs from pinned memory and the device->host read of the
+result array.
+"""
+import argparse
+import json
+import os
+import statistics
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+PUBLISHED_BEST_BUSBW_GBPS = 0.1028  # BASELINE.md §3 (README.md:347)
+
+
+def reference_arm():
+    # The reference is a Maven/Java project: `pip install /root/reference` fails ("Neither
+    # 'setup.py' nor 'pyproject.toml' found") and the image has no JDK/Maven. See DESIGN.md.
+    print(json.dumps({"impl": "reference",
+                      "unavailable": "reference is pure Java (Maven); no JDK/Maven/pyproject on this image, "
+                                     "pip install of /root/reference is not possible"}))
+    return 0
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock + throttle reasons of one GPU while the timed region runs."""
+
+    def __init__(self, index, period=0.05):
+        super().__init__(daemon=True)
+        self.index, self.period = index, period
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._nvml = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self._nvml = pynvml
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = int(vis.split(",")[index]) if vis and vis.split(",")[index].isdigit() else index
+            self._h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self._h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self._nvml = None
+
+    def run(self):
+        if self._nvml is None:
+            return
+        nv = self._nvml
+        names = {
+            getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8): "hw_slowdown",
+            getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+            getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+            getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4): "sw_power_cap",
+        }
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self._h, nv.NVML_CLOCK_SM))
+                try:
+                    mask = nv.nvmlDeviceGetCurrentClocksEventReasons(self._h)
+                except Exception:
+                    mask = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self._h)
+                for bit, name in names.items():
+                    if mask & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self._stop.wait(self.period)
+
+    def finish(self):
+        self._stop.set()
+        self.join(timeout=2)
+        return {"sm_mhz": statistics.median(self.samples) if self.samples else None,
+                "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours")
+    ap.add_argument("--elems", type=int, default=64 << 20)
+    ap.add_argument("--threads", type=int, default=8)
+    ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return reference_arm()
+
+    import torch
+    from ytk_mp4j_b200 import CommMaster, Operands, Operators, ThreadCommSlave
+    from ytk_mp4j_b200 import _native as NV
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    addr = os.environ.get("MASTER_ADDR", "127.0.0.1")
+    base_port = int(os.environ.get("MASTER_PORT", "29500"))
+    W = max(args.warmup, 3)
+    K, T, n = args.steps, args.threads, args.elems
+    torch.cuda.set_device(local_rank)
+
+    master = None
+    if rank == 0:
+        port = base_port + 17 if world > 1 else 0
+        master = CommMaster(world, port, quiet=True).start()
+        port = master.port
+    else:
+        port = base_port + 17
+    comm = ThreadCommSlave("bench", T, addr, port, rank_hint=rank, host="127.0.0.1")
+    pcs = comm.processCommSlave
+    plane = comm.init_gpu(device=local_rank)
+    fop, SUM = Operands.FLOAT_OPERAND(), Operators.Float.SUM
+    P = world * T
+    S = n * 4
+
+    bufs = [torch.full((n,), 1e-30 * (t + 1 + rank * T), dtype=torch.float32, device="cuda") for t in range(T)]
+    # ---- correctness gate before timing: known pattern through the same kernel
+    chk = [torch.full((4099,), float(rank * T + t + 1), device="cuda") for t in range(T)]
+    plane.thread_allreduce(chk, fop, SUM, 0, 4099)
+    torch.cuda.synchronize()
+    assert all(bool(torch.all(c == P * (P + 1) / 2)) for c in chk), "allreduce self-check failed"
+
+    def step():
+        plane.thread_allreduce(bufs, fop, SUM, 0, n)
+
+    for _ in range(W):
+        step()
+    torch.cuda.synchronize()
+    pcs.barrier()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    starts = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
+    ends = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for i in range(K):
+        starts[i].record()
+        step()
+        ends[i].record()
+    torch.cuda.synchronize()
+    wall_ms = (time.perf_counter() - t0) * 1e3
+    pcs.barrier()
+    clocks = sampler.finish()
+    plane.check()
+    dev_ms = sum(s.elapsed_time(e) for s, e in zip(starts, ends))
+    algo_desc = plane.last()
+    # max over ranks through our own host allreduce (double MAX)
+    dop, DMAX = Operands.DOUBLE_OPERAND(), Operators.Double.MAX
+    dev_ms = pcs.allreduce(dev_ms, dop, DMAX)
+    wall_ms = pcs.allreduce(wall_ms, dop, DMAX)
+    ms_per_step = dev_ms / K
+    busbw = (S / (ms_per_step * 1e-3)) * 2 * (P - 1) / P / 1e9
+    value = world * busbw
+    # HBM traffic of one step on one GPU: read T*S + write T*S (+ staging at N > 1)
+    hbm_bytes = 2 * T * S + (0 if world == 1 else 3 * S)
+    hbm_gbs = hbm_bytes / (ms_per_step * 1e-3) / 1e9
+
+    # ---- end to end through the public API: T python threads, pinned H2D per step, D2H of the result
+    e2e = None
+    if not args.no_e2e:
+        Ke = max(1, args.e2e_steps)
+        host_in = [torch.full((n,), 1e-30, dtype=torch.float32).pin_memory() for _ in range(T)]
+        host_out = torch.empty(n, dtype=torch.float32).pin_memory()
+        e2e_times = []
+
+        def worker(t):
+            comm.setThreadId(t)
+            torch.cuda.set_device(local_rank)
+            for it in range(Ke + 1):
+                comm.barrier()
+                if t == 0:
+                    torch.cuda.synchronize()
+                    e2e_times.append(time.perf_counter())
+                bufs[t].copy_(host_in[t], non_blocking=True)          # H2D of this step's input
+                torch.cuda.current_stream().synchronize()
+                comm.allreduceArray(bufs[t], fop, SUM, 0, n)           # public API
+                if t == 0:
+                    host_out.copy_(bufs[0], non_blocking=True)         # D2H read of the result
+                    torch.cuda.synchronize()
+                    e2e_times.append(time.perf_counter())
+        ths = [threading.Thread(target=worker, args=(t,)) for t in range(T)]
+        for th in ths:
+            th.start()
+        for th in ths:
+            th.join()
+        per = [(e2e_times[2 * i + 1] - e2e_times[2 * i]) * 1e3 for i in range(1, Ke + 1)]  # drop warm-up
+        e2e_ms = pcs.allreduce(sum(per) / len(per), dop, DMAX)
+        e2e_busbw = (S / (e2e_ms * 1e-3)) * 2 * (P - 1) / P / 1e9
+        e2e = {"value": round(world * e2e_busbw, 3), "unit": "GB/s", "ms_per_step": round(e2e_ms, 3),
+               "steps": Ke, "h2d_bytes_per_step": T * S, "d2h_bytes_per_step": S,
+               "api": "ThreadCommSlave.allreduceArray (T python threads, pinned host tensors)"}
+
+    pcs.barrier()
+    comm.close(0)
+    if master is not None:
+        master.stop(timeout_s=10)
+        master.close()
+    if rank == 0:
+        out = {
+            "metric": "allreduce_bus_bandwidth_aggregate",
+            "value": round(value, 3),
+            "unit": "GB/s",
+            "n_gpus": world,
+            "steps": K,
+            "warmup": W,
+            "ms_per_step": round(ms_per_step, 4),
+            "higher_is_better": True,
+            "scaling": "weak",
+            "vs_baseline": round(value / (world * PUBLISHED_BEST_BUSBW_GBPS), 1),
+            "dtype": "fp32",
+            "data": "synthetic",
+            "impl": "ours",
+            "config": {
+                "model": "ThreadCommSlave allreduceArray float SUM (BASELINE.json config 3)",
+                "procs": world, "threads_per_proc": T, "participants": P,
+                "elems_per_array": n, "bytes_per_array": S, "global_batch": P, "seq_len": n,
+                "parallelism": "dp%d x %d threads" % (world, T),
+                "l2_policy": "inputs (2 GiB per GPU) larger than L2; no flush needed",
+                "baseline_number": "0.1028 GB/s per-rank bus bandwidth (README.md:347, 1 GbE) x N ranks",
+                "kernel": algo_desc,
+            },
+            "busbw_per_rank_GBps": round(busbw, 3),
+            "hbm_GBps_per_gpu": round(hbm_gbs, 1),
+            "wall_ms_per_step": round(wall_ms / K, 4),
+            "clocks": clocks,
+            "gpu_launches": K,
+            "e2e": e2e,
+        }
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+            out["hbm_frac_of_measured"] = round(hbm_gbs / peaks["hbm_gbs"], 3)
+        except Exception:
+            pass
+        print(json.dumps(out))
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

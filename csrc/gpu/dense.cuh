@@ -1,0 +1,43 @@
+// Argument blocks of the dense collective kernels (shared by the kernels and the host launcher).
+#pragma once
+#include "peer.cuh"
+
+namespace mp4j {
+
+// One work item per rank of the "gather-reduce-scatter" kernel: reduce elements [lo, hi) over the
+// ranks in src_mask (ascending rank order => identical bits everywhere) and store the result into
+// the heaps of the ranks in dst_mask and/or a local pointer. All seven array collectives are
+// instances of this shape (see dense.cu).
+struct GrsItem {
+  long long lo, hi;        // element range (bytes when the op is COPY)
+  unsigned src_mask;       // which ranks' heaps are read
+  unsigned dst_mask;       // which ranks' heaps are written
+  void* dst_local;         // optional: element 0 of a local (non-symmetric) output array
+  const void* src_local;   // optional: local input copied into this rank's heap first (one-shot)
+};
+
+struct GrsArgs {
+  PeerTable tab;
+  unsigned long long src_off;  // byte offset in every heap of element 0 of the source array
+  unsigned long long dst_off;  // byte offset in every heap of element 0 of the destination array
+  int entry_barrier;
+  int exit_barrier;
+  int vec_ok;                  // local src/dst pointers are 16-byte congruent with the heap addresses
+  int pad_;
+  GrsItem item[kMaxRanks];     // indexed by rank in emulation, [0] otherwise
+};
+
+// Fused thread-level + inter-GPU allreduce (ThreadCommSlave.allreduceArray on CUDA tensors).
+struct ThreadArgs {
+  PeerTable tab;
+  int T;                        // thread buffers per rank
+  int fanout;                   // 1: result to all T buffers; 0: only to bufs[dst_index]
+  int dst_index;
+  int pad_;
+  long long from, to;           // element range
+  unsigned long long stg_off;   // byte offset in every heap of the per-block staging slots
+  unsigned long long slot_bytes;  // bytes per block slot (multiple of 16 * world)
+  void* bufs[kMaxRanks][MP4J_MAX_THREADS];  // [rank][thread] in emulation, [0][thread] otherwise
+};
+
+}  // namespace mp4j

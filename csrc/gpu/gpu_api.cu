@@ -1,0 +1,164 @@
+// extern "C" surface of the GPU data plane (include/mp4j_gpu.h).
+#include <string.h>
+
+#include "../../include/mp4j.h"
+#include "../capi/capi_util.h"
+#include "../host/process_comm.h"
+#include "gpu_plane.h"
+
+using namespace mp4j;
+
+struct mp4j_gpu {
+  GpuPlane* g;
+  bool owned_by_comm;
+};
+
+static void gpu_dtor(mp4j_comm* c) {
+  auto* h = (mp4j_gpu*)c->gpu;
+  if (!h) return;
+  delete h->g;
+  delete h;
+  c->gpu = nullptr;
+}
+
+static GpuOptions make_opts(size_t heap_bytes, size_t staging_bytes) {
+  GpuOptions o;
+  o.load_env();
+  if (heap_bytes) o.heap_bytes = heap_bytes;
+  if (staging_bytes) o.staging_bytes = staging_bytes;
+  return o;
+}
+
+static void copy_out(const std::string& s, char* buf, size_t n) {
+  if (!n) return;
+  size_t k = s.size() < n - 1 ? s.size() : n - 1;
+  memcpy(buf, s.data(), k);
+  buf[k] = 0;
+}
+
+extern "C" {
+
+int mp4j_gpu_init(mp4j_comm* c, int device, size_t heap_bytes, size_t staging_bytes, mp4j_gpu** out) {
+  MP4J_API_BEGIN
+  if (!c->gpu) {
+    auto* h = new mp4j_gpu{nullptr, true};
+    try {
+      h->g = GpuPlane::create_real(c->pc, device, make_opts(heap_bytes, staging_bytes));
+    } catch (...) {
+      delete h;
+      throw;
+    }
+    c->gpu = h;
+    c->gpu_dtor = gpu_dtor;
+  }
+  *out = (mp4j_gpu*)c->gpu;
+  MP4J_API_END
+}
+
+int mp4j_gpu_emu_create(int world, int device, size_t heap_bytes, size_t staging_bytes, mp4j_gpu** out) {
+  MP4J_API_BEGIN
+  auto* h = new mp4j_gpu{nullptr, false};
+  try {
+    h->g = GpuPlane::create_emulated(world, device, make_opts(heap_bytes, staging_bytes));
+  } catch (...) {
+    delete h;
+    throw;
+  }
+  *out = h;
+  MP4J_API_END
+}
+
+void mp4j_gpu_destroy(mp4j_gpu* g) {
+  if (!g || g->owned_by_comm) return;
+  delete g->g;
+  delete g;
+}
+
+int mp4j_gpu_world(mp4j_gpu* g) { return g->g->world(); }
+int mp4j_gpu_rank(mp4j_gpu* g) { return g->g->rank(); }
+int mp4j_gpu_has_multicast(mp4j_gpu* g) { return g->g->has_multicast() ? 1 : 0; }
+
+int mp4j_gpu_describe(mp4j_gpu* g, char* buf, size_t n) {
+  MP4J_API_BEGIN
+  copy_out(g->g->describe(), buf, n);
+  MP4J_API_END
+}
+
+int mp4j_gpu_last(mp4j_gpu* g, char* buf, size_t n) {
+  MP4J_API_BEGIN
+  const CollStat& s = g->g->last();
+  copy_out(std::string(s.name) + " algo=" + s.algo + " bytes=" + std::to_string(s.bytes) +
+               " grid=" + std::to_string(s.grid) + " staged=" + (s.staged ? "1" : "0"),
+           buf, n);
+  MP4J_API_END
+}
+
+int mp4j_gpu_alloc(mp4j_gpu* g, size_t bytes, size_t* off) {
+  MP4J_API_BEGIN
+  *off = g->g->alloc(bytes);
+  MP4J_API_END
+}
+int mp4j_gpu_free(mp4j_gpu* g, size_t off) {
+  MP4J_API_BEGIN
+  g->g->free(off);
+  MP4J_API_END
+}
+void* mp4j_gpu_ptr(mp4j_gpu* g, int rank, size_t off) { return g->g->ptr(rank, off); }
+int mp4j_gpu_check(mp4j_gpu* g) {
+  MP4J_API_BEGIN
+  g->g->check_error();
+  MP4J_API_END
+}
+
+int mp4j_gpu_allreduce(mp4j_gpu* g, void* const* arrs, int dtype, int op, int64_t from, int64_t to, int algo,
+                       void* stream) {
+  MP4J_API_BEGIN
+  g->g->allreduce(arrs, dtype, op, from, to, algo, (cudaStream_t)stream);
+  MP4J_API_END
+}
+int mp4j_gpu_reduce_scatter(mp4j_gpu* g, void* const* arrs, int dtype, int op, int64_t from,
+                            const int64_t* counts, int algo, void* stream) {
+  MP4J_API_BEGIN
+  g->g->reduce_scatter(arrs, dtype, op, from, counts, algo, (cudaStream_t)stream);
+  MP4J_API_END
+}
+int mp4j_gpu_allgather(mp4j_gpu* g, void* const* arrs, int dtype, const int64_t* froms, const int64_t* tos,
+                       int algo, void* stream) {
+  MP4J_API_BEGIN
+  g->g->allgather(arrs, dtype, froms, tos, algo, (cudaStream_t)stream);
+  MP4J_API_END
+}
+int mp4j_gpu_broadcast(mp4j_gpu* g, void* const* arrs, int dtype, int64_t from, int64_t to, int root, int algo,
+                       void* stream) {
+  MP4J_API_BEGIN
+  g->g->broadcast(arrs, dtype, from, to, root, algo, (cudaStream_t)stream);
+  MP4J_API_END
+}
+int mp4j_gpu_gather(mp4j_gpu* g, void* const* arrs, int dtype, const int64_t* froms, const int64_t* tos,
+                    int root, void* stream) {
+  MP4J_API_BEGIN
+  g->g->gather(arrs, dtype, froms, tos, root, (cudaStream_t)stream);
+  MP4J_API_END
+}
+int mp4j_gpu_scatter(mp4j_gpu* g, void* const* arrs, int dtype, const int64_t* froms, const int64_t* tos,
+                     int root, void* stream) {
+  MP4J_API_BEGIN
+  g->g->scatter(arrs, dtype, froms, tos, root, (cudaStream_t)stream);
+  MP4J_API_END
+}
+int mp4j_gpu_reduce(mp4j_gpu* g, void* const* arrs, int dtype, int op, int64_t from, int64_t to, int root,
+                    int algo, void* stream) {
+  MP4J_API_BEGIN
+  g->g->reduce(arrs, dtype, op, from, to, root, algo, (cudaStream_t)stream);
+  MP4J_API_END
+}
+int mp4j_gpu_thread_allreduce(mp4j_gpu* g, void* const* bufs, int T, int dtype, int op, int64_t from,
+                              int64_t to, int fanout, int dst, int local_only, int thread_algo, int algo,
+                              void* stream) {
+  MP4J_API_BEGIN
+  g->g->thread_allreduce(bufs, T, dtype, op, from, to, fanout, dst, local_only != 0,
+                         (thread_algo & 0xff) | (algo << 16), (cudaStream_t)stream);
+  MP4J_API_END
+}
+
+}  // extern "C"

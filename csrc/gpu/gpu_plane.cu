@@ -1,0 +1,442 @@
+#include "gpu_plane.h"
+
+#include <stdlib.h>
+#include <string.h>
+
+#include <algorithm>
+
+#include "../host/process_comm.h"
+#include "cuda_check.h"
+#include "launch.h"
+
+namespace mp4j {
+
+namespace {
+size_t env_size(const char* name, size_t dflt) {
+  const char* v = getenv(name);
+  return (v && *v) ? (size_t)strtoull(v, nullptr, 10) : dflt;
+}
+size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+}  // namespace
+
+void GpuOptions::load_env() {
+  heap_bytes = env_size("MP4J_HEAP_BYTES", heap_bytes);
+  staging_bytes = env_size("MP4J_STAGING_BYTES", staging_bytes);
+  thread_slot_bytes = env_size("MP4J_THREAD_SLOT_BYTES", thread_slot_bytes);
+  oneshot_max_bytes = env_size("MP4J_ONE_SHOT_MAX_BYTES", oneshot_max_bytes);
+  nvls_min_bytes = env_size("MP4J_NVLS_MIN_BYTES", nvls_min_bytes);
+  max_blocks = (int)env_size("MP4J_MAX_BLOCKS", (size_t)max_blocks);
+  if (getenv("MP4J_NVLS")) want_multicast = atoi(getenv("MP4J_NVLS")) != 0;
+  if (getenv("MP4J_GPU_TIMEOUT_S")) timeout_s = atof(getenv("MP4J_GPU_TIMEOUT_S"));
+}
+
+GpuPlane* GpuPlane::create_real(ProcessComm* pc, int device, GpuOptions opt) {
+  std::unique_ptr<GpuPlane> g(new GpuPlane());
+  g->device_ = device;
+  MP4J_CUDA(cudaSetDevice(device));
+  g->heap_.init_real(pc, device, opt.heap_bytes, opt.want_multicast);
+  g->finish_init(opt);
+  return g.release();
+}
+
+GpuPlane* GpuPlane::create_emulated(int world, int device, GpuOptions opt) {
+  std::unique_ptr<GpuPlane> g(new GpuPlane());
+  g->device_ = device;
+  MP4J_CUDA(cudaSetDevice(device));
+  g->heap_.init_emulated(world, device, opt.heap_bytes);
+  g->finish_init(opt);
+  return g.release();
+}
+
+void GpuPlane::finish_init(GpuOptions opt) {
+  opt_ = opt;
+  MP4J_CUDA(cudaDeviceGetAttribute(&sms_, cudaDevAttrMultiProcessorCount, device_));
+  void* h = nullptr;
+  MP4J_CUDA(cudaHostAlloc(&h, 64, cudaHostAllocMapped));
+  err_host_ = (uint32_t*)h;
+  *err_host_ = 0;
+  void* d = nullptr;
+  MP4J_CUDA(cudaHostGetDevicePointer(&d, h, 0));
+  err_dev_ = (uint32_t*)d;
+  // heap layout
+  size_t off = kSigPadBytes;
+  const size_t one = align_up(opt_.oneshot_max_bytes + 256, 256);
+  oneshot_off_[0] = off;
+  oneshot_off_[1] = off + one;
+  off += 2 * one;
+  const int tgrid = std::min(kMaxBlocks, sms_ * thread_max_blocks_per_sm());
+  opt_.thread_slot_bytes = align_up(opt_.thread_slot_bytes, 16 * 8 * 8);
+  thread_off_ = align_up(off, 4096);
+  thread_bytes_ = (size_t)tgrid * opt_.thread_slot_bytes;
+  off = thread_off_ + thread_bytes_;
+  staging_off_ = align_up(off, 4096);
+  opt_.staging_bytes = align_up(opt_.staging_bytes, 4096);
+  off = staging_off_ + opt_.staging_bytes;
+  user_off_ = align_up(off, 4096);
+  if (user_off_ > heap_.bytes())
+    throw Error("symmetric heap too small: need at least " + std::to_string(user_off_) + " bytes for pads+staging, have " +
+                std::to_string(heap_.bytes()));
+}
+
+GpuPlane::~GpuPlane() {
+  cudaDeviceSynchronize();
+  if (err_host_) cudaFreeHost(err_host_);
+}
+
+std::string GpuPlane::describe() const {
+  return std::string("mode=") + heap_.mode() + " world=" + std::to_string(world()) + " rank=" + std::to_string(rank()) +
+         " heap=" + std::to_string(heap_.bytes()) + " staging=" + std::to_string(opt_.staging_bytes) +
+         " user_off=" + std::to_string(user_off_) + " sms=" + std::to_string(sms_) +
+         (heap_.notes().empty() ? "" : " notes=[" + heap_.notes() + "]");
+}
+
+PeerTable GpuPlane::table() const {
+  PeerTable t{};
+  t.world = world();
+  t.rank = rank();
+  t.emulate = emulated() ? 1 : 0;
+  for (int q = 0; q < world(); ++q) {
+    t.heap[q] = heap_.base(q);
+    t.sig[q] = (uint32_t*)heap_.base(q);
+  }
+  t.mc_heap = heap_.mc_base();
+  t.err = err_dev_;
+  t.timeout_ns = (unsigned long long)(opt_.timeout_s * 1e9);
+  return t;
+}
+
+size_t GpuPlane::alloc(size_t bytes) {
+  std::lock_guard<std::mutex> lk(alloc_mu_);
+  bytes = align_up(std::max<size_t>(bytes, 1), 256);
+  size_t cur = user_off_;
+  for (auto& kv : used_) {  // ordered by offset: first fit
+    if (kv.first - cur >= bytes) break;
+    cur = kv.first + kv.second;
+  }
+  if (cur + bytes > heap_.bytes())
+    throw Error("symmetric heap exhausted (raise MP4J_HEAP_BYTES): want " + std::to_string(bytes));
+  used_[cur] = bytes;
+  return cur;
+}
+
+void GpuPlane::free(size_t off) {
+  std::lock_guard<std::mutex> lk(alloc_mu_);
+  used_.erase(off);
+}
+
+void GpuPlane::check_error() {
+  if (err_host_ && *err_host_) {
+    *err_host_ = 0;
+    throw Error("GPU collective: a peer did not arrive within the device-side timeout (dead or diverged rank?)");
+  }
+}
+
+int GpuPlane::pick_grid(long long max_units, int max_blocks_per_sm) const {
+  long long cap = (long long)sms_ * max_blocks_per_sm;
+  // emulation: all rows of the cooperative grid must be co-resident, and instantiations other than
+  // the probed one may only fit one 512-thread block per SM
+  if (emulated()) cap = sms_ / world();
+  cap = std::min<long long>(cap, kMaxBlocks);
+  if (opt_.max_blocks > 0) cap = std::min<long long>(cap, opt_.max_blocks);
+  cap = std::max<long long>(cap, 1);
+  long long want = (max_units + (long long)grs_threads() * 2 - 1) / ((long long)grs_threads() * 2);
+  return (int)std::max<long long>(1, std::min(want, cap));
+}
+
+// true if every local array sits inside the symmetric user region at one common offset
+bool GpuPlane::offsets_symmetric(void* const* arrs, size_t* off) const {
+  const int L = local_ranks();
+  for (int i = 0; i < L; ++i) {
+    const int r = emulated() ? i : rank();
+    const char* p = (const char*)arrs[i];
+    const char* b = heap_.base(r);
+    if (p < b + user_off_ || p >= b + heap_.bytes()) return false;
+    const size_t o = (size_t)(p - b);
+    if (i == 0) *off = o;
+    else if (o != *off) return false;
+  }
+  return true;
+}
+
+void GpuPlane::run_grs(const char* name, void* const* arrs, int dtype, int op, const int64_t* lo, const int64_t* hi,
+                       const unsigned* src_mask, const unsigned* dst_mask, bool reduce_like, int algo,
+                       cudaStream_t s) {
+  const int p = world();
+  const int L = local_ranks();
+  const size_t es = dtype_size(dtype);
+  if (es == 0) throw Error("unknown dtype");
+  if (op != MP4J_COPY && !op_valid_for(dtype, op)) throw Error("operator is not defined for this dtype");
+  // unit conversion: COPY kernels work on bytes
+  const long long scale = (op == MP4J_COPY) ? (long long)es : 1;
+  const size_t kes = (op == MP4J_COPY) ? 1 : es;
+  long long span_lo = INT64_MAX, span_hi = INT64_MIN, max_n = 0;
+  for (int q = 0; q < p; ++q) {
+    if (hi[q] <= lo[q]) continue;
+    span_lo = std::min<long long>(span_lo, lo[q]);
+    span_hi = std::max<long long>(span_hi, hi[q]);
+    max_n = std::max<long long>(max_n, hi[q] - lo[q]);
+  }
+  if (max_n == 0) return;
+  const size_t span_bytes = (size_t)(span_hi - span_lo) * es;
+
+  GrsArgs a{};
+  a.tab = table();
+  a.entry_barrier = 1;
+  a.exit_barrier = 1;
+  a.vec_ok = 1;
+  const bool nvls_ok = has_multicast() && nvls_supported(dtype, op) &&
+                       (algo == MP4J_ALGO_NVLS || (algo == MP4J_ALGO_AUTO && span_bytes >= opt_.nvls_min_bytes));
+  last_.name = name;
+  last_.bytes = span_bytes;
+
+  size_t sym_off = 0;
+  const bool zero_copy = offsets_symmetric(arrs, &sym_off);
+  last_.staged = !zero_copy;
+  last_.algo = nvls_ok ? "nvls" : "p2p";
+  if (zero_copy) {
+    a.src_off = a.dst_off = sym_off;
+    for (int i = 0; i < L; ++i) {
+      const int q = emulated() ? i : rank();
+      GrsItem& it = a.item[i];
+      it.lo = lo[q] * scale;
+      it.hi = std::max(hi[q], lo[q]) * scale;
+      it.src_mask = src_mask[q];
+      it.dst_mask = dst_mask[q];
+    }
+    const int grid = pick_grid((max_n * (long long)es + 15) / 16, grs_max_blocks_per_sm());
+    last_.grid = grid;
+    launch_grs(dtype, op, nvls_ok, a, grid, s);
+    return;
+  }
+  // ---- staged: window the span through the symmetric staging buffer
+  const long long win = (long long)(opt_.staging_bytes / es);
+  for (long long w0 = span_lo; w0 < span_hi; w0 += win) {
+    const long long w1 = std::min(span_hi, w0 + win);
+    long long wmax = 0;
+    for (int q = 0; q < p; ++q) wmax = std::max(wmax, std::min<long long>(hi[q], w1) - std::max<long long>(lo[q], w0));
+    if (wmax <= 0) continue;
+    for (int i = 0; i < L; ++i) {
+      const int r = emulated() ? i : rank();
+      MP4J_CUDA(cudaMemcpyAsync(heap_.base(r) + staging_off_, (const char*)arrs[i] + (size_t)w0 * es,
+                                (size_t)(w1 - w0) * es, cudaMemcpyDeviceToDevice, s));
+    }
+    // element w0 lives at staging_off_: offset of element 0 = staging_off_ - w0*es (mod 2^64)
+    a.src_off = a.dst_off = (unsigned long long)staging_off_ - (unsigned long long)w0 * es;
+    for (int i = 0; i < L; ++i) {
+      const int q = emulated() ? i : rank();
+      GrsItem& it = a.item[i];
+      const long long l = std::max<long long>(lo[q], w0), h = std::min<long long>(hi[q], w1);
+      it.lo = l * scale;
+      it.hi = std::max(h, l) * scale;
+      it.src_mask = src_mask[q];
+      it.dst_mask = dst_mask[q];
+    }
+    const int grid = pick_grid((wmax * (long long)es + 15) / 16, grs_max_blocks_per_sm());
+    last_.grid = grid;
+    launch_grs(dtype, op, nvls_ok, a, grid, s);
+    for (int i = 0; i < L; ++i) {
+      const int r = emulated() ? i : rank();
+      MP4J_CUDA(cudaMemcpyAsync((char*)arrs[i] + (size_t)w0 * es, heap_.base(r) + staging_off_,
+                                (size_t)(w1 - w0) * es, cudaMemcpyDeviceToDevice, s));
+    }
+  }
+  (void)reduce_like;
+  (void)kes;
+}
+
+void GpuPlane::allreduce(void* const* arrs, int dtype, int op, int64_t from, int64_t to, int algo, cudaStream_t s) {
+  check_from_to(from, to);
+  const int p = world();
+  if (p == 1 || from == to) return;
+  const size_t es = dtype_size(dtype);
+  const size_t bytes = (size_t)(to - from) * es;
+  if (!op_valid_for(dtype, op) || op == MP4J_COPY) throw Error("operator is not defined for this dtype");
+  const unsigned full = (1u << p) - 1u;
+  const bool oneshot = algo == MP4J_ALGO_ONESHOT || (algo == MP4J_ALGO_AUTO && bytes <= opt_.oneshot_max_bytes);
+  if (oneshot && bytes <= opt_.oneshot_max_bytes) {
+    // every rank copies its input into a double-buffered symmetric slot, then reads all p slots
+    GrsArgs a{};
+    a.tab = table();
+    a.entry_barrier = 1;
+    a.exit_barrier = 0;  // safe: the slot alternates, see DESIGN.md "one-shot slot reuse"
+    const size_t slot = oneshot_off_[oneshot_next_];
+    oneshot_next_ ^= 1;
+    a.src_off = a.dst_off = (unsigned long long)slot - (unsigned long long)from * es;
+    a.vec_ok = 1;
+    const int L = local_ranks();
+    for (int i = 0; i < L; ++i) {
+      GrsItem& it = a.item[i];
+      it.lo = from;
+      it.hi = to;
+      it.src_mask = full;
+      it.dst_mask = 0;
+      it.src_local = arrs[i];
+      it.dst_local = arrs[i];
+      if ((((uintptr_t)arrs[i] + (size_t)from * es) & 15) != 0) a.vec_ok = 0;
+    }
+    const int grid = pick_grid((long long)(bytes + 15) / 16, grs_max_blocks_per_sm());
+    last_ = CollStat{"allreduce", "oneshot", bytes, grid, false};
+    launch_grs(dtype, op, false, a, grid, s);
+    return;
+  }
+  int64_t lo[kMaxRanks], hi[kMaxRanks];
+  unsigned sm[kMaxRanks], dm[kMaxRanks];
+  // internal partition is free to be 16-byte friendly: results do not depend on who reduces what
+  const long long n = to - from, epv = (long long)(16 / es);
+  const long long per = ((n + p - 1) / p + epv - 1) / epv * epv;
+  for (int q = 0; q < p; ++q) {
+    lo[q] = std::min<long long>(to, from + q * per);
+    hi[q] = std::min<long long>(to, from + (q + 1) * per);
+    sm[q] = dm[q] = full;
+  }
+  run_grs("allreduce", arrs, dtype, op, lo, hi, sm, dm, true, algo == MP4J_ALGO_ONESHOT ? MP4J_ALGO_AUTO : algo, s);
+  if (strcmp(last_.algo, "p2p") == 0) last_.algo = "twoshot";
+}
+
+void GpuPlane::reduce_scatter(void* const* arrs, int dtype, int op, int64_t from, const int64_t* counts, int algo,
+                              cudaStream_t s) {
+  const int p = world();
+  check_from_counts(from, counts, p);
+  if (p == 1) return;
+  int64_t lo[kMaxRanks], hi[kMaxRanks];
+  unsigned sm[kMaxRanks], dm[kMaxRanks];
+  froms_tos_from_counts(from, counts, p, lo, hi);
+  for (int q = 0; q < p; ++q) {
+    sm[q] = (1u << p) - 1u;
+    dm[q] = 1u << q;
+  }
+  run_grs("reduce_scatter", arrs, dtype, op, lo, hi, sm, dm, true, algo, s);
+}
+
+void GpuPlane::allgather(void* const* arrs, int dtype, const int64_t* froms, const int64_t* tos, int algo,
+                         cudaStream_t s) {
+  const int p = world();
+  check_froms_tos(froms, tos, p);
+  if (p == 1) return;
+  unsigned sm[kMaxRanks], dm[kMaxRanks];
+  for (int q = 0; q < p; ++q) {
+    sm[q] = 1u << q;
+    dm[q] = (1u << p) - 1u;
+  }
+  run_grs("allgather", arrs, dtype, MP4J_COPY, froms, tos, sm, dm, false, algo, s);
+}
+
+void GpuPlane::broadcast(void* const* arrs, int dtype, int64_t from, int64_t to, int root, int algo, cudaStream_t s) {
+  const int p = world();
+  check_from_to(from, to);
+  if (root < 0 || root >= p) throw Error("root rank out of range");
+  if (p == 1 || from == to) return;
+  // every rank pulls one balanced slice from the root and pushes it to everybody: the root's
+  // egress is N(p-1)/p instead of N(p-1), the shape of the reference's scatter+allgather (PCS:750-770)
+  int64_t lo[kMaxRanks], hi[kMaxRanks];
+  unsigned sm[kMaxRanks], dm[kMaxRanks];
+  balanced_split(from, to, p, lo, hi);
+  for (int q = 0; q < p; ++q) {
+    sm[q] = 1u << root;
+    dm[q] = (1u << p) - 1u;
+  }
+  run_grs("broadcast", arrs, dtype, MP4J_COPY, lo, hi, sm, dm, false, algo, s);
+}
+
+void GpuPlane::gather(void* const* arrs, int dtype, const int64_t* froms, const int64_t* tos, int root,
+                      cudaStream_t s) {
+  const int p = world();
+  check_froms_tos(froms, tos, p);
+  if (root < 0 || root >= p) throw Error("root rank out of range");
+  if (p == 1) return;
+  unsigned sm[kMaxRanks], dm[kMaxRanks];
+  for (int q = 0; q < p; ++q) {  // every rank pushes its own segment into the root's array
+    sm[q] = 1u << q;
+    dm[q] = 1u << root;
+  }
+  run_grs("gather", arrs, dtype, MP4J_COPY, froms, tos, sm, dm, false, MP4J_ALGO_TWOSHOT, s);
+}
+
+void GpuPlane::scatter(void* const* arrs, int dtype, const int64_t* froms, const int64_t* tos, int root,
+                       cudaStream_t s) {
+  const int p = world();
+  check_froms_tos(froms, tos, p);
+  if (root < 0 || root >= p) throw Error("root rank out of range");
+  if (p == 1) return;
+  unsigned sm[kMaxRanks], dm[kMaxRanks];
+  for (int q = 0; q < p; ++q) {  // every rank pulls its own segment out of the root's array
+    sm[q] = 1u << root;
+    dm[q] = 1u << q;
+  }
+  run_grs("scatter", arrs, dtype, MP4J_COPY, froms, tos, sm, dm, false, MP4J_ALGO_TWOSHOT, s);
+}
+
+void GpuPlane::reduce(void* const* arrs, int dtype, int op, int64_t from, int64_t to, int root, int algo,
+                      cudaStream_t s) {
+  const int p = world();
+  check_from_to(from, to);
+  if (root < 0 || root >= p) throw Error("root rank out of range");
+  if (p == 1 || from == to) return;
+  int64_t lo[kMaxRanks], hi[kMaxRanks];
+  unsigned sm[kMaxRanks], dm[kMaxRanks];
+  balanced_split(from, to, p, lo, hi);
+  for (int q = 0; q < p; ++q) {  // reduce-scatter whose results land directly in the root
+    sm[q] = (1u << p) - 1u;
+    dm[q] = 1u << root;
+  }
+  run_grs("reduce", arrs, dtype, op, lo, hi, sm, dm, true, algo, s);
+}
+
+void GpuPlane::thread_allreduce(void* const* bufs, int T, int dtype, int op, int64_t from, int64_t to, int fanout,
+                                int dst, bool local_only, int algo, cudaStream_t s) {
+  check_from_to(from, to);
+  if (T < 1 || T > MP4J_MAX_THREADS) throw Error("thread count out of range");
+  if (dst < 0 || dst >= T) throw Error("dst thread out of range");
+  if (!op_valid_for(dtype, op) || op == MP4J_COPY) throw Error("operator is not defined for this dtype");
+  if (from == to) return;
+  const size_t es = dtype_size(dtype);
+  const size_t nbytes = (size_t)(to - from) * es;
+  const int p = local_only ? 1 : world();
+  const int L = local_ranks();
+  bool vec = (nbytes % 16) == 0;
+  for (int i = 0; i < L * T; ++i)
+    if ((((uintptr_t)bufs[i] + (size_t)from * es) & 15) != 0) vec = false;
+  const int vec_flag = vec ? 0 : 0x100;
+  ThreadArgs a{};
+  a.T = T;
+  a.fanout = fanout;
+  a.dst_index = dst;
+  a.from = from;
+  a.to = to;
+  const long long units = (long long)(nbytes / (vec ? 16 : es));
+  if (p == 1) {
+    // intra-GPU only; in emulation each emulated rank reduces its own T buffers
+    const bool cluster = vec && (algo & 0xff) == 1 && thread_cluster_supported(dtype, op, T, 1);
+    for (int i = 0; i < L; ++i) {
+      a.tab = table();
+      a.tab.world = 1;
+      a.tab.emulate = 0;
+      a.tab.rank = 0;
+      for (int t = 0; t < T; ++t) a.bufs[0][t] = bufs[i * T + t];
+      long long cap = (long long)sms_ * thread_max_blocks_per_sm();
+      if (opt_.max_blocks > 0) cap = std::min<long long>(cap, opt_.max_blocks);
+      const int grid = (int)std::max<long long>(1, std::min<long long>(cap, (units + thread_threads() - 1) / thread_threads()));
+      last_ = CollStat{"thread_allreduce", cluster ? "cluster-dsmem" : "register", nbytes, grid, false};
+      launch_thread_allreduce(dtype, op, false, a, grid, (cluster ? 1 : 0) | vec_flag, s);
+    }
+    return;
+  }
+  a.tab = table();
+  for (int i = 0; i < L; ++i)
+    for (int t = 0; t < T; ++t) a.bufs[i][t] = bufs[i * T + t];
+  const size_t slot = opt_.thread_slot_bytes / (16 * p) * (16 * p);
+  a.slot_bytes = slot;
+  a.stg_off = thread_off_;
+  long long cap = (long long)sms_ * thread_max_blocks_per_sm();
+  if (emulated()) cap /= p;
+  cap = std::min<long long>(cap, (long long)(thread_bytes_ / slot));
+  cap = std::min<long long>(cap, kMaxBlocks);
+  if (opt_.max_blocks > 0) cap = std::min<long long>(cap, opt_.max_blocks);
+  const int grid = (int)std::max<long long>(1, std::min<long long>(cap, (long long)((nbytes + slot - 1) / slot)));
+  const bool nvls = vec && has_multicast() && nvls_supported(dtype, op) &&
+                    (algo >> 16 == MP4J_ALGO_NVLS || (algo >> 16 == MP4J_ALGO_AUTO && nbytes >= opt_.nvls_min_bytes));
+  last_ = CollStat{"thread_allreduce", nvls ? "fused-nvls" : "fused-p2p", nbytes, grid, false};
+  launch_thread_allreduce(dtype, op, nvls, a, grid, 0 | vec_flag, s);
+}
+
+}  // namespace mp4j

@@ -1,0 +1,105 @@
+// GpuPlane: host-side owner of the GPU data plane of one communicator - symmetric heap, signal
+// pads, staging windows, algorithm choice and kernel launches. One per ProcessComm ("real" mode,
+// one process per GPU) or one per test process ("emulated" mode: `world` ranks on one GPU, every
+// collective is ONE cooperative launch whose grid rows are the ranks).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <map>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "dense.cuh"
+#include "symm_heap.h"
+
+namespace mp4j {
+
+class ProcessComm;
+
+struct GpuOptions {
+  size_t heap_bytes = 1ull << 30;       // MP4J_HEAP_BYTES
+  size_t staging_bytes = 128ull << 20;  // general staging window for non-symmetric tensors
+  size_t thread_slot_bytes = 128 << 10; // per-block slot of the fused thread kernel
+  size_t oneshot_max_bytes = 256 << 10; // <= : one-shot allreduce (MP4J_ONE_SHOT_MAX_BYTES)
+  size_t nvls_min_bytes = 512 << 10;    // >= : NVLS when available (MP4J_NVLS_MIN_BYTES)
+  bool want_multicast = true;           // MP4J_NVLS=0 disables
+  int max_blocks = 0;                   // 0 = occupancy-derived (MP4J_MAX_BLOCKS)
+  double timeout_s = 60.0;              // device-side flag-wait watchdog (MP4J_GPU_TIMEOUT_S)
+  void load_env();
+};
+
+struct CollStat {  // last collective, for logs / tuning
+  const char* name = "";
+  const char* algo = "";
+  size_t bytes = 0;
+  int grid = 0;
+  bool staged = false;
+};
+
+class GpuPlane {
+ public:
+  static GpuPlane* create_real(ProcessComm* pc, int device, GpuOptions opt);
+  static GpuPlane* create_emulated(int world, int device, GpuOptions opt);
+  ~GpuPlane();
+
+  int world() const { return heap_.world(); }
+  int rank() const { return heap_.rank(); }
+  bool emulated() const { return heap_.emulated(); }
+  bool has_multicast() const { return heap_.mc_base() != nullptr; }
+  std::string describe() const;
+  const CollStat& last() const { return last_; }
+
+  // symmetric allocation: same offset on every rank. Returns the offset; ptr(rank, off) maps it.
+  size_t alloc(size_t bytes);
+  void free(size_t off);
+  void* ptr(int rank, size_t off) const { return heap_.base(rank) + off; }
+
+  // Dense collectives. `arrs`: element-0 pointers of the user arrays, one per LOCAL rank
+  // (1 in real mode, world in emulation). Ranges are element ranges. All in place.
+  void allreduce(void* const* arrs, int dtype, int op, int64_t from, int64_t to, int algo, cudaStream_t s);
+  void reduce_scatter(void* const* arrs, int dtype, int op, int64_t from, const int64_t* counts, int algo,
+                      cudaStream_t s);
+  void allgather(void* const* arrs, int dtype, const int64_t* froms, const int64_t* tos, int algo, cudaStream_t s);
+  void broadcast(void* const* arrs, int dtype, int64_t from, int64_t to, int root, int algo, cudaStream_t s);
+  void gather(void* const* arrs, int dtype, const int64_t* froms, const int64_t* tos, int root, cudaStream_t s);
+  void scatter(void* const* arrs, int dtype, const int64_t* froms, const int64_t* tos, int root, cudaStream_t s);
+  void reduce(void* const* arrs, int dtype, int op, int64_t from, int64_t to, int root, int algo, cudaStream_t s);
+  // Thread-level fused allreduce: bufs[local_rank * T + t]. fanout=0 writes only thread `dst`.
+  // local_only: skip the inter-GPU step (intra-process thread reduce, DOP:441-457).
+  void thread_allreduce(void* const* bufs, int T, int dtype, int op, int64_t from, int64_t to, int fanout, int dst,
+                        bool local_only, int algo, cudaStream_t s);
+  // Raises if a kernel reported a peer-wait timeout since the last check.
+  void check_error();
+
+ private:
+  GpuPlane() {}
+  void finish_init(GpuOptions opt);
+  int local_ranks() const { return emulated() ? world() : 1; }
+  PeerTable table() const;
+  struct Plan;
+  // Generic driver: windows + staging + one GRS launch per window.
+  void run_grs(const char* name, void* const* arrs, int dtype, int op, const int64_t* lo, const int64_t* hi,
+               const unsigned* src_mask, const unsigned* dst_mask, bool reduce_like, int algo, cudaStream_t s);
+  int pick_grid(long long max_units, int max_blocks_per_sm) const;
+  bool offsets_symmetric(void* const* arrs, size_t* off) const;
+
+  SymmHeap heap_;
+  GpuOptions opt_;
+  int device_ = 0, sms_ = 0;
+  uint32_t* err_host_ = nullptr;
+  uint32_t* err_dev_ = nullptr;
+  // heap layout (byte offsets)
+  size_t oneshot_off_[2] = {0, 0};
+  int oneshot_next_ = 0;
+  size_t thread_off_ = 0, thread_bytes_ = 0;
+  size_t staging_off_ = 0;
+  size_t user_off_ = 0;
+  // trivial first-fit allocator over [user_off_, heap bytes)
+  std::mutex alloc_mu_;
+  std::map<size_t, size_t> used_;  // off -> bytes
+  CollStat last_;
+};
+
+}  // namespace mp4j

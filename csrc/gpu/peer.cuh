@@ -1,0 +1,217 @@
+// Device-side building blocks of the GPU data plane: the peer table every kernel receives,
+// system-scope flag primitives, the per-block cross-GPU barrier, 16-byte vector helpers and
+// multimem (NVLS) wrappers.
+//
+// Replaces, on the device, what the reference does with a TCP connect per message plus a master
+// barrier RPC per phase (PCS:391-425, 503, 731, 1153, 1367): kernels load/store peer HBM directly
+// over NVLink and synchronise through signal pads in symmetric memory.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/mp4j_types.h"
+#include "../core/ops.h"
+
+namespace mp4j {
+
+constexpr int kMaxRanks = MP4J_MAX_RANKS;
+constexpr int kMaxBlocks = 1024;                      // flag rows per signal pad
+constexpr size_t kSigFlagsBytes = kMaxBlocks * kMaxRanks * sizeof(uint32_t);
+constexpr size_t kSigEpochOff = kSigFlagsBytes;       // per-block epoch counters (local use only)
+constexpr size_t kSigPadBytes = 64 * 1024;            // flags (32 KiB) + epochs (4 KiB) + spare
+
+struct PeerTable {
+  int world;
+  int rank;                       // real mode; emulation derives the rank from blockIdx.y
+  int emulate;                    // 1: all "ranks" live on this GPU, one grid row per rank
+  int pad_;
+  char* heap[kMaxRanks];          // every rank's symmetric heap as mapped HERE
+  uint32_t* sig[kMaxRanks];       // every rank's signal pad as mapped HERE
+  char* mc_heap;                  // multicast (NVLS) mapping of the heaps, or nullptr
+  uint32_t* err;                  // host-visible error word: 1 = peer wait timed out
+  unsigned long long timeout_ns;  // device-side watchdog for flag waits
+};
+
+__device__ __forceinline__ int my_rank(const PeerTable& t) { return t.emulate ? (int)blockIdx.y : t.rank; }
+
+// ---- system-scope flag access
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+
+// Waits until *flag reaches `want` (wrap-safe). Returns false on watchdog timeout, after raising
+// the host-visible error word: a dead peer must not hang every other rank's kernel.
+__device__ __forceinline__ bool wait_flag(const PeerTable& t, const uint32_t* flag, uint32_t want) {
+  if ((int32_t)(ld_acquire_sys(flag) - want) >= 0) return true;
+  unsigned long long t0 = globaltimer_ns();
+  for (unsigned spins = 1;; ++spins) {
+    if ((int32_t)(ld_acquire_sys(flag) - want) >= 0) return true;
+    if ((spins & 1023u) == 0 && globaltimer_ns() - t0 > t.timeout_ns) {
+      atomicExch((unsigned*)t.err, 1u);
+      return false;
+    }
+  }
+}
+
+// Per-block epoch counter: persists across launches in the local pad so flags never need a reset.
+struct BlockEpoch {
+  uint32_t* slot;
+  uint32_t value;
+  __device__ __forceinline__ void load(const PeerTable& t, int rank) {
+    slot = (uint32_t*)((char*)t.sig[rank] + kSigEpochOff) + blockIdx.x;
+    value = *(volatile uint32_t*)slot;
+  }
+  __device__ __forceinline__ void store() {
+    if (threadIdx.x == 0) *(volatile uint32_t*)slot = value;
+  }
+};
+
+// Cross-GPU barrier between the same-index blocks of all ranks. Data written by any thread of the
+// block before the call is visible to the peers' block after their call returns (bar.sync orders
+// the CTA's writes before the releasing thread; st.release.sys is cumulative).
+__device__ __forceinline__ void block_barrier_peers(const PeerTable& t, int rank, BlockEpoch& ep) {
+  ep.value += 1;
+  __syncthreads();
+  if (threadIdx.x < (unsigned)t.world) {
+    const int q = threadIdx.x;
+    st_release_sys(t.sig[q] + blockIdx.x * kMaxRanks + rank, ep.value);
+    wait_flag(t, t.sig[rank] + blockIdx.x * kMaxRanks + q, ep.value);
+  }
+  __syncthreads();
+}
+
+// ---- 16-byte vector moves (streaming: touched once, keep them out of L1)
+struct __align__(16) Vec16 {
+  uint32_t x, y, z, w;
+};
+__device__ __forceinline__ Vec16 ld_stream(const void* p) {
+  Vec16 v;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "l"(p));
+  return v;
+}
+// plain (coherent) load: for data another GPU or an earlier phase of this kernel produced
+__device__ __forceinline__ Vec16 ld_coherent(const void* p) {
+  Vec16 v;
+  asm volatile("ld.global.relaxed.sys.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "l"(p)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_stream(void* p, const Vec16& v) {
+  asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y),
+               "r"(v.z), "r"(v.w)
+               : "memory");
+}
+
+template <typename T, int OP>
+__device__ __forceinline__ Vec16 vec_reduce(const Vec16& a, const Vec16& b) {
+  constexpr int N = 16 / sizeof(T);
+  union U {
+    Vec16 v;
+    T e[N];
+    __device__ U() {}
+  } ua, ub;
+  ua.v = a;
+  ub.v = b;
+#pragma unroll
+  for (int i = 0; i < N; ++i) ua.e[i] = Reduce<T, OP>::apply(ua.e[i], ub.e[i]);
+  return ua.v;
+}
+
+// ---- NVLS: in-switch reduction / broadcast through the multicast mapping
+template <typename T, int OP>
+struct Nvls {
+  static constexpr bool supported = false;
+  __device__ static Vec16 ld_reduce(const void*) { return Vec16{}; }
+};
+template <>
+struct Nvls<float, MP4J_SUM> {
+  static constexpr bool supported = true;
+  __device__ __forceinline__ static Vec16 ld_reduce(const void* mc) {
+    Vec16 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                 : "l"(mc)
+                 : "memory");
+    return v;
+  }
+};
+template <>
+struct Nvls<double, MP4J_SUM> {
+  static constexpr bool supported = true;
+  __device__ __forceinline__ static Vec16 ld_reduce(const void* mc) {
+    union {
+      Vec16 v;
+      double d[2];
+    } u;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.f64 %0, [%1];" : "=d"(u.d[0]) : "l"(mc) : "memory");
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.f64 %0, [%1];"
+                 : "=d"(u.d[1])
+                 : "l"((const char*)mc + 8)
+                 : "memory");
+    return u.v;
+  }
+};
+#define MP4J_NVLS_INT(T, OPC, PTXOP, PTXTY, W)                                                            \
+  template <>                                                                                            \
+  struct Nvls<T, OPC> {                                                                                  \
+    static constexpr bool supported = true;                                                              \
+    __device__ __forceinline__ static Vec16 ld_reduce(const void* mc) {                                  \
+      union {                                                                                            \
+        Vec16 v;                                                                                         \
+        T e[16 / sizeof(T)];                                                                             \
+      } u;                                                                                               \
+      _Pragma("unroll") for (int i = 0; i < (int)(16 / sizeof(T)); ++i) {                                \
+        asm volatile("multimem.ld_reduce.relaxed.sys.global." PTXOP "." PTXTY " %0, [%1];"               \
+                     : "=" W(u.e[i])                                                                     \
+                     : "l"((const char*)mc + i * sizeof(T))                                              \
+                     : "memory");                                                                        \
+      }                                                                                                  \
+      return u.v;                                                                                        \
+    }                                                                                                    \
+  };
+MP4J_NVLS_INT(int32_t, MP4J_SUM, "add", "u32", "r")
+MP4J_NVLS_INT(int32_t, MP4J_MAX, "max", "s32", "r")
+MP4J_NVLS_INT(int32_t, MP4J_MIN, "min", "s32", "r")
+MP4J_NVLS_INT(int32_t, MP4J_BAND, "and", "b32", "r")
+MP4J_NVLS_INT(int32_t, MP4J_BOR, "or", "b32", "r")
+MP4J_NVLS_INT(int32_t, MP4J_BXOR, "xor", "b32", "r")
+MP4J_NVLS_INT(int64_t, MP4J_SUM, "add", "u64", "l")
+MP4J_NVLS_INT(int64_t, MP4J_MAX, "max", "s64", "l")
+MP4J_NVLS_INT(int64_t, MP4J_MIN, "min", "s64", "l")
+MP4J_NVLS_INT(int64_t, MP4J_BAND, "and", "b64", "l")
+MP4J_NVLS_INT(int64_t, MP4J_BOR, "or", "b64", "l")
+MP4J_NVLS_INT(int64_t, MP4J_BXOR, "xor", "b64", "l")
+#undef MP4J_NVLS_INT
+
+__device__ __forceinline__ void multimem_st(void* mc, const Vec16& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc), "r"(v.x), "r"(v.y),
+               "r"(v.z), "r"(v.w)
+               : "memory");
+}
+
+inline bool nvls_supported(int dtype, int op) {
+  if (op == MP4J_COPY) return true;  // multimem.st broadcast
+  switch (dtype) {
+    case MP4J_F32: case MP4J_F64: return op == MP4J_SUM;
+    case MP4J_I32: case MP4J_I64:
+      return op == MP4J_SUM || op == MP4J_MAX || op == MP4J_MIN || op == MP4J_BAND || op == MP4J_BOR ||
+             op == MP4J_BXOR;
+  }
+  return false;
+}
+
+}  // namespace mp4j

@@ -1,4 +1,56 @@
-/* GPU half of the C ABI (filled in by csrc/gpu). Included from mp4j.h inside extern "C". */
+/* GPU half of the C ABI. Included from mp4j.h inside extern "C".
+ *
+ * A mp4j_gpu is the GPU data plane of one communicator: symmetric heap mapped on every peer,
+ * signal pads, staging windows and the sm_100a collective kernels. `arrs` arguments are arrays of
+ * element-0 device pointers, one per LOCAL rank: 1 entry for a real communicator, `world` entries
+ * for an emulated plane (all ranks on one GPU, used by single-GPU tests). `stream` is a
+ * cudaStream_t passed as void* (NULL = default stream). All collectives are in place and
+ * asynchronous with respect to the host.
+ */
 #ifndef MP4J_GPU_H_
 #define MP4J_GPU_H_
-#endif
+
+typedef struct mp4j_gpu mp4j_gpu;
+
+/* Collective over the communicator: every rank calls it with its own device. 0 sizes = defaults /
+ * environment (MP4J_HEAP_BYTES, MP4J_STAGING_BYTES, ...). The plane is owned by the communicator. */
+int mp4j_gpu_init(mp4j_comm* c, int device, size_t heap_bytes, size_t staging_bytes, mp4j_gpu** out);
+/* Single-process plane with `world` emulated ranks on `device`. Free with mp4j_gpu_destroy. */
+int mp4j_gpu_emu_create(int world, int device, size_t heap_bytes, size_t staging_bytes, mp4j_gpu** out);
+void mp4j_gpu_destroy(mp4j_gpu* g);
+int mp4j_gpu_world(mp4j_gpu* g);
+int mp4j_gpu_rank(mp4j_gpu* g);
+int mp4j_gpu_has_multicast(mp4j_gpu* g);
+/* Human-readable description (mode, sizes, notes) and the last collective's record. */
+int mp4j_gpu_describe(mp4j_gpu* g, char* buf, size_t n);
+int mp4j_gpu_last(mp4j_gpu* g, char* buf, size_t n);
+/* Symmetric allocation: the same offset is valid on every rank (collective, deterministic). */
+int mp4j_gpu_alloc(mp4j_gpu* g, size_t bytes, size_t* off);
+int mp4j_gpu_free(mp4j_gpu* g, size_t off);
+void* mp4j_gpu_ptr(mp4j_gpu* g, int rank, size_t off);
+/* Throws away nothing: returns MP4J_ERR if a kernel reported a peer-wait timeout. */
+int mp4j_gpu_check(mp4j_gpu* g);
+
+int mp4j_gpu_allreduce(mp4j_gpu* g, void* const* arrs, int dtype, int op, int64_t from, int64_t to, int algo,
+                       void* stream);                                                   /* PCS:1733 */
+int mp4j_gpu_reduce_scatter(mp4j_gpu* g, void* const* arrs, int dtype, int op, int64_t from,
+                            const int64_t* counts, int algo, void* stream);              /* PCS:1174 */
+int mp4j_gpu_allgather(mp4j_gpu* g, void* const* arrs, int dtype, const int64_t* froms, const int64_t* tos,
+                       int algo, void* stream);                                          /* PCS:620 */
+int mp4j_gpu_broadcast(mp4j_gpu* g, void* const* arrs, int dtype, int64_t from, int64_t to, int root, int algo,
+                       void* stream);                                                    /* PCS:750 */
+int mp4j_gpu_gather(mp4j_gpu* g, void* const* arrs, int dtype, const int64_t* froms, const int64_t* tos,
+                    int root, void* stream);                                             /* PCS:535 */
+int mp4j_gpu_scatter(mp4j_gpu* g, void* const* arrs, int dtype, const int64_t* froms, const int64_t* tos,
+                     int root, void* stream);                                            /* PCS:900 */
+int mp4j_gpu_reduce(mp4j_gpu* g, void* const* arrs, int dtype, int op, int64_t from, int64_t to, int root,
+                    int algo, void* stream);                                             /* PCS:1390 */
+/* ThreadCommSlave.allreduceArray on device buffers (TCS:1915): bufs[local_rank * T + t].
+ * fanout = 1 writes the result to all T buffers, 0 only to thread `dst`; local_only = 1 skips the
+ * inter-GPU step (the thread-level reduce of TCS:259-303 alone). thread_algo: 0 register, 1
+ * cluster/DSMEM (intra-GPU only). */
+int mp4j_gpu_thread_allreduce(mp4j_gpu* g, void* const* bufs, int T, int dtype, int op, int64_t from,
+                              int64_t to, int fanout, int dst, int local_only, int thread_algo, int algo,
+                              void* stream);
+
+#endif /* MP4J_GPU_H_ */

@@ -1,0 +1,38 @@
+"""Real multi-process GPU path: one process per GPU, symmetric heap mapped across processes (VMM fd
+passing or CUDA IPC), signal pads over NVLink. Needs >= 2 GPUs; the single-GPU box skips it and
+relies on the emulated-rank tests for the kernels plus the CPU tests for the control plane."""
+import pytest
+import torch
+
+import workers_gpu
+from ytk_mp4j_b200.parallel.local_cluster import run_cluster
+
+pytestmark = pytest.mark.gpu
+
+
+def _ngpu():
+    return torch.cuda.device_count() if torch.cuda.is_available() else 0
+
+
+@pytest.mark.skipif(_ngpu() < 2, reason="needs >= 2 GPUs")
+@pytest.mark.parametrize("p", [2, 4, 8])
+def test_process_collectives_on_gpus(p):
+    if _ngpu() < p:
+        pytest.skip("needs %d GPUs" % p)
+    res, code, logs = run_cluster(p, workers_gpu.process_gpu, (), timeout=300)
+    assert code == 0 and all(r["ok"] for r in res), res
+
+
+@pytest.mark.skipif(_ngpu() < 2, reason="needs >= 2 GPUs")
+@pytest.mark.parametrize("p,T", [(2, 4), (4, 2)])
+def test_thread_allreduce_on_gpus(p, T):
+    if _ngpu() < p:
+        pytest.skip("needs %d GPUs" % p)
+    res, code, logs = run_cluster(p, workers_gpu.thread_gpu, (), threads=T, timeout=300)
+    assert code == 0 and all(all(x) for x in res)
+
+
+def test_single_process_comm_on_gpu():
+    # p = 1: every collective short-circuits, thread collectives still run the intra-GPU kernel
+    res, code, logs = run_cluster(1, workers_gpu.thread_gpu, (), threads=4, timeout=300)
+    assert code == 0 and all(all(x) for x in res)

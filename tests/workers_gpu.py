@@ -1,0 +1,91 @@
+"""GPU worker bodies for tests/test_gpu_multiproc.py (public API end to end on CUDA tensors)."""
+import torch
+
+from ytk_mp4j_b200 import CommUtils, Operands, Operators
+from ytk_mp4j_b200 import _native as N
+
+
+def process_gpu(comm):
+    p, r = comm.getSlaveNum(), comm.getRank()
+    torch.cuda.set_device(r % torch.cuda.device_count())
+    comm.init_gpu(device=r % torch.cuda.device_count(), heap_bytes=512 << 20, staging_bytes=32 << 20)
+    info = {"desc": comm.gpu.describe(), "ok": False}
+    fop, dop, iop = Operands.FLOAT_OPERAND(), Operands.DOUBLE_OPERAND(), Operands.INT_OPERAND()
+    for n in (5, 1000, 100003, (4 << 20) + 3):
+        for algo in (N.ALGO_AUTO, N.ALGO_ONESHOT, N.ALGO_TWOSHOT) + ((N.ALGO_NVLS,) if comm.gpu.has_multicast else ()):
+            x = torch.full((n,), float(r + 1), device="cuda")
+            comm.gpu.allreduce(x, fop, Operators.Float.SUM, 1, n, algo=algo)
+            torch.cuda.synchronize()
+            assert torch.all(x[1:] == p * (p + 1) / 2) and x[0] == r + 1, (n, algo, comm.gpu.last())
+    # zero-copy symmetric tensor
+    n = 1 << 20
+    x = comm.empty(n, dop)
+    x.fill_(r)
+    comm.allreduceArray(x, dop, Operators.Double.MAX, 0, n)
+    torch.cuda.synchronize()
+    assert torch.all(x == p - 1) and "staged=0" in comm.gpu.last()
+    # the other six collectives, reference value patterns
+    n = 100003
+    froms, tos = CommUtils.createProcessArrayFroms(n, p), CommUtils.createProcessArrayTos(n, p)
+    owner = torch.empty(n, dtype=torch.int32)
+    for q in range(p):
+        owner[froms[q]:tos[q]] = q
+    owner = owner.cuda()
+    root = p - 1
+    x = torch.full((n,), -1, dtype=torch.int32, device="cuda")
+    x[froms[r]:tos[r]] = r
+    comm.allgatherArray(x, iop, froms, tos)
+    assert torch.equal(x, owner)
+    x = torch.full((n,), -1, dtype=torch.int32, device="cuda")
+    x[froms[r]:tos[r]] = r
+    comm.gatherArray(x, iop, froms, tos, root)
+    if r == root:
+        assert torch.equal(x, owner)
+    x = owner.clone() if r == root else torch.full((n,), -1, dtype=torch.int32, device="cuda")
+    comm.scatterArray(x, iop, froms, tos, root)
+    assert torch.all(x[froms[r]:tos[r]] == r)
+    x = owner.clone()
+    comm.reduceScatterArray(x, iop, Operators.Int.SUM, 0, [t - f for f, t in zip(froms, tos)])
+    assert torch.all(x[froms[r]:tos[r]] == r * p)
+    x = torch.full((n,), 1 if r == root else -1, dtype=torch.int32, device="cuda")
+    comm.broadcastArray(x, iop, 0, n, root)
+    assert torch.all(x == 1)
+    x = torch.ones(n, dtype=torch.int32, device="cuda")
+    comm.reduceArray(x, iop, Operators.Int.SUM, 0, n, root)
+    if r == root:
+        assert torch.all(x == p)
+    x = torch.ones(7, dtype=torch.float32, device="cuda")
+    comm.allreduceArrayRpc(x, fop, Operators.Float.SUM)
+    assert torch.all(x == p)
+    torch.cuda.synchronize()
+    comm.gpu.check()
+    comm.barrier()
+    info["ok"] = True
+    return info
+
+
+def thread_gpu(comm, tid):
+    p, r, T = comm.getSlaveNum(), comm.getRank(), comm.getThreadNum()
+    dev = r % torch.cuda.device_count()
+    torch.cuda.set_device(dev)
+    if tid == 0:
+        comm.init_gpu(device=dev, heap_bytes=512 << 20, staging_bytes=32 << 20)
+    comm.threadBarrier()
+    fop = Operands.FLOAT_OPERAND()
+    for n in (1000, (2 << 20) + 4):
+        x = torch.full((n,), float(r * T + tid + 1), device="cuda")
+        torch.cuda.synchronize()
+        comm.allreduceArray(x, fop, Operators.Float.SUM, 0, n)
+        torch.cuda.synchronize()
+        total = p * T * (p * T + 1) / 2
+        assert torch.all(x == total), (n, x[:4])
+    # reduce to (root, rootThread) through the generic thread path on CUDA tensors
+    n = 4099
+    x = torch.ones(n, device="cuda")
+    torch.cuda.synchronize()
+    comm.reduceArray(x, fop, Operators.Float.SUM, 0, n, p - 1, T - 1)
+    torch.cuda.synchronize()
+    if r == p - 1 and tid == T - 1:
+        assert torch.all(x == p * T)
+    comm.barrier()
+    return True

@@ -1,0 +1,292 @@
+"""Python face of the GPU data plane (csrc/gpu, include/mp4j_gpu.h).
+
+GpuPlane  - attached to a ProcessCommSlave: one process per GPU, peers mapped over NVLink.
+EmuPlane  - `world` emulated ranks on ONE GPU (every collective is one cooperative launch whose
+            grid rows are the ranks): how the kernels' multi-rank logic is tested on a single GPU.
+Both only marshal pointers: all work happens in libmp4j.so. There is no eager/PyTorch fallback;
+a missing or failing native call raises Mp4jException.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+import torch
+
+from .. import _native as N
+from ..exception import Mp4jException, check
+
+_P = N._proto
+_P("mp4j_gpu_init", C.c_int, C.c_void_p, C.c_int, C.c_size_t, C.c_size_t, N.c_vpp)
+_P("mp4j_gpu_emu_create", C.c_int, C.c_int, C.c_int, C.c_size_t, C.c_size_t, N.c_vpp)
+_P("mp4j_gpu_destroy", None, C.c_void_p)
+_P("mp4j_gpu_world", C.c_int, C.c_void_p)
+_P("mp4j_gpu_rank", C.c_int, C.c_void_p)
+_P("mp4j_gpu_has_multicast", C.c_int, C.c_void_p)
+_P("mp4j_gpu_describe", C.c_int, C.c_void_p, C.c_char_p, C.c_size_t)
+_P("mp4j_gpu_last", C.c_int, C.c_void_p, C.c_char_p, C.c_size_t)
+_P("mp4j_gpu_alloc", C.c_int, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t))
+_P("mp4j_gpu_free", C.c_int, C.c_void_p, C.c_size_t)
+_P("mp4j_gpu_ptr", C.c_void_p, C.c_void_p, C.c_int, C.c_size_t)
+_P("mp4j_gpu_check", C.c_int, C.c_void_p)
+_P("mp4j_gpu_allreduce", C.c_int, C.c_void_p, N.c_vpp, C.c_int, C.c_int, C.c_int64, C.c_int64, C.c_int, C.c_void_p)
+_P("mp4j_gpu_reduce_scatter", C.c_int, C.c_void_p, N.c_vpp, C.c_int, C.c_int, C.c_int64, N.c_i64p, C.c_int,
+   C.c_void_p)
+_P("mp4j_gpu_allgather", C.c_int, C.c_void_p, N.c_vpp, C.c_int, N.c_i64p, N.c_i64p, C.c_int, C.c_void_p)
+_P("mp4j_gpu_broadcast", C.c_int, C.c_void_p, N.c_vpp, C.c_int, C.c_int64, C.c_int64, C.c_int, C.c_int, C.c_void_p)
+_P("mp4j_gpu_gather", C.c_int, C.c_void_p, N.c_vpp, C.c_int, N.c_i64p, N.c_i64p, C.c_int, C.c_void_p)
+_P("mp4j_gpu_scatter", C.c_int, C.c_void_p, N.c_vpp, C.c_int, N.c_i64p, N.c_i64p, C.c_int, C.c_void_p)
+_P("mp4j_gpu_reduce", C.c_int, C.c_void_p, N.c_vpp, C.c_int, C.c_int, C.c_int64, C.c_int64, C.c_int, C.c_int,
+   C.c_void_p)
+_P("mp4j_gpu_thread_allreduce", C.c_int, C.c_void_p, N.c_vpp, C.c_int, C.c_int, C.c_int, C.c_int64, C.c_int64,
+   C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p)
+
+TORCH_DTYPES = {
+    N.F64: torch.float64, N.F32: torch.float32, N.I64: torch.int64, N.I32: torch.int32,
+    N.I16: torch.int16, N.I8: torch.int8, N.BF16: torch.bfloat16, N.F16: torch.float16,
+}
+DTYPE_CODES = {v: k for k, v in TORCH_DTYPES.items()}
+_TYPESTR = {N.F64: "<f8", N.F32: "<f4", N.I64: "<i8", N.I32: "<i4", N.I16: "<i2", N.I8: "|i1", N.F16: "<f2"}
+_ES = {N.F64: 8, N.F32: 4, N.I64: 8, N.I32: 4, N.I16: 2, N.I8: 1, N.BF16: 2, N.F16: 2}
+
+THREAD_ALGO = {"register": 0, "cluster": 1}
+
+
+class _RawCuda:
+    """Minimal __cuda_array_interface__ carrier so torch can wrap symmetric-heap memory."""
+
+    def __init__(self, ptr, n, code, owner):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": _TYPESTR[code], "data": (ptr, False),
+                                         "version": 2, "strides": None}
+        self._owner = owner
+
+
+def _stream_ptr(stream=None):
+    s = stream if stream is not None else torch.cuda.current_stream()
+    return C.c_void_p(s.cuda_stream)
+
+
+def _ptr_array(tensors):
+    return (C.c_void_p * len(tensors))(*[C.c_void_p(t.data_ptr()) for t in tensors])
+
+
+def _code_of(t, operand=None):
+    code = DTYPE_CODES.get(t.dtype)
+    if code is None:
+        raise Mp4jException("unsupported tensor dtype %s" % t.dtype)
+    if operand is not None and operand.code != code:
+        raise Mp4jException("tensor dtype %s does not match operand %s" % (t.dtype, operand.name))
+    return code
+
+
+def _check_tensor(t):
+    if not t.is_cuda or t.dim() != 1 or not t.is_contiguous():
+        raise Mp4jException("GPU collectives need 1-D contiguous CUDA tensors")
+
+
+def _native_op(operator):
+    if operator is None:
+        return N.COPY
+    if not operator.is_native:
+        raise Mp4jException("custom Python operators run on the host path only; "
+                            "move the tensor to the CPU or use a predefined operator")
+    return operator.code
+
+
+class _PlaneBase:
+    """Shared marshalling; subclasses define self._g and how many local ranks an `arrs` list has."""
+
+    _g = None
+
+    def describe(self):
+        buf = C.create_string_buffer(1024)
+        check(N.lib.mp4j_gpu_describe(self._g, buf, 1024))
+        return buf.value.decode()
+
+    def last(self):
+        buf = C.create_string_buffer(512)
+        check(N.lib.mp4j_gpu_last(self._g, buf, 512))
+        return buf.value.decode()
+
+    @property
+    def world(self):
+        return N.lib.mp4j_gpu_world(self._g)
+
+    @property
+    def has_multicast(self):
+        return bool(N.lib.mp4j_gpu_has_multicast(self._g))
+
+    def check(self):
+        """Raises if a kernel hit the device-side peer-wait watchdog since the last call."""
+        check(N.lib.mp4j_gpu_check(self._g))
+
+    def _alloc_off(self, nbytes):
+        off = C.c_size_t()
+        check(N.lib.mp4j_gpu_alloc(self._g, nbytes, C.byref(off)))
+        return off.value
+
+    def _wrap(self, rank, off, n, code):
+        ptr = N.lib.mp4j_gpu_ptr(self._g, rank, off)
+        if code == N.BF16:
+            t = torch.as_tensor(_RawCuda(ptr, n, N.I16, self), device="cuda:%d" % self.device)
+            return t.view(torch.bfloat16)
+        return torch.as_tensor(_RawCuda(ptr, n, code, self), device="cuda:%d" % self.device)
+
+    # raw collectives on lists of tensors (one per local rank)
+    def _allreduce(self, ts, code, op, f, t, algo, stream):
+        check(N.lib.mp4j_gpu_allreduce(self._g, _ptr_array(ts), code, op, f, t, algo, _stream_ptr(stream)))
+
+    def _reduce_scatter(self, ts, code, op, f, counts, algo, stream):
+        check(N.lib.mp4j_gpu_reduce_scatter(self._g, _ptr_array(ts), code, op, f, N.i64_array(counts), algo,
+                                            _stream_ptr(stream)))
+
+    def _allgather(self, ts, code, froms, tos, algo, stream):
+        check(N.lib.mp4j_gpu_allgather(self._g, _ptr_array(ts), code, N.i64_array(froms), N.i64_array(tos), algo,
+                                       _stream_ptr(stream)))
+
+    def _broadcast(self, ts, code, f, t, root, algo, stream):
+        check(N.lib.mp4j_gpu_broadcast(self._g, _ptr_array(ts), code, f, t, root, algo, _stream_ptr(stream)))
+
+    def _gather(self, ts, code, froms, tos, root, stream):
+        check(N.lib.mp4j_gpu_gather(self._g, _ptr_array(ts), code, N.i64_array(froms), N.i64_array(tos), root,
+                                    _stream_ptr(stream)))
+
+    def _scatter(self, ts, code, froms, tos, root, stream):
+        check(N.lib.mp4j_gpu_scatter(self._g, _ptr_array(ts), code, N.i64_array(froms), N.i64_array(tos), root,
+                                     _stream_ptr(stream)))
+
+    def _reduce(self, ts, code, op, f, t, root, algo, stream):
+        check(N.lib.mp4j_gpu_reduce(self._g, _ptr_array(ts), code, op, f, t, root, algo, _stream_ptr(stream)))
+
+    def _thread_allreduce(self, ts, T, code, op, f, t, fanout, dst, local_only, thread_algo, algo, stream):
+        check(N.lib.mp4j_gpu_thread_allreduce(self._g, _ptr_array(ts), T, code, op, f, t, 1 if fanout else 0, dst,
+                                              1 if local_only else 0, thread_algo, algo, _stream_ptr(stream)))
+
+
+class GpuPlane(_PlaneBase):
+    """GPU data plane of a ProcessCommSlave (one process per GPU)."""
+
+    def __init__(self, comm, device=None, heap_bytes=None, staging_bytes=None):
+        if not torch.cuda.is_available():
+            raise Mp4jException("the GPU data plane needs a CUDA device")
+        if device is None:
+            device = int(os.environ.get("LOCAL_RANK", torch.cuda.current_device()))
+        self.device = int(device)
+        torch.cuda.set_device(self.device)
+        torch.cuda.init()
+        self._comm = comm
+        self._g = C.c_void_p()
+        check(N.lib.mp4j_gpu_init(comm._h, self.device, int(heap_bytes or 0), int(staging_bytes or 0),
+                                  C.byref(self._g)))
+        self.thread_algo = THREAD_ALGO[os.environ.get("MP4J_THREAD_ALGO", "register")]
+        comm.debug("gpu plane: " + self.describe(), onlyRank0=False)
+
+    def close(self):
+        self._g = None  # owned and destroyed by the native communicator
+
+    def empty(self, n, operand):
+        """n-element tensor inside the symmetric heap (collective: every rank must call it in the
+        same order). Collectives on it are zero-copy."""
+        off = self._alloc_off(int(n) * _ES[operand.code])
+        return self._wrap(N.lib.mp4j_gpu_rank(self._g), off, int(n), operand.code)
+
+    # --- ProcessCommSlave dispatch targets
+    def allreduce(self, t, operand, operator, f, to, algo=N.ALGO_AUTO, stream=None):
+        _check_tensor(t)
+        self._allreduce([t], _code_of(t, operand), _native_op(operator), f, to, algo, stream)
+
+    def reduce_scatter(self, t, operand, operator, f, counts, algo=N.ALGO_AUTO, stream=None):
+        _check_tensor(t)
+        self._reduce_scatter([t], _code_of(t, operand), _native_op(operator), f, counts, algo, stream)
+
+    def allgather(self, t, operand, froms, tos, algo=N.ALGO_AUTO, stream=None):
+        _check_tensor(t)
+        self._allgather([t], _code_of(t, operand), froms, tos, algo, stream)
+
+    def broadcast(self, t, operand, f, to, root, algo=N.ALGO_AUTO, stream=None):
+        _check_tensor(t)
+        self._broadcast([t], _code_of(t, operand), f, to, root, algo, stream)
+
+    def gather(self, t, operand, froms, tos, root, stream=None):
+        _check_tensor(t)
+        self._gather([t], _code_of(t, operand), froms, tos, root, stream)
+
+    def scatter(self, t, operand, froms, tos, root, stream=None):
+        _check_tensor(t)
+        self._scatter([t], _code_of(t, operand), froms, tos, root, stream)
+
+    def reduce(self, t, operand, operator, f, to, root, algo=N.ALGO_AUTO, stream=None):
+        _check_tensor(t)
+        self._reduce([t], _code_of(t, operand), _native_op(operator), f, to, root, algo, stream)
+
+    # --- ThreadCommSlave dispatch targets
+    def thread_allreduce(self, ts, operand, operator, f, to, algo=N.ALGO_AUTO, stream=None):
+        for t in ts:
+            _check_tensor(t)
+        local = self.world == 1
+        self._thread_allreduce(ts, len(ts), _code_of(ts[0], operand), _native_op(operator), f, to, True, 0, local,
+                               self.thread_algo if local else 0, algo, stream)
+
+    def thread_reduce(self, ts, operand, operator, f, to, dst, stream=None):
+        """Intra-process reduce of the T buffers into ts[dst] (thread path of DOP:441-457)."""
+        for t in ts:
+            _check_tensor(t)
+        self._thread_allreduce(ts, len(ts), _code_of(ts[0], operand), _native_op(operator), f, to, False, dst, True,
+                               0, N.ALGO_AUTO, stream)
+
+
+class EmuPlane(_PlaneBase):
+    """`world` emulated ranks on one GPU. Methods take one tensor per emulated rank."""
+
+    def __init__(self, world, device=0, heap_bytes=256 << 20, staging_bytes=32 << 20):
+        self.device = int(device)
+        torch.cuda.set_device(self.device)
+        torch.cuda.init()
+        self._g = C.c_void_p()
+        check(N.lib.mp4j_gpu_emu_create(int(world), self.device, int(heap_bytes), int(staging_bytes),
+                                        C.byref(self._g)))
+
+    def close(self):
+        if self._g:
+            torch.cuda.synchronize()
+            N.lib.mp4j_gpu_destroy(self._g)
+            self._g = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def empty(self, n, code):
+        """Symmetric allocation: returns one tensor per emulated rank, all at the same offset."""
+        off = self._alloc_off(int(n) * _ES[code])
+        return [self._wrap(r, off, int(n), code) for r in range(self.world)]
+
+    def allreduce(self, ts, op, f, t, algo=N.ALGO_AUTO, stream=None):
+        self._allreduce(ts, _code_of(ts[0]), op, f, t, algo, stream)
+
+    def reduce_scatter(self, ts, op, f, counts, algo=N.ALGO_AUTO, stream=None):
+        self._reduce_scatter(ts, _code_of(ts[0]), op, f, counts, algo, stream)
+
+    def allgather(self, ts, froms, tos, algo=N.ALGO_AUTO, stream=None):
+        self._allgather(ts, _code_of(ts[0]), froms, tos, algo, stream)
+
+    def broadcast(self, ts, f, t, root, algo=N.ALGO_AUTO, stream=None):
+        self._broadcast(ts, _code_of(ts[0]), f, t, root, algo, stream)
+
+    def gather(self, ts, froms, tos, root, stream=None):
+        self._gather(ts, _code_of(ts[0]), froms, tos, root, stream)
+
+    def scatter(self, ts, froms, tos, root, stream=None):
+        self._scatter(ts, _code_of(ts[0]), froms, tos, root, stream)
+
+    def reduce(self, ts, op, f, t, root, algo=N.ALGO_AUTO, stream=None):
+        self._reduce(ts, _code_of(ts[0]), op, f, t, root, algo, stream)
+
+    def thread_allreduce(self, ts_by_rank, op, f, t, fanout=True, dst=0, local_only=False, thread_algo=0,
+                         algo=N.ALGO_AUTO, stream=None):
+        """ts_by_rank: [rank][thread] tensors."""
+        T = len(ts_by_rank[0])
+        flat = [x for row in ts_by_rank for x in row]
+        self._thread_allreduce(flat, T, _code_of(flat[0]), op, f, t, fanout, dst, local_only, thread_algo, algo,
+                               stream)
