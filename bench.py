@@ -44,11 +44,11 @@ def reference_arm():
 class ClockSampler(threading.Thread):
     """Samples SM clock + throttle reasons of one GPU while the timed region runs."""
 
-    def __init__(self, index, period=0.05):
+    def __init__(self, index, period=0.004):
         super().__init__(daemon=True)
         self.index, self.period = index, period
         self.samples, self.reasons, self.max_mhz = [], set(), None
-        self._stop = threading.Event()
+        self._halt = threading.Event()
         self._nvml = None
         try:
             import pynvml
@@ -71,7 +71,7 @@ class ClockSampler(threading.Thread):
             getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
             getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4): "sw_power_cap",
         }
-        while not self._stop.is_set():
+        while not self._halt.is_set():
             try:
                 self.samples.append(nv.nvmlDeviceGetClockInfo(self._h, nv.NVML_CLOCK_SM))
                 try:
@@ -83,10 +83,10 @@ class ClockSampler(threading.Thread):
                         self.reasons.add(name)
             except Exception:
                 pass
-            self._stop.wait(self.period)
+            self._halt.wait(self.period)
 
     def finish(self):
-        self._stop.set()
+        self._halt.set()
         self.join(timeout=2)
         return {"sm_mhz": statistics.median(self.samples) if self.samples else None,
                 "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
@@ -187,10 +187,13 @@ def main():
             comm.setThreadId(t)
             torch.cuda.set_device(local_rank)
             for it in range(Ke + 1):
-                comm.barrier()
                 if t == 0:
+                    # thread 0 reaches the barrier last (it ends every step with a full device
+                    # sync while the others wait here), so the GPU is idle at this timestamp and
+                    # nobody has started the next step's copies yet
                     torch.cuda.synchronize()
                     e2e_times.append(time.perf_counter())
+                comm.barrier()
                 bufs[t].copy_(host_in[t], non_blocking=True)          # H2D of this step's input
                 torch.cuda.current_stream().synchronize()
                 comm.allreduceArray(bufs[t], fop, SUM, 0, n)           # public API
