@@ -67,7 +67,7 @@ void GpuPlane::finish_init(GpuOptions opt) {
   const int tgrid = std::min(kMaxBlocks, sms_ * thread_max_blocks_per_sm());
   opt_.thread_slot_bytes = align_up(opt_.thread_slot_bytes, 16 * 8 * 8);
   thread_off_ = align_up(off, 4096);
-  thread_bytes_ = (size_t)tgrid * opt_.thread_slot_bytes;
+  thread_bytes_ = (size_t)std::max(tgrid, sms_ * thread_ws_slots()) * opt_.thread_slot_bytes;
   off = thread_off_ + thread_bytes_;
   staging_off_ = align_up(off, 4096);
   opt_.staging_bytes = align_up(opt_.staging_bytes, 4096);
@@ -407,6 +407,9 @@ void GpuPlane::thread_allreduce(void* const* bufs, int T, int dtype, int op, int
   if (p == 1) {
     // intra-GPU only; in emulation each emulated rank reduces its own T buffers
     const bool cluster = vec && (algo & 0xff) == 1 && thread_cluster_supported(dtype, op, T, 1);
+    bool fast = vec && (algo & 0xff) == 0 && (nbytes % 32) == 0 && thread_local_fast_supported(dtype, op, T);
+    for (int i = 0; fast && i < L * T; ++i)
+      if ((((uintptr_t)bufs[i] + (size_t)from * es) & 31) != 0) fast = false;
     for (int i = 0; i < L; ++i) {
       a.tab = table();
       a.tab.world = 1;
@@ -416,14 +419,35 @@ void GpuPlane::thread_allreduce(void* const* bufs, int T, int dtype, int op, int
       long long cap = (long long)sms_ * thread_max_blocks_per_sm();
       if (opt_.max_blocks > 0) cap = std::min<long long>(cap, opt_.max_blocks);
       const int grid = (int)std::max<long long>(1, std::min<long long>(cap, (units + thread_threads() - 1) / thread_threads()));
-      last_ = CollStat{"thread_allreduce", cluster ? "cluster-dsmem" : "register", nbytes, grid, false};
-      launch_thread_allreduce(dtype, op, false, a, grid, (cluster ? 1 : 0) | vec_flag, s);
+      last_ = CollStat{"thread_allreduce", cluster ? "cluster-dsmem" : (fast ? "local-256bit" : "register"), nbytes,
+                       grid, false};
+      launch_thread_allreduce(dtype, op, false, a, grid, (cluster ? 1 : (fast ? 2 : 0)) | vec_flag, s);
     }
     return;
   }
   a.tab = table();
   for (int i = 0; i < L; ++i)
     for (int t = 0; t < T; ++t) a.bufs[i][t] = bufs[i * T + t];
+  // ---- preferred: warp-specialised kernel (HBM read / NVLink / HBM write overlap inside each SM)
+  bool ws = vec && (algo & 0xff) == 0 && (nbytes % 32) == 0 && thread_local_fast_supported(dtype, op, T);
+  for (int i = 0; ws && i < L * T; ++i)
+    if ((((uintptr_t)bufs[i] + (size_t)from * es) & 31) != 0) ws = false;
+  if (ws) {
+    const size_t wslot = opt_.thread_slot_bytes / 32 * 32;
+    a.slot_bytes = wslot;
+    a.stg_off = thread_off_;
+    long long wcap = sms_;
+    if (emulated()) wcap /= p;
+    wcap = std::min<long long>(wcap, (long long)(thread_bytes_ / (wslot * thread_ws_slots())));
+    wcap = std::min<long long>(wcap, thread_ws_max_blocks());
+    if (opt_.max_blocks > 0) wcap = std::min<long long>(wcap, opt_.max_blocks);
+    const int wgrid = (int)std::max<long long>(1, std::min<long long>(wcap, (long long)((nbytes + wslot - 1) / wslot)));
+    const bool wnvls = has_multicast() && nvls_supported(dtype, op) &&
+                       (algo >> 16 == MP4J_ALGO_NVLS || (algo >> 16 == MP4J_ALGO_AUTO && nbytes >= opt_.nvls_min_bytes));
+    last_ = CollStat{"thread_allreduce", wnvls ? "fused-ws-nvls" : "fused-ws-p2p", nbytes, wgrid, false};
+    launch_thread_fused_ws(dtype, op, wnvls, a, wgrid, s);
+    return;
+  }
   const size_t slot = opt_.thread_slot_bytes / (16 * p) * (16 * p);
   a.slot_bytes = slot;
   a.stg_off = thread_off_;

@@ -18,5 +18,12 @@ void launch_thread_allreduce(int dtype, int op, bool nvls, const ThreadArgs& arg
 int thread_max_blocks_per_sm();
 int thread_threads();
 bool thread_cluster_supported(int dtype, int op, int T, int world);
+bool thread_local_fast_supported(int dtype, int op, int T);  // algo 2: static-T, 256-bit accesses
+
+// thread_fused_ws.cu: warp-specialised fused kernel (world > 1, 32-byte aligned, T in {2,4,8},
+// SUM/MAX/MIN on 4/8-byte types). One CTA per SM; needs grid * slots * slot_bytes of staging.
+void launch_thread_fused_ws(int dtype, int op, bool nvls, const ThreadArgs& args, int grid, cudaStream_t stream);
+int thread_ws_slots();
+int thread_ws_max_blocks();
 
 }  // namespace mp4j

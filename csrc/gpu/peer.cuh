@@ -18,7 +18,13 @@ constexpr int kMaxRanks = MP4J_MAX_RANKS;
 constexpr int kMaxBlocks = 1024;                      // flag rows per signal pad
 constexpr size_t kSigFlagsBytes = kMaxBlocks * kMaxRanks * sizeof(uint32_t);
 constexpr size_t kSigEpochOff = kSigFlagsBytes;       // per-block epoch counters (local use only)
-constexpr size_t kSigPadBytes = 64 * 1024;            // flags (32 KiB) + epochs (4 KiB) + spare
+// warp-specialised fused thread kernel: its own chunk counters and two flag arrays (phase A done,
+// phase B done), rows = blocks (<= kWsMaxBlocks), columns = source rank
+constexpr int kWsMaxBlocks = 512;
+constexpr size_t kSigWsEpochOff = kSigEpochOff + 4096;
+constexpr size_t kSigWsFaOff = kSigWsEpochOff + 4096;
+constexpr size_t kSigWsFbOff = kSigWsFaOff + kWsMaxBlocks * kMaxRanks * sizeof(uint32_t);
+constexpr size_t kSigPadBytes = 128 * 1024;           // everything above, zero-initialised once
 
 struct PeerTable {
   int world;
@@ -113,6 +119,39 @@ __device__ __forceinline__ Vec16 ld_coherent(const void* p) {
 __device__ __forceinline__ void st_stream(void* p, const Vec16& v) {
   asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y),
                "r"(v.z), "r"(v.w)
+               : "memory");
+}
+
+// ---- 32-byte vector moves: LDG.E.256 / STG.E.256 are new on sm_100 (PTX .v8.b32, needs an L2
+// eviction-priority qualifier); they are what lifts a many-stream reduce to the copy roofline.
+struct __align__(32) Vec32 {
+  Vec16 lo, hi;
+};
+__device__ __forceinline__ Vec32 ld_stream32(const void* p) {  // read-once input
+  Vec32 v;
+  asm volatile("ld.global.nc.L1::no_allocate.L2::evict_first.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(v.lo.x), "=r"(v.lo.y), "=r"(v.lo.z), "=r"(v.lo.w), "=r"(v.hi.x), "=r"(v.hi.y), "=r"(v.hi.z),
+                 "=r"(v.hi.w)
+               : "l"(p));
+  return v;
+}
+__device__ __forceinline__ Vec32 ld_coherent32(const void* p) {  // data produced during this kernel
+  Vec32 v;
+  asm volatile("ld.global.relaxed.sys.L2::evict_first.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(v.lo.x), "=r"(v.lo.y), "=r"(v.lo.z), "=r"(v.lo.w), "=r"(v.hi.x), "=r"(v.hi.y), "=r"(v.hi.z),
+                 "=r"(v.hi.w)
+               : "l"(p)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_stream32(void* p, const Vec32& v) {  // write-once output
+  asm volatile("st.global.L1::no_allocate.L2::evict_first.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p),
+               "r"(v.lo.x), "r"(v.lo.y), "r"(v.lo.z), "r"(v.lo.w), "r"(v.hi.x), "r"(v.hi.y), "r"(v.hi.z), "r"(v.hi.w)
+               : "memory");
+}
+__device__ __forceinline__ void st_keep32(void* p, const Vec32& v) {  // staging: will be re-read from L2
+  asm volatile("st.global.L2::evict_last.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "r"(v.lo.x),
+               "r"(v.lo.y), "r"(v.lo.z), "r"(v.lo.w), "r"(v.hi.x), "r"(v.hi.y), "r"(v.hi.z), "r"(v.hi.w)
                : "memory");
 }
 

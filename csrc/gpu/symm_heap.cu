@@ -139,13 +139,15 @@ void send_fds(int sock, int src_rank, const std::vector<int>& fds) {
   msghdr msg{};
   msg.msg_iov = &iov;
   msg.msg_iovlen = 1;
-  msg.msg_control = ctrl;
-  msg.msg_controllen = CMSG_SPACE(sizeof(int) * fds.size());
-  cmsghdr* c = CMSG_FIRSTHDR(&msg);
-  c->cmsg_level = SOL_SOCKET;
-  c->cmsg_type = SCM_RIGHTS;
-  c->cmsg_len = CMSG_LEN(sizeof(int) * fds.size());
-  memcpy(CMSG_DATA(c), fds.data(), sizeof(int) * fds.size());
+  if (!fds.empty()) {  // a rank with nothing to share still announces itself (header only)
+    msg.msg_control = ctrl;
+    msg.msg_controllen = CMSG_SPACE(sizeof(int) * fds.size());
+    cmsghdr* c = CMSG_FIRSTHDR(&msg);
+    c->cmsg_level = SOL_SOCKET;
+    c->cmsg_type = SCM_RIGHTS;
+    c->cmsg_len = CMSG_LEN(sizeof(int) * fds.size());
+    memcpy(CMSG_DATA(c), fds.data(), sizeof(int) * fds.size());
+  }
   if (::sendmsg(sock, &msg, 0) < 0) throw Error(std::string("sendmsg(SCM_RIGHTS): ") + strerror(errno));
 }
 void recv_fds(int sock, int* src_rank, std::vector<int>* fds) {
@@ -161,6 +163,7 @@ void recv_fds(int sock, int* src_rank, std::vector<int>* fds) {
   if (k != (ssize_t)sizeof(hdr)) throw Error("recvmsg(SCM_RIGHTS) failed");
   *src_rank = hdr[0];
   fds->assign(hdr[1], -1);
+  if (hdr[1] == 0) return;
   cmsghdr* c = CMSG_FIRSTHDR(&msg);
   if (!c || c->cmsg_type != SCM_RIGHTS) throw Error("no fds in control message");
   memcpy(fds->data(), CMSG_DATA(c), sizeof(int) * hdr[1]);

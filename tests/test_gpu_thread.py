@@ -114,3 +114,39 @@ def test_thread_cluster_dsmem_variant(planes, T, n):
         want = want + x
     for t in range(T):
         assert torch.equal(dev[0][t].cpu(), want), t
+
+
+@pytest.mark.parametrize("thread_algo,name", [(0, "local-256bit"), (3, "register")])
+def test_thread_local_variants_agree(planes, thread_algo, name):
+    plane = planes(1)
+    T, n = 8, 1 << 20
+    g = torch.Generator().manual_seed(5)
+    host = [[torch.randn(n, generator=g, dtype=torch.float32) for _ in range(T)]]
+    dev = [[h.cuda() for h in host[0]]]
+    plane.thread_allreduce(dev, N.SUM, 0, n, thread_algo=thread_algo)
+    torch.cuda.synchronize()
+    assert name in plane.last()
+    want = expected(host)
+    for t in range(T):
+        assert torch.equal(dev[0][t].cpu(), want)
+
+
+@pytest.mark.parametrize("world,T", [(2, 8), (4, 4), (8, 2)])
+@pytest.mark.parametrize("thread_algo,name", [(0, "fused-ws"), (3, "fused-p2p")])
+def test_thread_fused_variants_agree(planes, world, T, thread_algo, name):
+    """Warp-specialised kernel vs chunk-synchronous fallback: identical bits, several chunks per block."""
+    plane = planes(world)
+    n = (6 << 20) + 64  # > grid * slot so blocks iterate and recycle their slot ring
+    g = torch.Generator().manual_seed(world * 7 + T)
+    host = [[torch.randn(n, generator=g, dtype=torch.float32) for _ in range(T)] for _ in range(world)]
+    dev = [[h.cuda() for h in row] for row in host]
+    for rep in range(2):  # second call exercises the persistent chunk counters
+        plane.thread_allreduce(dev, N.SUM, 0, n, thread_algo=thread_algo)
+        torch.cuda.synchronize()
+        plane.check()
+        assert name in plane.last(), plane.last()
+        want = expected(host)
+        for r in range(world):
+            for t in range(T):
+                assert torch.equal(dev[r][t].cpu(), want), (rep, r, t)
+        host = [[want.clone() for _ in range(T)] for _ in range(world)]

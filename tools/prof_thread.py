@@ -15,7 +15,7 @@ from ytk_mp4j_b200 import _native as N  # noqa: E402
 from ytk_mp4j_b200.parallel.gpu_plane import EmuPlane, THREAD_ALGO  # noqa: E402
 
 ap = argparse.ArgumentParser()
-ap.add_argument("--algo", default="register")
+ap.add_argument("--algo", default="auto")
 ap.add_argument("--world", type=int, default=1)
 ap.add_argument("--T", type=int, default=8)
 ap.add_argument("--elems", type=int, default=64 << 20)

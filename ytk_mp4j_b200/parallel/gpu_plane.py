@@ -48,7 +48,8 @@ DTYPE_CODES = {v: k for k, v in TORCH_DTYPES.items()}
 _TYPESTR = {N.F64: "<f8", N.F32: "<f4", N.I64: "<i8", N.I32: "<i4", N.I16: "<i2", N.I8: "|i1", N.F16: "<f2"}
 _ES = {N.F64: 8, N.F32: 4, N.I64: 8, N.I32: 4, N.I16: 2, N.I8: 1, N.BF16: 2, N.F16: 2}
 
-THREAD_ALGO = {"register": 0, "cluster": 1}
+# intra-GPU thread-reduce variants: auto = 256-bit static-T fast path when eligible, else register
+THREAD_ALGO = {"auto": 0, "cluster": 1, "register": 3}
 
 
 class _RawCuda:
@@ -177,7 +178,7 @@ class GpuPlane(_PlaneBase):
         self._g = C.c_void_p()
         check(N.lib.mp4j_gpu_init(comm._h, self.device, int(heap_bytes or 0), int(staging_bytes or 0),
                                   C.byref(self._g)))
-        self.thread_algo = THREAD_ALGO[os.environ.get("MP4J_THREAD_ALGO", "register")]
+        self.thread_algo = THREAD_ALGO[os.environ.get("MP4J_THREAD_ALGO", "auto")]
         comm.debug("gpu plane: " + self.describe(), onlyRank0=False)
 
     def close(self):
