@@ -67,7 +67,7 @@ __device__ __forceinline__ void st_elementwise(void* p, const Vec16& v) {
   for (int i = 0; i < (int)(16 / sizeof(T)); ++i) ((T*)p)[i] = u.e[i];
 }
 
-template <typename T, int OP, bool NVLS>
+template <typename T, int OP, bool NVLS, int W>
 __global__ void __launch_bounds__(kThreads) grs_kernel(const __grid_constant__ GrsArgs a) {
   const PeerTable& tab = a.tab;
   const int rank = my_rank(tab);
@@ -120,21 +120,90 @@ __global__ void __launch_bounds__(kThreads) grs_kernel(const __grid_constant__ G
   const unsigned smask = it.src_mask & full, dmask = it.dst_mask & full;
   const bool multi_src = (smask & (smask - 1)) != 0;
 
-  // ---- vector body
-  for (long long v = gtid; v < nvec; v += gstride) {
-    Vec16 acc;
-    bool done = false;
-    if constexpr (NVLS) {
-      if (multi_src && smask == full) {
-        acc = Nvls<T, OP>::ld_reduce(tab.mc_heap + src_b0 + v * 16);
-        done = true;
+  // ---- vector body. An NVLink round trip costs ~2-3 us and the asm-volatile accessors are never
+  // reordered by the compiler, so memory-level parallelism is explicit: every thread keeps ~8
+  // independent 16-byte requests in flight (kU vectors x sources). W > 0 is the compile-time world
+  // size that lets the (vector, source) tile live in registers; W == 0 is the generic fallback.
+  const bool single_src = smask != 0 && !multi_src;
+  const int src0 = single_src ? (__ffs(smask) - 1) : 0;
+  if (NVLS || single_src || (W > 0 && smask == full)) {
+    constexpr int kU = (NVLS || W == 0) ? 8 : (W >= 8 ? 1 : 8 / W);
+    constexpr int kW = W > 0 ? W : 1;
+    for (long long v0 = gtid; v0 < nvec; v0 += gstride * 8) {
+#pragma unroll
+      for (int b = 0; b < 8 / kU; ++b) {
+        const long long vb = v0 + (long long)b * kU * gstride;
+        Vec16 acc[kU];
+        if (single_src) {
+#pragma unroll
+          for (int j = 0; j < kU; ++j) {
+            const long long v = vb + j * gstride;
+            if (v < nvec) acc[j] = ld_coherent(tab.heap[src0] + src_b0 + v * 16);
+          }
+        } else if constexpr (NVLS) {
+#pragma unroll
+          for (int j = 0; j < kU; ++j) {
+            const long long v = vb + j * gstride;
+            if (v < nvec) acc[j] = Nvls<T, OP>::ld_reduce(tab.mc_heap + src_b0 + v * 16);
+          }
+        } else {
+          Vec16 x[kU][kW];
+#pragma unroll
+          for (int j = 0; j < kU; ++j) {
+            const long long v = vb + j * gstride;
+#pragma unroll
+            for (int q = 0; q < kW; ++q)
+              if (v < nvec) x[j][q] = ld_coherent(tab.heap[q] + src_b0 + v * 16);
+          }
+#pragma unroll
+          for (int j = 0; j < kU; ++j) {
+            acc[j] = x[j][0];
+#pragma unroll
+            for (int q = 1; q < kW; ++q) acc[j] = vreduce<T, OP>(acc[j], x[j][q]);  // ascending rank order
+          }
+        }
+        bool stored = false;
+        if constexpr (NVLS) {
+          if (dmask == full) {
+#pragma unroll
+            for (int j = 0; j < kU; ++j) {
+              const long long v = vb + j * gstride;
+              if (v < nvec) multimem_st(tab.mc_heap + dst_b0 + v * 16, acc[j]);
+            }
+            stored = true;
+          }
+        }
+        if (!stored) {
+          for (int q = 0; q < world; ++q) {
+            if (!((dmask >> q) & 1u)) continue;
+#pragma unroll
+            for (int j = 0; j < kU; ++j) {
+              const long long v = vb + j * gstride;
+              if (v < nvec) st_stream(tab.heap[q] + dst_b0 + v * 16, acc[j]);
+            }
+          }
+        }
+        if (it.dst_local != nullptr) {
+#pragma unroll
+          for (int j = 0; j < kU; ++j) {
+            const long long v = vb + j * gstride;
+            if (v < nvec) {
+              char* p = (char*)it.dst_local + (unsigned long long)(it.lo + head) * ES + v * 16;
+              if (a.vec_ok) st_stream(p, acc[j]);
+              else st_elementwise<T>(p, acc[j]);
+            }
+          }
+        }
       }
     }
-    if (!done) {
+  } else {
+    // generic: any source mask, runtime world, one vector at a time
+    for (long long v = gtid; v < nvec; v += gstride) {
       Vec16 x[kMaxRanks];
 #pragma unroll
       for (int q = 0; q < kMaxRanks; ++q)
         if (q < world && ((smask >> q) & 1u)) x[q] = ld_coherent(tab.heap[q] + src_b0 + v * 16);
+      Vec16 acc;
       bool first = true;
 #pragma unroll
       for (int q = 0; q < kMaxRanks; ++q) {
@@ -143,23 +212,14 @@ __global__ void __launch_bounds__(kThreads) grs_kernel(const __grid_constant__ G
           first = false;
         }
       }
-    }
-    bool stored = false;
-    if constexpr (NVLS) {
-      if (dmask == full) {
-        multimem_st(tab.mc_heap + dst_b0 + v * 16, acc);
-        stored = true;
-      }
-    }
-    if (!stored) {
 #pragma unroll
       for (int q = 0; q < kMaxRanks; ++q)
         if (q < world && ((dmask >> q) & 1u)) st_stream(tab.heap[q] + dst_b0 + v * 16, acc);
-    }
-    if (it.dst_local != nullptr) {
-      char* p = (char*)it.dst_local + (unsigned long long)(it.lo + head) * ES + v * 16;
-      if (a.vec_ok) st_stream(p, acc);
-      else st_elementwise<T>(p, acc);
+      if (it.dst_local != nullptr) {
+        char* p = (char*)it.dst_local + (unsigned long long)(it.lo + head) * ES + v * 16;
+        if (a.vec_ok) st_stream(p, acc);
+        else st_elementwise<T>(p, acc);
+      }
     }
   }
 
@@ -186,9 +246,9 @@ __global__ void __launch_bounds__(kThreads) grs_kernel(const __grid_constant__ G
   ep.store();
 }
 
-template <typename T, int OP, bool NVLS>
+template <typename T, int OP, bool NVLS, int W = 0>
 void launch_one(const GrsArgs& args, int grid, cudaStream_t stream) {
-  auto kfn = grs_kernel<T, OP, NVLS>;
+  auto kfn = grs_kernel<T, OP, NVLS, W>;
   if (args.tab.emulate) {
     void* params[] = {(void*)&args};
     MP4J_CUDA(cudaLaunchCooperativeKernel((const void*)kfn, dim3(grid, args.tab.world), dim3(kThreads), params, 0,
@@ -203,6 +263,14 @@ template <typename T, int OP>
 void launch_nvls_or_not(const GrsArgs& args, bool nvls, int grid, cudaStream_t stream) {
   if constexpr (Nvls<T, OP>::supported || OP == MP4J_COPY) {
     if (nvls) return launch_one<T, OP, true>(args, grid, stream);
+  }
+  // compile-time world size for the operators and types that carry the bulk of the traffic
+  if constexpr (sizeof(T) >= 4 && (OP == MP4J_SUM || OP == MP4J_MAX || OP == MP4J_MIN)) {
+    switch (args.tab.world) {
+      case 2: return launch_one<T, OP, false, 2>(args, grid, stream);
+      case 4: return launch_one<T, OP, false, 4>(args, grid, stream);
+      case 8: return launch_one<T, OP, false, 8>(args, grid, stream);
+    }
   }
   launch_one<T, OP, false>(args, grid, stream);
 }
@@ -237,7 +305,7 @@ int grs_max_blocks_per_sm() {
   static int cached = -1;
   if (cached < 0) {
     int nb = 0;
-    MP4J_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, grs_kernel<float, MP4J_SUM, false>, kThreads, 0));
+    MP4J_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, grs_kernel<float, MP4J_SUM, false, 0>, kThreads, 0));
     cached = std::max(nb, 1);
   }
   return cached;

@@ -26,6 +26,7 @@ void GpuOptions::load_env() {
   oneshot_max_bytes = env_size("MP4J_ONE_SHOT_MAX_BYTES", oneshot_max_bytes);
   nvls_min_bytes = env_size("MP4J_NVLS_MIN_BYTES", nvls_min_bytes);
   max_blocks = (int)env_size("MP4J_MAX_BLOCKS", (size_t)max_blocks);
+  nvls_min_world = (int)env_size("MP4J_NVLS_MIN_WORLD", (size_t)nvls_min_world);
   if (getenv("MP4J_NVLS")) want_multicast = atoi(getenv("MP4J_NVLS")) != 0;
   if (getenv("MP4J_GPU_TIMEOUT_S")) timeout_s = atof(getenv("MP4J_GPU_TIMEOUT_S"));
 }
@@ -185,7 +186,7 @@ void GpuPlane::run_grs(const char* name, void* const* arrs, int dtype, int op, c
   a.exit_barrier = 1;
   a.vec_ok = 1;
   const bool nvls_ok = has_multicast() && nvls_supported(dtype, op) &&
-                       (algo == MP4J_ALGO_NVLS || (algo == MP4J_ALGO_AUTO && span_bytes >= opt_.nvls_min_bytes));
+                       (algo == MP4J_ALGO_NVLS || (algo == MP4J_ALGO_AUTO && nvls_auto(span_bytes)));
   last_.name = name;
   last_.bytes = span_bytes;
 
@@ -443,7 +444,7 @@ void GpuPlane::thread_allreduce(void* const* bufs, int T, int dtype, int op, int
     if (opt_.max_blocks > 0) wcap = std::min<long long>(wcap, opt_.max_blocks);
     const int wgrid = (int)std::max<long long>(1, std::min<long long>(wcap, (long long)((nbytes + wslot - 1) / wslot)));
     const bool wnvls = has_multicast() && nvls_supported(dtype, op) &&
-                       (algo >> 16 == MP4J_ALGO_NVLS || (algo >> 16 == MP4J_ALGO_AUTO && nbytes >= opt_.nvls_min_bytes));
+                       (algo >> 16 == MP4J_ALGO_NVLS || (algo >> 16 == MP4J_ALGO_AUTO && nvls_auto(nbytes)));
     last_ = CollStat{"thread_allreduce", wnvls ? "fused-ws-nvls" : "fused-ws-p2p", nbytes, wgrid, false};
     launch_thread_fused_ws(dtype, op, wnvls, a, wgrid, s);
     return;
@@ -458,7 +459,7 @@ void GpuPlane::thread_allreduce(void* const* bufs, int T, int dtype, int op, int
   if (opt_.max_blocks > 0) cap = std::min<long long>(cap, opt_.max_blocks);
   const int grid = (int)std::max<long long>(1, std::min<long long>(cap, (long long)((nbytes + slot - 1) / slot)));
   const bool nvls = vec && has_multicast() && nvls_supported(dtype, op) &&
-                    (algo >> 16 == MP4J_ALGO_NVLS || (algo >> 16 == MP4J_ALGO_AUTO && nbytes >= opt_.nvls_min_bytes));
+                    (algo >> 16 == MP4J_ALGO_NVLS || (algo >> 16 == MP4J_ALGO_AUTO && nvls_auto(nbytes)));
   last_ = CollStat{"thread_allreduce", nvls ? "fused-nvls" : "fused-p2p", nbytes, grid, false};
   launch_thread_allreduce(dtype, op, nvls, a, grid, 0 | vec_flag, s);
 }

@@ -24,6 +24,7 @@ struct GpuOptions {
   size_t thread_slot_bytes = 128 << 10; // per-block slot of the fused thread kernel
   size_t oneshot_max_bytes = 256 << 10; // <= : one-shot allreduce (MP4J_ONE_SHOT_MAX_BYTES)
   size_t nvls_min_bytes = 512 << 10;    // >= : NVLS when available (MP4J_NVLS_MIN_BYTES)
+  int nvls_min_world = 2;               // AUTO uses NVLS only when world > this (MP4J_NVLS_MIN_WORLD)
   bool want_multicast = true;           // MP4J_NVLS=0 disables
   int max_blocks = 0;                   // 0 = occupancy-derived (MP4J_MAX_BLOCKS)
   double timeout_s = 60.0;              // device-side flag-wait watchdog (MP4J_GPU_TIMEOUT_S)
@@ -83,6 +84,9 @@ class GpuPlane {
   void run_grs(const char* name, void* const* arrs, int dtype, int op, const int64_t* lo, const int64_t* hi,
                const unsigned* src_mask, const unsigned* dst_mask, bool reduce_like, int algo, cudaStream_t s);
   int pick_grid(long long max_units, int max_blocks_per_sm) const;
+  // AUTO's NVLS rule, from measurement (profiles/): in-switch reduction only pays once it removes
+  // traffic, i.e. beyond 2 ranks, and for messages large enough to amortise the multicast path.
+  bool nvls_auto(size_t bytes) const { return world() > opt_.nvls_min_world && bytes >= opt_.nvls_min_bytes; }
   bool offsets_symmetric(void* const* arrs, size_t* off) const;
 
   SymmHeap heap_;

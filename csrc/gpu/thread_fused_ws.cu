@@ -96,23 +96,40 @@ __global__ void __launch_bounds__(kWsThreads, 1) thread_fused_ws_kernel(const __
       named_bar(2, kThreadsB);
       const unsigned long long so = ring_off + (unsigned long long)(k % kSlots) * a.slot_bytes;
       const int lo = (int)((long long)nv16 * rank / world), hi = (int)((long long)nv16 * (rank + 1) / world);
-      for (int v = lo + bt; v < hi; v += kThreadsB) {
-        const unsigned long long o = so + (unsigned long long)v * 16;
+      // An NVLink round trip is ~2-3 us: keep kBatch independent 16-byte requests in flight per
+      // thread (the asm volatile accessors are never reordered, so batching is explicit).
+      constexpr int kBatch = 8;
+      for (int v0 = lo + bt; v0 < hi; v0 += kThreadsB * kBatch) {
+        Vec16 acc[kBatch];
         if constexpr (NVLS) {
-          const Vec16 acc = Nvls<T, OP>::ld_reduce(tab.mc_heap + o);
-          multimem_st(tab.mc_heap + o, acc);
+#pragma unroll
+          for (int j = 0; j < kBatch; ++j) {
+            const int v = v0 + j * kThreadsB;
+            if (v < hi) acc[j] = Nvls<T, OP>::ld_reduce(tab.mc_heap + so + (unsigned long long)v * 16);
+          }
+#pragma unroll
+          for (int j = 0; j < kBatch; ++j) {
+            const int v = v0 + j * kThreadsB;
+            if (v < hi) multimem_st(tab.mc_heap + so + (unsigned long long)v * 16, acc[j]);
+          }
         } else {
-          Vec16 x[kMaxRanks];
+          for (int q = 0; q < world; ++q) {  // ascending rank order => identical bits on every rank
+            Vec16 x[kBatch];
 #pragma unroll
-          for (int q = 0; q < kMaxRanks; ++q)
-            if (q < world) x[q] = ld_coherent(tab.heap[q] + o);
-          Vec16 acc = x[0];
+            for (int j = 0; j < kBatch; ++j) {
+              const int v = v0 + j * kThreadsB;
+              if (v < hi) x[j] = ld_coherent(tab.heap[q] + so + (unsigned long long)v * 16);
+            }
 #pragma unroll
-          for (int q = 1; q < kMaxRanks; ++q)
-            if (q < world) acc = vec_reduce<T, OP>(acc, x[q]);
+            for (int j = 0; j < kBatch; ++j) acc[j] = (q == 0) ? x[j] : vec_reduce<T, OP>(acc[j], x[j]);
+          }
+          for (int q = 0; q < world; ++q) {
 #pragma unroll
-          for (int q = 0; q < kMaxRanks; ++q)
-            if (q < world) st_stream(tab.heap[q] + o, acc);
+            for (int j = 0; j < kBatch; ++j) {
+              const int v = v0 + j * kThreadsB;
+              if (v < hi) st_stream(tab.heap[q] + so + (unsigned long long)v * 16, acc[j]);
+            }
+          }
         }
       }
       named_bar(2, kThreadsB);
