@@ -33,7 +33,7 @@ struct ThreadArgs {
   int T;                        // thread buffers per rank
   int fanout;                   // 1: result to all T buffers; 0: only to bufs[dst_index]
   int dst_index;
-  int pad_;
+  int slots;                    // ring depth of the warp-specialised kernel
   long long from, to;           // element range
   unsigned long long stg_off;   // byte offset in every heap of the per-block staging slots
   unsigned long long slot_bytes;  // bytes per block slot (multiple of 16 * world)

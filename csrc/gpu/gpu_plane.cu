@@ -23,6 +23,7 @@ void GpuOptions::load_env() {
   heap_bytes = env_size("MP4J_HEAP_BYTES", heap_bytes);
   staging_bytes = env_size("MP4J_STAGING_BYTES", staging_bytes);
   thread_slot_bytes = env_size("MP4J_THREAD_SLOT_BYTES", thread_slot_bytes);
+  thread_slots = (int)env_size("MP4J_THREAD_SLOTS", (size_t)thread_slots);
   oneshot_max_bytes = env_size("MP4J_ONE_SHOT_MAX_BYTES", oneshot_max_bytes);
   nvls_min_bytes = env_size("MP4J_NVLS_MIN_BYTES", nvls_min_bytes);
   max_blocks = (int)env_size("MP4J_MAX_BLOCKS", (size_t)max_blocks);
@@ -68,7 +69,8 @@ void GpuPlane::finish_init(GpuOptions opt) {
   const int tgrid = std::min(kMaxBlocks, sms_ * thread_max_blocks_per_sm());
   opt_.thread_slot_bytes = align_up(opt_.thread_slot_bytes, 16 * 8 * 8);
   thread_off_ = align_up(off, 4096);
-  thread_bytes_ = (size_t)std::max(tgrid, sms_ * thread_ws_slots()) * opt_.thread_slot_bytes;
+  opt_.thread_slots = std::max(2, std::min(opt_.thread_slots, thread_ws_slots()));
+  thread_bytes_ = (size_t)std::max(tgrid, sms_ * opt_.thread_slots) * opt_.thread_slot_bytes;
   off = thread_off_ + thread_bytes_;
   staging_off_ = align_up(off, 4096);
   opt_.staging_bytes = align_up(opt_.staging_bytes, 4096);
@@ -436,10 +438,11 @@ void GpuPlane::thread_allreduce(void* const* bufs, int T, int dtype, int op, int
   if (ws) {
     const size_t wslot = opt_.thread_slot_bytes / 32 * 32;
     a.slot_bytes = wslot;
+    a.slots = opt_.thread_slots;
     a.stg_off = thread_off_;
     long long wcap = sms_;
     if (emulated()) wcap /= p;
-    wcap = std::min<long long>(wcap, (long long)(thread_bytes_ / (wslot * thread_ws_slots())));
+    wcap = std::min<long long>(wcap, (long long)(thread_bytes_ / (wslot * opt_.thread_slots)));
     wcap = std::min<long long>(wcap, thread_ws_max_blocks());
     if (opt_.max_blocks > 0) wcap = std::min<long long>(wcap, opt_.max_blocks);
     const int wgrid = (int)std::max<long long>(1, std::min<long long>(wcap, (long long)((nbytes + wslot - 1) / wslot)));

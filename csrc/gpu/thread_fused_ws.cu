@@ -27,7 +27,7 @@ namespace {
 constexpr int kWarpsA = 6, kWarpsB = 4, kWarpsC = 6;
 constexpr int kThreadsA = kWarpsA * 32, kThreadsB = kWarpsB * 32, kThreadsC = kWarpsC * 32;
 constexpr int kWsThreads = kThreadsA + kThreadsB + kThreadsC;  // 512
-constexpr int kSlots = 3;
+constexpr int kMaxSlots = 8;  // ring depth is a launch parameter (ThreadArgs::slots), 2..kMaxSlots
 
 __device__ __forceinline__ void named_bar(int id, int nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
@@ -48,6 +48,7 @@ __global__ void __launch_bounds__(kWsThreads, 1) thread_fused_ws_kernel(const __
   const long long mine = nchunks > (long long)blockIdx.x ? (nchunks - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
   uint32_t* ws_epoch = (uint32_t*)((char*)tab.sig[rank] + kSigWsEpochOff) + blockIdx.x;
   const uint32_t base = *(volatile uint32_t*)ws_epoch;
+  const int kSlots = a.slots;
   const unsigned long long ring_off = a.stg_off + (unsigned long long)blockIdx.x * kSlots * a.slot_bytes;
   if (threadIdx.x == 0) c_done = 0;
   __syncthreads();
@@ -210,7 +211,7 @@ void launch_ws_type(int op, const ThreadArgs& args, bool nvls, int grid, cudaStr
 
 }  // namespace
 
-int thread_ws_slots() { return kSlots; }
+int thread_ws_slots() { return kMaxSlots; }
 int thread_ws_max_blocks() { return kWsMaxBlocks; }
 
 void launch_thread_fused_ws(int dtype, int op, bool nvls, const ThreadArgs& args, int grid, cudaStream_t stream) {
