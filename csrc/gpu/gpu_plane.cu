@@ -28,6 +28,7 @@ void GpuOptions::load_env() {
   nvls_min_bytes = env_size("MP4J_NVLS_MIN_BYTES", nvls_min_bytes);
   max_blocks = (int)env_size("MP4J_MAX_BLOCKS", (size_t)max_blocks);
   nvls_min_world = (int)env_size("MP4J_NVLS_MIN_WORLD", (size_t)nvls_min_world);
+  poll_ns = (int)env_size("MP4J_POLL_NS", (size_t)poll_ns);
   if (getenv("MP4J_NVLS")) want_multicast = atoi(getenv("MP4J_NVLS")) != 0;
   if (getenv("MP4J_GPU_TIMEOUT_S")) timeout_s = atof(getenv("MP4J_GPU_TIMEOUT_S"));
 }
@@ -105,6 +106,7 @@ PeerTable GpuPlane::table() const {
   t.mc_heap = heap_.mc_base();
   t.err = err_dev_;
   t.timeout_ns = (unsigned long long)(opt_.timeout_s * 1e9);
+  t.poll_ns = opt_.poll_ns;
   return t;
 }
 

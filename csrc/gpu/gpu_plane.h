@@ -28,6 +28,7 @@ struct GpuOptions {
   int nvls_min_world = 2;               // AUTO uses NVLS only when world > this (MP4J_NVLS_MIN_WORLD)
   bool want_multicast = true;           // MP4J_NVLS=0 disables
   int max_blocks = 0;                   // 0 = occupancy-derived (MP4J_MAX_BLOCKS)
+  int poll_ns = 0;                      // sleep between device-side flag polls (MP4J_POLL_NS)
   double timeout_s = 60.0;              // device-side flag-wait watchdog (MP4J_GPU_TIMEOUT_S)
   void load_env();
 };

@@ -30,7 +30,7 @@ struct PeerTable {
   int world;
   int rank;                       // real mode; emulation derives the rank from blockIdx.y
   int emulate;                    // 1: all "ranks" live on this GPU, one grid row per rank
-  int pad_;
+  int poll_ns;                    // sleep between flag polls; 0 = tight spin (MP4J_POLL_NS)
   char* heap[kMaxRanks];          // every rank's symmetric heap as mapped HERE
   uint32_t* sig[kMaxRanks];       // every rank's signal pad as mapped HERE
   char* mc_heap;                  // multicast (NVLS) mapping of the heaps, or nullptr
@@ -57,11 +57,27 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
 
 // Waits until *flag reaches `want` (wrap-safe). Returns false on watchdog timeout, after raising
 // the host-visible error word: a dead peer must not hang every other rank's kernel.
+// Polling uses RELAXED loads with a short sleep and ONE acquire fence once the flag has arrived:
+// an acquire at system scope invalidates the SM's L1 (CCTL.IVALL) and drains the LSU, so spinning
+// on ld.acquire would tax the streaming warps that share the SM with the poller.
+__device__ __forceinline__ uint32_t ld_relaxed_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
 __device__ __forceinline__ bool wait_flag(const PeerTable& t, const uint32_t* flag, uint32_t want) {
-  if ((int32_t)(ld_acquire_sys(flag) - want) >= 0) return true;
+  if ((int32_t)(ld_relaxed_sys(flag) - want) >= 0) {
+    (void)ld_acquire_sys(flag);  // acquire once, on the already-arrived flag (cheaper than a full fence)
+    return true;
+  }
   unsigned long long t0 = globaltimer_ns();
   for (unsigned spins = 1;; ++spins) {
-    if ((int32_t)(ld_acquire_sys(flag) - want) >= 0) return true;
+    if (t.poll_ns > 0) __nanosleep((unsigned)t.poll_ns);
+    if ((int32_t)(ld_relaxed_sys(flag) - want) >= 0) {
+      (void)ld_acquire_sys(flag);  // acquire once, on the already-arrived flag (cheaper than a full fence)
+      return true;
+    }
     if ((spins & 1023u) == 0 && globaltimer_ns() - t0 > t.timeout_ns) {
       atomicExch((unsigned*)t.err, 1u);
       return false;
