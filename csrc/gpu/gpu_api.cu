@@ -161,4 +161,16 @@ int mp4j_gpu_thread_allreduce(mp4j_gpu* g, void* const* bufs, int T, int dtype, 
   MP4J_API_END
 }
 
+int mp4j_gpu_map_collective(mp4j_gpu* g, int mode, const int64_t* const* keys, const void* const* vals,
+                            const int64_t* n, int64_t max_n, int64_t out_cap, int dtype, int op, int partition,
+                            int64_t** out_keys, void** out_vals, uint64_t** info, void* stream) {
+  MP4J_API_BEGIN
+  const int L = g->g->emulated() ? g->g->world() : 1;
+  long long nn[MP4J_MAX_RANKS];
+  for (int i = 0; i < L; ++i) nn[i] = n[i];
+  g->g->map_collective(mode, (const long long* const*)keys, vals, nn, max_n, out_cap, dtype, op, partition,
+                       (long long**)out_keys, out_vals, (unsigned long long**)info, (cudaStream_t)stream);
+  MP4J_API_END
+}
+
 }  // extern "C"

@@ -84,6 +84,7 @@ void GpuPlane::finish_init(GpuOptions opt) {
 
 GpuPlane::~GpuPlane() {
   cudaDeviceSynchronize();
+  map_release();
   if (err_host_) cudaFreeHost(err_host_);
 }
 

@@ -76,6 +76,18 @@ class GpuPlane {
   // Raises if a kernel reported a peer-wait timeout since the last check.
   void check_error();
 
+  // ---- sparse (map container) collectives: allreduceMap / reduceScatterMap / allgatherMap on
+  // (int64 key, value) device arrays. One entry per LOCAL rank in every array argument.
+  // mode 0 = allreduce (every rank gets the merged map), 1 = reduce-scatter (every rank gets the
+  // keys it owns), 2 = allgather (concatenation in rank order, no reduction).
+  // max_n = max over ALL ranks of n (agreed by the caller); out_cap = capacity of the result in
+  // pairs, identical on every rank. Results live in plane-owned buffers that stay valid until the
+  // next map call: *out_keys/*out_vals receive their addresses, info_host (pinned, 4 x u64 per local
+  // rank, valid after the stream is synchronised) = {pairs, receive overflow, output overflow, own}.
+  void map_collective(int mode, const long long* const* keys, const void* const* vals, const long long* n,
+                      long long max_n, long long out_cap, int dtype, int op, int partition, long long** out_keys,
+                      void** out_vals, unsigned long long** info_host, cudaStream_t s);
+
  private:
   GpuPlane() {}
   void finish_init(GpuOptions opt);
@@ -106,6 +118,9 @@ class GpuPlane {
   std::mutex alloc_mu_;
   std::map<size_t, size_t> used_;  // off -> bytes
   CollStat last_;
+  struct MapWork;
+  MapWork* map_ = nullptr;
+  void map_release();
 };
 
 }  // namespace mp4j

@@ -27,3 +27,23 @@ int thread_ws_slots();
 int thread_ws_max_blocks();
 
 }  // namespace mp4j
+
+#include "map_kernels.cuh"
+
+namespace mp4j {
+// map_kernels.cu (type/op-erased launchers of the sparse-map kernels)
+int map_threads();
+void map_launch_partition(int dtype, const MapExchangeArgs& a, int grid, cudaStream_t s);
+void map_launch_clear(int dtype, int op, const MapTable& t, int grid, cudaStream_t s);
+void map_launch_merge(int dtype, int op, const PeerTable& tab, int rank, const MapTable& t,
+                      unsigned long long rkeys_off, unsigned long long rvals_off, unsigned long long rcnt_off,
+                      long long cap, int grid, cudaStream_t s);
+void map_launch_merge_local(int dtype, int op, const MapTable& t, const long long* keys, const void* vals,
+                            long long n, int grid, cudaStream_t s);
+void map_launch_compact(int dtype, const MapTable& t, long long* out_keys, void* out_vals,
+                        unsigned long long* count, unsigned long long out_cap, int grid, cudaStream_t s);
+void map_launch_gather(int dtype, const PeerTable& tab, unsigned long long ocnt_off, unsigned long long okeys_off,
+                       unsigned long long ovals_off, unsigned long long out_cap, const long long* const* own_keys,
+                       const void* const* own_vals, const unsigned long long* const* own_count, int nlocal, bool push,
+                       int grid, cudaStream_t s);
+}  // namespace mp4j

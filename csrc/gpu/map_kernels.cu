@@ -1,0 +1,409 @@
+// Sparse (map container) collectives on the GPU: allreduceMap / reduceScatterMap / allgatherMap
+// (PCS:2053-2081, 1299-1327, 666-692) as hash-partition -> peer exchange -> hash-merge.
+//
+// The reference hash-partitions a HashMap<String,T> into p HashMaps on the CPU (PCS:2059-2072),
+// ring-reduce-scatters them with a get/put + operator call per (String, value) pair (DOP:225-257),
+// ring-allgathers the p reduced maps and merges them (PCS:2074-2081). Here:
+//   K10 map_partition_push : every (key, value) pair is written STRAIGHT into the owner GPU's
+//        receive region over NVLink (no local bucket copy, no serialisation); per-destination
+//        cursors are warp-aggregated atomics; the last block publishes the counts and meets the
+//        peers at a flag barrier.
+//   K11 map_merge          : the owner inserts what it received into an open-addressing table
+//        (atomicCAS on the key, atomic operator on the value).
+//   map_compact            : table -> dense (key, value) arrays + owned count (published to peers).
+//   map_allgather_push     : every rank pushes its owned pairs to the right offset of every peer's
+//        output (offsets = prefix sums of the published counts, read on the device: no host sync).
+// Float sums use atomicAdd: the order of additions, hence the last bits, is not deterministic
+// (the reference's order is arrival order, PCS:1329-1373 - also unspecified).
+#include <algorithm>
+
+#include "cuda_check.h"
+#include "launch.h"
+#include "map_kernels.cuh"
+
+namespace mp4j {
+
+namespace {
+
+constexpr int kMapThreads = 256;
+constexpr int kCtrlRow = kMaxBlocks - 1;  // flag row used by the single "last block" of a map kernel
+
+__device__ __forceinline__ unsigned long long splitmix64(unsigned long long x) {
+  x += 0x9e3779b97f4a7c15ull;
+  x = (x ^ (x >> 30)) * 0xbf58476d1ce4e5b9ull;
+  x = (x ^ (x >> 27)) * 0x94d049bb133111ebull;
+  return x ^ (x >> 31);
+}
+
+__device__ __forceinline__ int owner_of(long long key, int p, int partition) {
+  if (partition == MP4J_MAP_PART_JAVA32) {
+    int h = (int)(unsigned)(unsigned long long)key;  // low 32 bits = String.hashCode()
+    int m = h % p;                                   // C remainder has Java's sign rule
+    return m < 0 ? m + p : m;
+  }
+  return (int)(splitmix64((unsigned long long)key) % (unsigned)p);
+}
+
+// cross-rank barrier executed by ONE block per rank (whichever finished last) on a fixed flag row
+__device__ __forceinline__ void ctrl_barrier_peers(const PeerTable& t, int rank) {
+  uint32_t* eslot = (uint32_t*)((char*)t.sig[rank] + kSigEpochOff) + kCtrlRow;
+  __shared__ uint32_t epoch_s;
+  if (threadIdx.x == 0) epoch_s = *(volatile uint32_t*)eslot + 1;
+  __syncthreads();
+  const uint32_t e = epoch_s;
+  if (threadIdx.x < (unsigned)t.world) {
+    const int q = threadIdx.x;
+    st_release_sys(t.sig[q] + kCtrlRow * kMaxRanks + rank, e);
+    wait_flag(t, t.sig[rank] + kCtrlRow * kMaxRanks + q, e);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) *(volatile uint32_t*)eslot = e;
+}
+
+// returns true for exactly one block per rank row: the one that finished last
+__device__ __forceinline__ bool last_block_of_rank(unsigned long long* ticket) {
+  __shared__ bool last;
+  __threadfence_system();  // this block's peer stores are performed before it takes a ticket
+  __syncthreads();
+  if (threadIdx.x == 0) last = (atomicAdd(ticket, 1ull) == (unsigned long long)gridDim.x - 1);
+  __syncthreads();
+  if (last) __threadfence_system();
+  return last;
+}
+
+// ---------------------------------------------------------------------------------------- K10
+template <typename V>
+__global__ void __launch_bounds__(kMapThreads) map_partition_push_kernel(const __grid_constant__ MapExchangeArgs a) {
+  const PeerTable& tab = a.tab;
+  const int rank = my_rank(tab);
+  const int p = tab.world;
+  const int row = tab.emulate ? rank : 0;
+  const long long n = a.n[row];
+  const long long* keys = a.keys[row];
+  const V* vals = (const V*)a.vals[row];
+  unsigned long long* cursor = (unsigned long long*)(tab.heap[rank] + a.cursor_off);  // [p] + overflow + ticket
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  const unsigned lane = threadIdx.x & 31;
+  for (long long i0 = (long long)blockIdx.x * blockDim.x; i0 < n; i0 += stride) {
+    const long long i = i0 + threadIdx.x;
+    const bool active = i < n;
+    long long key = active ? keys[i] : 0;
+    V val = active ? vals[i] : V();
+    const int d = active ? owner_of(key, p, a.partition) : -1;
+    // warp-aggregated slot claim: one atomic per distinct destination per warp
+    const unsigned peers = __match_any_sync(0xffffffffu, d);
+    const int leader = __ffs(peers) - 1;
+    unsigned long long base = 0;
+    if (active && (int)lane == leader) base = atomicAdd(&cursor[d], (unsigned long long)__popc(peers));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    if (active) {
+      const unsigned long long slot = base + __popc(peers & ((1u << lane) - 1u));
+      if (slot < (unsigned long long)a.cap) {
+        // region `rank` of destination d
+        long long* rk = (long long*)(tab.heap[d] + a.rkeys_off) + (unsigned long long)rank * a.cap + slot;
+        V* rv = (V*)(tab.heap[d] + a.rvals_off) + (unsigned long long)rank * a.cap + slot;
+        *rk = key;
+        *rv = val;
+      } else {
+        cursor[p] = 1;  // overflow: reported by the host after the call
+      }
+    }
+  }
+  if (last_block_of_rank(&cursor[p + 1])) {
+    if (threadIdx.x < (unsigned)p) {
+      const int q = threadIdx.x;
+      const unsigned long long c = min(*(volatile unsigned long long*)&cursor[q], (unsigned long long)a.cap);
+      *((volatile unsigned long long*)(tab.heap[q] + a.rcnt_off) + rank) = c;
+    }
+    __syncthreads();
+    ctrl_barrier_peers(tab, rank);
+    if (threadIdx.x <= (unsigned)p + 1 && threadIdx.x != (unsigned)p) cursor[threadIdx.x] = 0;  // keep overflow flag
+  }
+}
+
+// ---------------------------------------------------------------------------------------- K11
+template <typename V, int OP>
+__device__ __forceinline__ void atomic_reduce(V* addr, V v) {
+  if constexpr (OP == MP4J_SUM) {
+    if constexpr (sizeof(V) == 8 && !is_fp<V>::value) atomicAdd((unsigned long long*)addr, (unsigned long long)v);
+    else atomicAdd(addr, v);
+  } else if constexpr (!is_fp<V>::value) {
+    if constexpr (OP == MP4J_MAX) atomicMax(addr, v);
+    else atomicMin(addr, v);
+  } else {
+    // float/double max/min: CAS loop with the reference's Math.max/min semantics (ops.h)
+    using U = typename std::conditional<sizeof(V) == 8, unsigned long long, unsigned int>::type;
+    U* ua = (U*)addr;
+    U old = *ua, assumed;
+    do {
+      assumed = old;
+      const V cur = bit_cast<V>(assumed);
+      const V nv = Reduce<V, OP>::apply(cur, v);
+      if (bit_cast<U>(nv) == assumed) break;
+      old = atomicCAS(ua, assumed, bit_cast<U>(nv));
+    } while (old != assumed);
+  }
+}
+
+template <typename V, int OP>
+__device__ __forceinline__ V identity() {
+  if constexpr (OP == MP4J_SUM) return V(0);
+  else if constexpr (is_fp<V>::value) {
+    // -inf / +inf
+    if constexpr (sizeof(V) == 8) return bit_cast<V>(OP == MP4J_MAX ? 0xfff0000000000000ull : 0x7ff0000000000000ull);
+    else return bit_cast<V>(OP == MP4J_MAX ? 0xff800000u : 0x7f800000u);
+  } else if constexpr (sizeof(V) == 8) {
+    return OP == MP4J_MAX ? (V)0x8000000000000000ull : (V)0x7fffffffffffffffull;
+  } else {
+    return OP == MP4J_MAX ? (V)0x80000000u : (V)0x7fffffffu;
+  }
+}
+
+template <typename V, int OP>
+__global__ void __launch_bounds__(kMapThreads) map_clear_kernel(MapTable t) {
+  const unsigned long long size = t.mask + 1;
+  for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < size;
+       i += (unsigned long long)gridDim.x * blockDim.x) {
+    t.keys[i] = kMapEmpty;
+    ((V*)t.vals)[i] = identity<V, OP>();
+  }
+}
+
+// inserts `cnt` pairs; table must have room (size >= 2 * pairs)
+template <typename V, int OP>
+__device__ __forceinline__ void table_insert(const MapTable& t, long long key, V val) {
+  unsigned long long h = splitmix64((unsigned long long)key ^ 0x5851f42d4c957f2dull) & t.mask;
+  for (;;) {
+    const long long prev = (long long)atomicCAS((unsigned long long*)&t.keys[h], (unsigned long long)kMapEmpty,
+                                                (unsigned long long)key);
+    if (prev == kMapEmpty || prev == key) {
+      atomic_reduce<V, OP>((V*)t.vals + h, val);
+      return;
+    }
+    h = (h + 1) & t.mask;
+  }
+}
+
+// merges the p receive regions of this rank (counts in the heap) into its table
+template <typename V, int OP>
+__global__ void __launch_bounds__(kMapThreads) map_merge_kernel(PeerTable tab, int rank_arg, MapTable t,
+                                                                unsigned long long rkeys_off,
+                                                                unsigned long long rvals_off,
+                                                                unsigned long long rcnt_off, long long cap) {
+  const int rank = rank_arg;
+  const int p = tab.world;
+  const unsigned long long* cnt = (const unsigned long long*)(tab.heap[rank] + rcnt_off);
+  const long long* rk = (const long long*)(tab.heap[rank] + rkeys_off);
+  const V* rv = (const V*)(tab.heap[rank] + rvals_off);
+  for (int s = 0; s < p; ++s) {
+    const unsigned long long c = cnt[s];
+    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < c;
+         i += (unsigned long long)gridDim.x * blockDim.x)
+      table_insert<V, OP>(t, rk[(unsigned long long)s * cap + i], rv[(unsigned long long)s * cap + i]);
+  }
+}
+
+// merges a plain local array of pairs (thread-level map reduce / local pre-aggregation)
+template <typename V, int OP>
+__global__ void __launch_bounds__(kMapThreads) map_merge_local_kernel(MapTable t, const long long* keys,
+                                                                      const V* vals, long long n) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    table_insert<V, OP>(t, keys[i], vals[i]);
+}
+
+// table -> dense arrays; count accumulates in *count (zeroed by the caller)
+template <typename V>
+__global__ void __launch_bounds__(kMapThreads) map_compact_kernel(MapTable t, long long* out_keys, V* out_vals,
+                                                                  unsigned long long* count,
+                                                                  unsigned long long out_cap) {
+  const unsigned long long size = t.mask + 1;
+  const unsigned lane = threadIdx.x & 31;
+  for (unsigned long long i0 = (unsigned long long)blockIdx.x * blockDim.x; i0 < size;
+       i0 += (unsigned long long)gridDim.x * blockDim.x) {
+    const unsigned long long i = i0 + threadIdx.x;
+    const bool live = i < size && t.keys[i] != kMapEmpty;
+    const unsigned m = __ballot_sync(0xffffffffu, live);
+    if (m == 0) continue;
+    unsigned long long base = 0;
+    const int leader = __ffs(m) - 1;
+    if ((int)lane == leader) base = atomicAdd(count, (unsigned long long)__popc(m));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    if (live) {
+      const unsigned long long o = base + __popc(m & ((1u << lane) - 1u));
+      if (o < out_cap) {
+        out_keys[o] = t.keys[i];
+        out_vals[o] = ((const V*)t.vals)[i];
+      }
+    }
+  }
+}
+
+// publishes this rank's owned count to every peer, meets the peers, then pushes the owned pairs to
+// offset sum(counts[q < rank]) of every peer's output arrays; total goes to *total_out.
+struct MapGatherArgs {
+  PeerTable tab;
+  unsigned long long ocnt_off;   // heap: uint64 [p] owned counts (slot r written by rank r)
+  unsigned long long okeys_off;  // heap: int64 [out_cap]
+  unsigned long long ovals_off;  // heap: V [out_cap]
+  unsigned long long out_cap;
+  const long long* own_keys[kMaxRanks];
+  const void* own_vals[kMaxRanks];
+  const unsigned long long* own_count[kMaxRanks];
+};
+
+__global__ void __launch_bounds__(kMapThreads) map_publish_count_kernel(const __grid_constant__ MapGatherArgs a) {
+  const PeerTable& tab = a.tab;
+  const int rank = my_rank(tab);
+  const int row = tab.emulate ? rank : 0;
+  if (threadIdx.x < (unsigned)tab.world)
+    *((volatile unsigned long long*)(tab.heap[threadIdx.x] + a.ocnt_off) + rank) = *a.own_count[row];
+  __syncthreads();
+  ctrl_barrier_peers(tab, rank);
+}
+
+template <typename V>
+__global__ void __launch_bounds__(kMapThreads) map_allgather_push_kernel(const __grid_constant__ MapGatherArgs a) {
+  const PeerTable& tab = a.tab;
+  const int rank = my_rank(tab);
+  const int p = tab.world;
+  const int row = tab.emulate ? rank : 0;
+  const volatile unsigned long long* oc = (const volatile unsigned long long*)(tab.heap[rank] + a.ocnt_off);
+  unsigned long long off = 0;
+  for (int q = 0; q < rank; ++q) off += oc[q];
+  const unsigned long long mine = oc[rank];
+  const long long* sk = a.own_keys[row];
+  const V* sv = (const V*)a.own_vals[row];
+  BlockEpoch ep;
+  ep.load(tab, rank);
+  for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < mine;
+       i += (unsigned long long)gridDim.x * blockDim.x) {
+    if (off + i >= a.out_cap) break;
+    const long long k = sk[i];
+    const V v = sv[i];
+    for (int q = 0; q < p; ++q) {
+      ((long long*)(tab.heap[q] + a.okeys_off))[off + i] = k;
+      ((V*)(tab.heap[q] + a.ovals_off))[off + i] = v;
+    }
+  }
+  block_barrier_peers(tab, rank, ep);  // all pushes landed everywhere before anyone reads its output
+  ep.store();
+}
+
+// ---------------------------------------------------------------------------------------- dispatch
+template <typename V>
+void launch_partition(const MapExchangeArgs& a, int grid, cudaStream_t s) {
+  auto kfn = map_partition_push_kernel<V>;
+  if (a.tab.emulate) {
+    void* params[] = {(void*)&a};
+    MP4J_CUDA(cudaLaunchCooperativeKernel((const void*)kfn, dim3(grid, a.tab.world), dim3(kMapThreads), params, 0, s));
+  } else {
+    kfn<<<grid, kMapThreads, 0, s>>>(a);
+    MP4J_CUDA(cudaGetLastError());
+  }
+}
+
+template <typename V>
+void launch_gather(const MapGatherArgs& a, bool push, int grid, cudaStream_t s) {
+  if (a.tab.emulate) {
+    void* params[] = {(void*)&a};
+    MP4J_CUDA(cudaLaunchCooperativeKernel((const void*)map_publish_count_kernel, dim3(1, a.tab.world),
+                                          dim3(kMapThreads), params, 0, s));
+    if (push)
+      MP4J_CUDA(cudaLaunchCooperativeKernel((const void*)map_allgather_push_kernel<V>, dim3(grid, a.tab.world),
+                                            dim3(kMapThreads), params, 0, s));
+  } else {
+    map_publish_count_kernel<<<1, kMapThreads, 0, s>>>(a);
+    if (push) map_allgather_push_kernel<V><<<grid, kMapThreads, 0, s>>>(a);
+    MP4J_CUDA(cudaGetLastError());
+  }
+}
+
+template <typename F>
+void dispatch_v(int dtype, F&& f) {
+  switch (dtype) {
+    case MP4J_F32: return f(float());
+    case MP4J_F64: return f(double());
+    case MP4J_I32: return f(int32_t());
+    case MP4J_I64: return f((long long)0);
+  }
+  throw Error("GPU maps support float/double/int/long values");
+}
+template <typename F>
+void dispatch_op(int op, F&& f) {
+  switch (op) {
+    case MP4J_SUM: return f(std::integral_constant<int, MP4J_SUM>());
+    case MP4J_MAX: return f(std::integral_constant<int, MP4J_MAX>());
+    case MP4J_MIN: return f(std::integral_constant<int, MP4J_MIN>());
+  }
+  throw Error("GPU maps support SUM/MAX/MIN");
+}
+
+}  // namespace
+
+// ---- type/op erased entry points used by the host side (map_plane.cu)
+int map_threads() { return kMapThreads; }
+
+void map_launch_partition(int dtype, const MapExchangeArgs& a, int grid, cudaStream_t s) {
+  dispatch_v(dtype, [&](auto v) { launch_partition<decltype(v)>(a, grid, s); });
+}
+
+void map_launch_clear(int dtype, int op, const MapTable& t, int grid, cudaStream_t s) {
+  dispatch_v(dtype, [&](auto v) {
+    dispatch_op(op, [&](auto o) {
+      map_clear_kernel<decltype(v), decltype(o)::value><<<grid, kMapThreads, 0, s>>>(t);
+    });
+  });
+  MP4J_CUDA(cudaGetLastError());
+}
+
+void map_launch_merge(int dtype, int op, const PeerTable& tab, int rank, const MapTable& t,
+                      unsigned long long rkeys_off, unsigned long long rvals_off, unsigned long long rcnt_off,
+                      long long cap, int grid, cudaStream_t s) {
+  dispatch_v(dtype, [&](auto v) {
+    dispatch_op(op, [&](auto o) {
+      map_merge_kernel<decltype(v), decltype(o)::value><<<grid, kMapThreads, 0, s>>>(tab, rank, t, rkeys_off, rvals_off,
+                                                                                    rcnt_off, cap);
+    });
+  });
+  MP4J_CUDA(cudaGetLastError());
+}
+
+void map_launch_merge_local(int dtype, int op, const MapTable& t, const long long* keys, const void* vals,
+                            long long n, int grid, cudaStream_t s) {
+  dispatch_v(dtype, [&](auto v) {
+    using V = decltype(v);
+    dispatch_op(op, [&](auto o) {
+      map_merge_local_kernel<V, decltype(o)::value><<<grid, kMapThreads, 0, s>>>(t, keys, (const V*)vals, n);
+    });
+  });
+  MP4J_CUDA(cudaGetLastError());
+}
+
+void map_launch_compact(int dtype, const MapTable& t, long long* out_keys, void* out_vals,
+                        unsigned long long* count, unsigned long long out_cap, int grid, cudaStream_t s) {
+  dispatch_v(dtype, [&](auto v) {
+    using V = decltype(v);
+    map_compact_kernel<V><<<grid, kMapThreads, 0, s>>>(t, out_keys, (V*)out_vals, count, out_cap);
+  });
+  MP4J_CUDA(cudaGetLastError());
+}
+
+void map_launch_gather(int dtype, const PeerTable& tab, unsigned long long ocnt_off, unsigned long long okeys_off,
+                       unsigned long long ovals_off, unsigned long long out_cap, const long long* const* own_keys,
+                       const void* const* own_vals, const unsigned long long* const* own_count, int nlocal, bool push,
+                       int grid, cudaStream_t s) {
+  MapGatherArgs a{};
+  a.tab = tab;
+  a.ocnt_off = ocnt_off;
+  a.okeys_off = okeys_off;
+  a.ovals_off = ovals_off;
+  a.out_cap = out_cap;
+  for (int i = 0; i < nlocal; ++i) {
+    a.own_keys[i] = own_keys[i];
+    a.own_vals[i] = own_vals[i];
+    a.own_count[i] = own_count[i];
+  }
+  dispatch_v(dtype, [&](auto v) { launch_gather<decltype(v)>(a, push, grid, s); });
+}
+
+}  // namespace mp4j

@@ -53,4 +53,16 @@ int mp4j_gpu_thread_allreduce(mp4j_gpu* g, void* const* bufs, int T, int dtype, 
                               int64_t to, int fanout, int dst, int local_only, int thread_algo, int algo,
                               void* stream);
 
+/* Sparse (map container) collectives on (int64 key, value) device arrays: allreduceMap (mode 0,
+ * PCS:2053), reduceScatterMap (mode 1, PCS:1299: every rank receives the keys it owns) and
+ * allgatherMap (mode 2, PCS:666: concatenation in rank order). One entry per LOCAL rank in every
+ * array argument. max_n = max over all ranks of n; out_cap = result capacity in pairs (same on all
+ * ranks). partition: 0 = splitmix64(key) % p, 1 = Java String.hashCode placement on the low 32 bits.
+ * Results stay in plane-owned device buffers until the next map call: out_keys/out_vals receive the
+ * addresses; info[i] points to 4 pinned u64 {pairs, receive overflow, output overflow, owned pairs},
+ * valid once `stream` has been synchronised. Key 0x8000000000000000 is reserved. */
+int mp4j_gpu_map_collective(mp4j_gpu* g, int mode, const int64_t* const* keys, const void* const* vals,
+                            const int64_t* n, int64_t max_n, int64_t out_cap, int dtype, int op, int partition,
+                            int64_t** out_keys, void** out_vals, uint64_t** info, void* stream);
+
 #endif /* MP4J_GPU_H_ */

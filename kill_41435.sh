@@ -1,0 +1,2 @@
+ssh test@127.0.0.1 "kill -9 9384"
+kill -9 8873

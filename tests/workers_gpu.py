@@ -57,6 +57,22 @@ def process_gpu(comm):
     x = torch.ones(7, dtype=torch.float32, device="cuda")
     comm.allreduceArrayRpc(x, fop, Operators.Float.SUM)
     assert torch.all(x == p)
+    # sparse map allreduce on tensors: shared keys + one private key per rank
+    # (ProcessAllReduceCheck.java:86-116), twice to exercise buffer reuse
+    obj = 20000
+    for rep in range(2):
+        keys = torch.cat([torch.arange(obj, dtype=torch.int64), torch.tensor([-(r + 1)], dtype=torch.int64)]).cuda()
+        vals = torch.ones(obj + 1, dtype=torch.float32, device="cuda")
+        k, v = comm.gpu.allreduce_map(keys, vals, Operators.Float.SUM)
+        assert k.numel() == obj + p
+        d = dict(zip(k.tolist(), v.tolist()))
+        assert all(d[i] == p for i in range(0, obj, 97)) and all(d[-(q + 1)] == 1 for q in range(p))
+    k, v = comm.gpu.reduce_scatter_map(keys, vals, Operators.Float.SUM)
+    tot = comm.allreduce(int(k.numel()), Operands.LONG_OPERAND(), Operators.Long.SUM)
+    assert tot == obj + p
+    k, v = comm.gpu.allgather_map(torch.full((3,), r, dtype=torch.int64, device="cuda"),
+                                  torch.full((3,), float(r), device="cuda"))
+    assert k.tolist() == [q for q in range(p) for _ in range(3)]
     torch.cuda.synchronize()
     comm.gpu.check()
     comm.barrier()

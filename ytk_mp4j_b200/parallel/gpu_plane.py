@@ -40,6 +40,12 @@ _P("mp4j_gpu_reduce", C.c_int, C.c_void_p, N.c_vpp, C.c_int, C.c_int, C.c_int64,
 _P("mp4j_gpu_thread_allreduce", C.c_int, C.c_void_p, N.c_vpp, C.c_int, C.c_int, C.c_int, C.c_int64, C.c_int64,
    C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p)
 
+_P("mp4j_gpu_map_collective", C.c_int, C.c_void_p, C.c_int, N.c_vpp, N.c_vpp, N.c_i64p, C.c_int64, C.c_int64, C.c_int,
+   C.c_int, C.c_int, N.c_vpp, N.c_vpp, N.c_vpp, C.c_void_p)
+
+MAP_MODES = {"allreduce": 0, "reduce_scatter": 1, "allgather": 2}
+MAP_PARTITIONS = {"mix": 0, "java32": 1}
+
 TORCH_DTYPES = {
     N.F64: torch.float64, N.F32: torch.float32, N.I64: torch.int64, N.I32: torch.int32,
     N.I16: torch.int16, N.I8: torch.int8, N.BF16: torch.bfloat16, N.F16: torch.float16,
@@ -163,6 +169,35 @@ class _PlaneBase:
                                               1 if local_only else 0, thread_algo, algo, _stream_ptr(stream)))
 
 
+    def _map_collective(self, mode, keys, vals, max_n, out_cap, op, partition, stream, clone=True):
+        """keys/vals: one tensor per local rank. Returns [(keys_out, vals_out, info)] per local rank."""
+        L = len(keys)
+        for k, v in zip(keys, vals):
+            _check_tensor(k)
+            _check_tensor(v)
+            if k.dtype != torch.int64 or k.numel() != v.numel():
+                raise Mp4jException("map collectives need int64 keys and as many values as keys")
+        code = _code_of(vals[0])
+        ok, ov, info = (C.c_void_p * L)(), (C.c_void_p * L)(), (C.c_void_p * L)()
+        check(N.lib.mp4j_gpu_map_collective(self._g, MAP_MODES[mode], _ptr_array(keys), _ptr_array(vals),
+                                            N.i64_array([k.numel() for k in keys]), int(max_n), int(out_cap), code, op,
+                                            MAP_PARTITIONS[partition], ok, ov, info, _stream_ptr(stream)))
+        (stream or torch.cuda.current_stream()).synchronize()
+        out = []
+        for i in range(L):
+            st = (C.c_uint64 * 4).from_address(info[i])
+            m, rov, oov, own = int(st[0]), int(st[1]), int(st[2]), int(st[3])
+            if rov:
+                raise Mp4jException("map collective: a receive region overflowed (very skewed key distribution); "
+                                    "raise max_n or pre-aggregate")
+            if oov:
+                raise Mp4jException("map collective: result has more than out_cap=%d pairs" % out_cap)
+            kt = torch.as_tensor(_RawCuda(ok[i], max(m, 1), N.I64, self), device="cuda:%d" % self.device)[:m]
+            vt = torch.as_tensor(_RawCuda(ov[i], max(m, 1), code, self), device="cuda:%d" % self.device)[:m]
+            out.append((kt.clone(), vt.clone(), own) if clone else (kt, vt, own))
+        return out
+
+
 class GpuPlane(_PlaneBase):
     """GPU data plane of a ProcessCommSlave (one process per GPU)."""
 
@@ -218,6 +253,39 @@ class GpuPlane(_PlaneBase):
     def reduce(self, t, operand, operator, f, to, root, algo=N.ALGO_AUTO, stream=None):
         _check_tensor(t)
         self._reduce([t], _code_of(t, operand), _native_op(operator), f, to, root, algo, stream)
+
+    # --- sparse maps on (int64 keys, values) tensors
+    def _map_sizes(self, n, out_cap):
+        from ..operands import Operands
+        from ..operators import Operators
+        lop = Operands.LONG_OPERAND()
+        max_n = self._comm.allreduce(int(n), lop, Operators.Long.MAX)
+        if out_cap is None:
+            out_cap = max(1, self._comm.allreduce(int(n), lop, Operators.Long.SUM))
+        return max_n, out_cap
+
+    def allreduce_map(self, keys, vals, operator, out_cap=None, partition="mix", stream=None):
+        """allreduceMap on tensors (PCS:2053): every rank gets the merged (keys, values); entries
+        with equal keys are reduced with `operator` (SUM/MAX/MIN). Order of the result is
+        unspecified (like a HashMap's). out_cap defaults to the sum of all ranks' sizes."""
+        max_n, out_cap = self._map_sizes(keys.numel(), out_cap)
+        k, v, _ = self._map_collective("allreduce", [keys], [vals], max_n, out_cap, _native_op(operator), partition,
+                                       stream)[0]
+        return k, v
+
+    def reduce_scatter_map(self, keys, vals, operator, partition="mix", stream=None):
+        """reduceScatterMap (PCS:1299) with hash ownership: this rank gets the reduced entries of
+        the keys it owns."""
+        max_n, out_cap = self._map_sizes(keys.numel(), 1)
+        k, v, _ = self._map_collective("reduce_scatter", [keys], [vals], max_n, out_cap, _native_op(operator),
+                                       partition, stream)[0]
+        return k, v
+
+    def allgather_map(self, keys, vals, out_cap=None, stream=None):
+        """allgatherMap (PCS:666): concatenation of all ranks' entries in rank order (no reduction)."""
+        max_n, out_cap = self._map_sizes(keys.numel(), out_cap)
+        k, v, _ = self._map_collective("allgather", [keys], [vals], max_n, out_cap, N.SUM, "mix", stream)[0]
+        return k, v
 
     # --- ThreadCommSlave dispatch targets
     def thread_allreduce(self, ts, operand, operator, f, to, algo=N.ALGO_AUTO, stream=None):
@@ -283,6 +351,13 @@ class EmuPlane(_PlaneBase):
 
     def reduce(self, ts, op, f, t, root, algo=N.ALGO_AUTO, stream=None):
         self._reduce(ts, _code_of(ts[0]), op, f, t, root, algo, stream)
+
+    def map_collective(self, mode, keys, vals, op=N.SUM, out_cap=None, partition="mix", stream=None):
+        """keys/vals: one tensor per emulated rank. Returns [(keys, vals, owned)] per rank."""
+        max_n = max(k.numel() for k in keys)
+        if out_cap is None:
+            out_cap = max(1, sum(k.numel() for k in keys))
+        return self._map_collective(mode, keys, vals, max_n, out_cap, op, partition, stream)
 
     def thread_allreduce(self, ts_by_rank, op, f, t, fanout=True, dst=0, local_only=False, thread_algo=0,
                          algo=N.ALGO_AUTO, stream=None):
