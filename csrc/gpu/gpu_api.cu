@@ -173,4 +173,13 @@ int mp4j_gpu_map_collective(mp4j_gpu* g, int mode, const int64_t* const* keys, c
   MP4J_API_END
 }
 
+int mp4j_gpu_map_reduce_local(mp4j_gpu* g, int local_rank, const int64_t* keys, const void* vals, int64_t n,
+                              int dtype, int op, int64_t* out_keys, void* out_vals, int64_t out_cap,
+                              uint64_t* out_count, void* stream) {
+  MP4J_API_BEGIN
+  g->g->map_reduce_local(local_rank, (const long long*)keys, vals, n, dtype, op, (long long*)out_keys, out_vals,
+                         out_cap, (unsigned long long*)out_count, (cudaStream_t)stream);
+  MP4J_API_END
+}
+
 }  // extern "C"

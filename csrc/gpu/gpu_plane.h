@@ -87,6 +87,13 @@ class GpuPlane {
   void map_collective(int mode, const long long* const* keys, const void* const* vals, const long long* n,
                       long long max_n, long long out_cap, int dtype, int op, int partition, long long** out_keys,
                       void** out_vals, unsigned long long** info_host, cudaStream_t s);
+  // Local reduce-by-key (the thread-level map merge of DOP:458-477 on device arrays, also usable
+  // as pre-aggregation): out = unique keys of (keys, vals) with equal keys reduced by `op`.
+  // *out_count (device u64) receives the number of unique keys (clamped to out_cap). The hash
+  // table is plane-owned scratch (cudaMalloc, cached and grown on demand).
+  void map_reduce_local(int local_rank, const long long* keys, const void* vals, long long n, int dtype, int op,
+                        long long* out_keys, void* out_vals, long long out_cap, unsigned long long* out_count,
+                        cudaStream_t s);
 
  private:
   GpuPlane() {}

@@ -71,6 +71,35 @@ void GpuPlane::map_release() {
   map_ = nullptr;
 }
 
+void GpuPlane::map_reduce_local(int local_rank, const long long* keys, const void* vals, long long n, int dtype,
+                                int op, long long* out_keys, void* out_vals, long long out_cap,
+                                unsigned long long* out_count, cudaStream_t s) {
+  if (local_rank < 0 || local_rank >= local_ranks()) throw Error("map_reduce_local: bad local rank");
+  if (!(dtype == MP4J_F32 || dtype == MP4J_F64 || dtype == MP4J_I32 || dtype == MP4J_I64))
+    throw Error("GPU maps support float/double/int/long values");
+  if (!(op == MP4J_SUM || op == MP4J_MAX || op == MP4J_MIN)) throw Error("GPU maps support SUM/MAX/MIN");
+  if (n < 0 || out_cap < 0) throw Error("map_reduce_local: bad sizes");
+  if (!map_) map_ = new MapWork();
+  auto& l = map_->local[local_rank];
+  const unsigned long long tsize = next_pow2(std::max<unsigned long long>(2ull * (unsigned long long)n, 1024));
+  if (l.tsize < tsize) {
+    MP4J_CUDA(cudaStreamSynchronize(s));
+    if (l.tkeys) cudaFree(l.tkeys);
+    if (l.tvals) cudaFree(l.tvals);
+    MP4J_CUDA(cudaMalloc(&l.tkeys, tsize * 8));
+    MP4J_CUDA(cudaMalloc(&l.tvals, tsize * 8));
+    l.tsize = tsize;
+  }
+  // use only as much of the table as this call needs: clearing dominates small calls otherwise
+  MapTable t{l.tkeys, l.tvals, tsize - 1};
+  const int blocks = std::max(1, std::min(sms_ * 4, kMaxBlocks - 2));
+  map_launch_clear(dtype, op, t, blocks, s);
+  MP4J_CUDA(cudaMemsetAsync(out_count, 0, 8, s));
+  if (n > 0) map_launch_merge_local(dtype, op, t, keys, vals, n, blocks, s);
+  map_launch_compact(dtype, t, out_keys, out_vals, out_count, (unsigned long long)out_cap, blocks, s);
+  last_ = CollStat{"map_reduce_local", "hash-merge", (size_t)n * (8 + dtype_size(dtype)), blocks, false};
+}
+
 void GpuPlane::map_collective(int mode, const long long* const* keys, const void* const* vals, const long long* n,
                               long long max_n, long long out_cap, int dtype, int op, int partition,
                               long long** out_keys, void** out_vals, unsigned long long** info_host,

@@ -65,4 +65,13 @@ int mp4j_gpu_map_collective(mp4j_gpu* g, int mode, const int64_t* const* keys, c
                             const int64_t* n, int64_t max_n, int64_t out_cap, int dtype, int op, int partition,
                             int64_t** out_keys, void** out_vals, uint64_t** info, void* stream);
 
+/* Local reduce-by-key on one GPU: the thread-level map merge (DOP:458-477) on device arrays.
+ * out_keys/out_vals (capacity out_cap pairs) receive the unique keys with equal keys reduced by
+ * `op` (SUM/MAX/MIN; float/double/int/long values), *out_count (device uint64) their number.
+ * The hash table is scratch owned by the plane (allocated with cudaMalloc, cached, grown on
+ * demand). Result order is unspecified. */
+int mp4j_gpu_map_reduce_local(mp4j_gpu* g, int local_rank, const int64_t* keys, const void* vals, int64_t n,
+                              int dtype, int op, int64_t* out_keys, void* out_vals, int64_t out_cap,
+                              uint64_t* out_count, void* stream);
+
 #endif /* MP4J_GPU_H_ */

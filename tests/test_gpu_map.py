@@ -122,3 +122,18 @@ def test_map_output_overflow_is_reported(planes):
     vals = [torch.ones(100, dtype=torch.float32).cuda() for _ in range(2)]
     with pytest.raises(Mp4jException):
         plane.map_collective("allreduce", keys, vals, N.SUM, out_cap=150)
+
+
+@pytest.mark.parametrize("dtype,op", [(torch.float32, N.SUM), (torch.int64, N.MAX), (torch.float64, N.MIN)])
+@pytest.mark.parametrize("n", [1, 1000, 200000])
+def test_map_reduce_local(planes, dtype, op, n):
+    """Thread-level map merge (DOP:458-477) on device arrays: reduce-by-key with a scratch hash table."""
+    plane = planes(1)
+    g = torch.Generator().manual_seed(n)
+    keys = torch.randint(-n, n, (n,), generator=g, dtype=torch.int64)
+    vals = torch.randint(-9, 9, (n,), generator=g).to(dtype)
+    want = ref_reduce([keys], [vals], op)
+    for rep in range(2):
+        k, v = plane.map_reduce_local(keys.cuda(), vals.cuda(), op)
+        got = dict(zip(k.tolist(), v.tolist()))
+        assert got == want and k.numel() == len(want)

@@ -43,6 +43,9 @@ _P("mp4j_gpu_thread_allreduce", C.c_int, C.c_void_p, N.c_vpp, C.c_int, C.c_int, 
 _P("mp4j_gpu_map_collective", C.c_int, C.c_void_p, C.c_int, N.c_vpp, N.c_vpp, N.c_i64p, C.c_int64, C.c_int64, C.c_int,
    C.c_int, C.c_int, N.c_vpp, N.c_vpp, N.c_vpp, C.c_void_p)
 
+_P("mp4j_gpu_map_reduce_local", C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_int,
+   C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p)
+
 MAP_MODES = {"allreduce": 0, "reduce_scatter": 1, "allgather": 2}
 MAP_PARTITIONS = {"mix": 0, "java32": 1}
 
@@ -168,6 +171,24 @@ class _PlaneBase:
         check(N.lib.mp4j_gpu_thread_allreduce(self._g, _ptr_array(ts), T, code, op, f, t, 1 if fanout else 0, dst,
                                               1 if local_only else 0, thread_algo, algo, _stream_ptr(stream)))
 
+
+    def map_reduce_local(self, keys, vals, op=N.SUM, local_rank=0, stream=None):
+        """Reduce-by-key on one GPU (thread-level map merge, DOP:458-477): concatenate the maps of
+        the threads of a process into (keys, vals) and get back unique keys with reduced values."""
+        _check_tensor(keys)
+        _check_tensor(vals)
+        if keys.dtype != torch.int64 or keys.numel() != vals.numel():
+            raise Mp4jException("map_reduce_local needs int64 keys and as many values as keys")
+        n = keys.numel()
+        ok = torch.empty(max(n, 1), dtype=torch.int64, device=keys.device)
+        ov = torch.empty(max(n, 1), dtype=vals.dtype, device=keys.device)
+        cnt = torch.zeros(1, dtype=torch.int64, device=keys.device)
+        op = op if isinstance(op, int) else _native_op(op)
+        check(N.lib.mp4j_gpu_map_reduce_local(self._g, int(local_rank), keys.data_ptr(), vals.data_ptr(), n,
+                                              _code_of(vals), op, ok.data_ptr(), ov.data_ptr(), n, cnt.data_ptr(),
+                                              _stream_ptr(stream)))
+        m = int(cnt.item())
+        return ok[:m], ov[:m]
 
     def _map_collective(self, mode, keys, vals, max_n, out_cap, op, partition, stream, clone=True):
         """keys/vals: one tensor per local rank. Returns [(keys_out, vals_out, info)] per local rank."""
