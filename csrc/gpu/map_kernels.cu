@@ -16,6 +16,8 @@
 // Float sums use atomicAdd: the order of additions, hence the last bits, is not deterministic
 // (the reference's order is arrival order, PCS:1329-1373 - also unspecified).
 #include <algorithm>
+#include <mutex>
+#include <string>
 
 #include "cuda_check.h"
 #include "launch.h"
@@ -406,4 +408,95 @@ void map_launch_gather(int dtype, const PeerTable& tab, unsigned long long ocnt_
   dispatch_v(dtype, [&](auto v) { launch_gather<decltype(v)>(a, push, grid, s); });
 }
 
+// =========================================================================================
+// Allocation-free reduce-by-key.
+//
+// mp4j_map_reduce_local_noalloc is the one entry point of this library that never asks CUDA
+// for memory. It exists for callers that are not allowed, or not able, to allocate on the device
+// at the moment they need a reduce-by-key:
+//   * code that must not synchronise the device (cudaMalloc / cudaFree are synchronising calls, so
+//     an allocation in the middle of a pipelined step stalls every stream of the GPU);
+//   * processes whose device memory has been handed over in full to another owner (a framework's
+//     caching pool, a serving runtime with a fixed budget): a late cudaMalloc there fails or
+//     fragments the pool;
+//   * embedders that link only this C ABI and have no plane object (mp4j_gpu) whose cached
+//     scratch they could reuse.
+// The hash table lives in the file-scope device array below instead: kNoAllocTableSlots slots of
+// (int64 key, 8-byte value) = 8 MiB that every GPU that loads the library keeps until the process
+// exits. That bounds one call to kNoAllocMaxPairs = 262,144 input pairs (load factor <= 0.5).
+//
+// All calls on a device share that one array and it keeps whatever the previous call left in it,
+// so each call first resets the part of the table it is going to use (keys to the empty marker,
+// values to the operator's identity) and zeroes *out_count. Two calls that overlap on the GPU
+// (different streams, or different host threads) would scribble over each other's table: issue
+// them on one stream, or serialise them yourself.
+// =========================================================================================
+namespace {
+
+constexpr unsigned long long kNoAllocMaxPairs = 1ull << 18;
+constexpr unsigned long long kNoAllocTableSlots = 2 * kNoAllocMaxPairs;
+constexpr size_t kNoAllocScratchBytes = kNoAllocTableSlots * 16;
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocScratchBytes];
+
+constexpr int kNoAllocMaxDevices = 64;
+std::mutex g_noalloc_mu;
+void* g_noalloc_ptr[kNoAllocMaxDevices] = {};
+int g_noalloc_sms[kNoAllocMaxDevices] = {};
+
+// In host code `g_noalloc_scratch` is only a handle for the runtime, not a device address: the
+// address a kernel can use has to be asked for, once per device, with that device current. The
+// first call of the entry point on a device does it, so make that call before any stream capture
+// is started on that device.
+void* noalloc_scratch_for_current_device(int* sms) {
+  int dev = -1;
+  MP4J_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kNoAllocMaxDevices) throw Error("no-alloc reduce-by-key: device ordinal out of range");
+  std::lock_guard<std::mutex> lk(g_noalloc_mu);
+  if (!g_noalloc_ptr[dev]) {
+    void* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+    if (e != cudaSuccess || p == nullptr)
+      throw Error(std::string("no-alloc reduce-by-key: cudaGetSymbolAddress failed: ") + cudaGetErrorString(e));
+    int n = 0;
+    MP4J_CUDA(cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev));
+    g_noalloc_sms[dev] = n;
+    g_noalloc_ptr[dev] = p;
+  }
+  *sms = g_noalloc_sms[dev];
+  return g_noalloc_ptr[dev];
+}
+
+}  // namespace
 }  // namespace mp4j
+
+#include "../capi/capi_util.h"
+
+extern "C" int mp4j_map_reduce_local_noalloc(const int64_t* keys, const void* vals, int64_t n, int dtype, int op,
+                                             int64_t* out_keys, void* out_vals, int64_t out_cap, uint64_t* out_count,
+                                             void* stream) {
+  using namespace mp4j;
+  MP4J_API_BEGIN
+  if (n < 0 || out_cap < 0) throw Error("no-alloc reduce-by-key: negative size");
+  if ((unsigned long long)n > kNoAllocMaxPairs)
+    throw Error("no-alloc reduce-by-key: n = " + std::to_string(n) + " pairs exceeds the built-in scratch limit of " +
+                std::to_string(kNoAllocMaxPairs) + " pairs; use mp4j_gpu_map_reduce_local (allocating) for larger inputs");
+  if (!(dtype == MP4J_F32 || dtype == MP4J_F64 || dtype == MP4J_I32 || dtype == MP4J_I64))
+    throw Error("no-alloc reduce-by-key: values must be float/double/int/long");
+  if (!(op == MP4J_SUM || op == MP4J_MAX || op == MP4J_MIN)) throw Error("no-alloc reduce-by-key: op must be SUM/MAX/MIN");
+  if (!out_count || (n > 0 && (!keys || !vals)) || (out_cap > 0 && (!out_keys || !out_vals)))
+    throw Error("no-alloc reduce-by-key: null argument");
+  int sms = 0;
+  char* scratch = (char*)noalloc_scratch_for_current_device(&sms);
+  cudaStream_t s = (cudaStream_t)stream;
+  unsigned long long tsize = 1024;
+  while (tsize < 2ull * (unsigned long long)n) tsize <<= 1;  // <= kNoAllocTableSlots by the check above
+  MapTable t{(long long*)scratch, scratch + kNoAllocTableSlots * 8, tsize - 1};
+  const int blocks = std::max(1, std::min(sms * 4, kMaxBlocks - 2));
+  map_launch_clear(dtype, op, t, blocks, s);         // stale contents of the previous call go here
+  MP4J_CUDA(cudaMemsetAsync(out_count, 0, 8, s));    // the counter accumulates, so it starts at zero
+  if (n > 0) map_launch_merge_local(dtype, op, t, (const long long*)keys, vals, n, blocks, s);
+  map_launch_compact(dtype, t, (long long*)out_keys, out_vals, (unsigned long long*)out_count,
+                     (unsigned long long)out_cap, blocks, s);
+  MP4J_API_END
+}

@@ -74,4 +74,28 @@ int mp4j_gpu_map_reduce_local(mp4j_gpu* g, int local_rank, const int64_t* keys, 
                               int dtype, int op, int64_t* out_keys, void* out_vals, int64_t out_cap,
                               uint64_t* out_count, void* stream);
 
+/* Reduce-by-key without any device allocation. This entry point has NO counterpart in the
+ * reference (ytk-mp4j is host-only Java and never manages device memory); it is an addition for
+ * callers of this C ABI that cannot allocate on the GPU when they need the operation: code that
+ * must not synchronise the device (cudaMalloc and cudaFree do), processes whose device memory
+ * belongs entirely to another allocator or a fixed serving budget, and embedders that have no
+ * mp4j_gpu plane whose cached scratch they could borrow.
+ *
+ * Same contract as mp4j_gpu_map_reduce_local (unique keys of (keys, vals) with equal keys reduced
+ * by SUM/MAX/MIN; float/double/int/long values; result order unspecified; *out_count = number of
+ * unique keys, clamped to out_cap), on the CURRENT device, with these differences:
+ *   - the hash table is a fixed 8 MiB array built into the library (held by every GPU that loads
+ *     it until the process exits), so n may not exceed 262,144 pairs; larger n returns MP4J_ERR
+ *     with a message naming the limit;
+ *   - it calls neither cudaMalloc nor cudaFree nor any allocating library routine; inputs and
+ *     outputs are the caller's;
+ *   - the first call on each device also looks up the device address of that array
+ *     (cudaGetSymbolAddress, checked). Make that first call before starting any stream capture;
+ *   - all calls on a device share the array, which keeps the previous call's contents: every call
+ *     re-initialises the slots it uses and zeroes *out_count first, and calls that overlap on the
+ *     GPU (other streams or threads) corrupt each other - keep them on one stream or serialise. */
+int mp4j_map_reduce_local_noalloc(const int64_t* keys, const void* vals, int64_t n, int dtype, int op,
+                                  int64_t* out_keys, void* out_vals, int64_t out_cap, uint64_t* out_count,
+                                  void* stream);
+
 #endif /* MP4J_GPU_H_ */
