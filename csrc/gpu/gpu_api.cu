@@ -173,6 +173,13 @@ int mp4j_gpu_map_collective(mp4j_gpu* g, int mode, const int64_t* const* keys, c
   MP4J_API_END
 }
 
+int mp4j_gpu_lr_xtr_reduce_scatter(mp4j_gpu* g, const void* const* xt, const void* const* rt, int F, int C, int64_t K,
+                                   float** shard_out, int* feats_per_rank, void* stream) {
+  MP4J_API_BEGIN
+  g->g->lr_xtr_reduce_scatter(xt, rt, F, C, K, shard_out, feats_per_rank, (cudaStream_t)stream);
+  MP4J_API_END
+}
+
 int mp4j_gpu_map_reduce_local(mp4j_gpu* g, int local_rank, const int64_t* keys, const void* vals, int64_t n,
                               int dtype, int op, int64_t* out_keys, void* out_vals, int64_t out_cap,
                               uint64_t* out_count, void* stream) {

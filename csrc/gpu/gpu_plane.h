@@ -87,6 +87,13 @@ class GpuPlane {
   void map_collective(int mode, const long long* const* keys, const void* const* vals, const long long* n,
                       long long max_n, long long out_cap, int dtype, int op, int partition, long long** out_keys,
                       void** out_vals, unsigned long long** info_host, cudaStream_t s);
+  // K12: LR gradient G = sum_ranks Xt[F x K] * Rt[C x K]^T as a tcgen05 GEMM whose tiles are added into
+  // the owner rank's shard (rows [q*fpr, (q+1)*fpr) of G) as they retire. xt/rt: bf16, K-major, one
+  // pointer per local rank. shard_out[i] = this rank's [fpr x C] fp32 shard (plane-owned, valid until
+  // the next call).
+  void lr_xtr_reduce_scatter(const void* const* xt, const void* const* rt, int F, int C, long long K,
+                             float** shard_out, int* feats_per_rank_out, cudaStream_t s);
+
   // Local reduce-by-key (the thread-level map merge of DOP:458-477 on device arrays, also usable
   // as pre-aggregation): out = unique keys of (keys, vals) with equal keys reduced by `op`.
   // *out_count (device u64) receives the number of unique keys (clamped to out_cap). The hash
@@ -125,6 +132,7 @@ class GpuPlane {
   std::mutex alloc_mu_;
   std::map<size_t, size_t> used_;  // off -> bytes
   CollStat last_;
+  size_t lr_shard_off_ = 0, lr_shard_bytes_ = 0;
   struct MapWork;
   MapWork* map_ = nullptr;
   void map_release();

@@ -1,0 +1,339 @@
+// K12 - logistic-regression gradient as a tcgen05 GEMM whose output tiles are reduce-scattered to
+// the owner GPUs as they retire (consumer: ytk-learn's distributed L-BFGS / LR,
+// R/README.md:268-278, which the reference serves with reduceScatterArray, PCS:1174-1209).
+//
+//   G[F x C] = sum over ranks of  Xt[F x K] * Rt[C x K]^T        (K = local rows, bf16 in, fp32 out)
+//   rank q ends up owning rows [q*F/p, (q+1)*F/p) of G           (the reduce-scatter)
+//
+// Both operands are K-major (the design matrix is kept feature-major, Xt, next to the row-major X
+// of the forward pass; the residuals are produced transposed), which is the canonical tcgen05
+// "TN" case: TMA (cp.async.bulk.tensor, 128-byte swizzle) stages [128 x 64] A tiles and [C x 64]
+// B tiles in shared memory through a 4-stage mbarrier ring; ONE elected thread issues
+// tcgen05.mma.cta_group::1.kind::f16 (M = 128, N = C, K = 16) with the fp32 accumulator in TMEM;
+// four epilogue warps read the accumulator back with tcgen05.ld (32 lanes x 32 columns per warp)
+// and add every row straight into the OWNER rank's shard in the symmetric heap with
+// red.global.add.f32 over NVLink - no local G is ever materialised, no separate collective runs.
+// Split-K across CTAs fills the 148 SMs when F/128 tiles are too few; the same atomics merge the
+// splits. Roles per CTA (192 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA
+// issuer, warps 2-5 = epilogue.
+#include <cuda.h>
+#include <cuda_bf16.h>
+
+#include <algorithm>
+
+#include "cuda_check.h"
+#include "gpu_plane.h"
+#include "launch.h"
+
+namespace mp4j {
+
+namespace {
+
+constexpr int kTileM = 128;    // features per CTA tile (UMMA M)
+constexpr int kBlockK = 64;    // bf16 elements per stage row = 128 bytes = one swizzle atom
+constexpr int kUmmaK = 16;
+constexpr int kStages = 4;
+constexpr int kGemmThreads = 192;
+constexpr int kMaxC = 256;
+
+struct LrArgs {
+  CUtensorMap tma_a[kMaxRanks];  // Xt of each local rank: dims {K, F}
+  CUtensorMap tma_b[kMaxRanks];  // Rt of each local rank: dims {K, C}
+  PeerTable tab;
+  unsigned long long out_off;    // heap offset of this rank's G shard [feats_per_rank x C] fp32
+  int F, C, K;
+  int feats_per_rank;            // ceil(F / p)
+  int k_blocks_per_split;        // 64-element K blocks handled by one CTA
+  int tmem_cols;                 // power of two >= max(32, C)
+};
+
+__device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_addr(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(bar)), "r"(bytes) : "memory");
+}
+// bounded wait: a protocol bug must surface as a trap, never as a hung GPU
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  const unsigned long long t0 = globaltimer_ns();
+  for (;;) {
+    uint32_t done;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(done)
+        : "r"(smem_addr(bar)), "r"(parity)
+        : "memory");
+    if (done) return;
+    if (globaltimer_ns() - t0 > 4000000000ull) __trap();
+  }
+}
+__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
+          smem_addr(smem_dst)),
+      "l"(map), "r"(c0), "r"(c1), "r"(smem_addr(bar))
+      : "memory");
+}
+// K-major, 128-byte swizzle: rows of 128 B, 8-row groups 1024 B apart (SBO), descriptor version 1
+__device__ __forceinline__ uint64_t umma_desc_sw128(const void* smem_tile, int k_byte_offset) {
+  const uint32_t addr = smem_addr(smem_tile) + (uint32_t)k_byte_offset;
+  uint64_t d = 0;
+  d |= (uint64_t)((addr & 0x3ffffu) >> 4);       // start address      [0,14)
+  d |= (uint64_t)1 << 16;                          // leading byte off.  [16,30) (unused for SW128 K-major)
+  d |= (uint64_t)(1024 >> 4) << 32;                // stride byte offset [32,46)
+  d |= (uint64_t)1 << 46;                          // version = 1 (Blackwell)
+  d |= (uint64_t)2 << 61;                          // layout type SWIZZLE_128B
+  return d;
+}
+// kind::f16 instruction descriptor: D = fp32, A = B = bf16, both K-major, M = 128, N = n
+__device__ __forceinline__ uint32_t umma_idesc_bf16(int n) {
+  uint32_t d = 0;
+  d |= 1u << 4;                    // c_format = F32
+  d |= 1u << 7;                    // a_format = BF16
+  d |= 1u << 10;                   // b_format = BF16
+  d |= (uint32_t)(n >> 3) << 17;   // n_dim
+  d |= (uint32_t)(kTileM >> 4) << 24;  // m_dim
+  return d;
+}
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                          uint32_t accumulate) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+      "}\n" ::"r"(tmem_d),
+      "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_addr(bar))
+               : "memory");
+}
+
+__global__ void __launch_bounds__(kGemmThreads, 1) lr_xtr_rs_kernel(const __grid_constant__ LrArgs a) {
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
+  __shared__ __align__(8) uint64_t full_bar[kStages], empty_bar[kStages], tmem_full_bar;
+  __shared__ uint32_t tmem_base_s;
+  const PeerTable& tab = a.tab;
+  const int rank = tab.emulate ? (int)blockIdx.z : tab.rank;
+  const int row = tab.emulate ? rank : 0;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int tile_m = blockIdx.x;
+  const int kb_total = (a.K + kBlockK - 1) / kBlockK;
+  const int kb_begin = blockIdx.y * a.k_blocks_per_split;
+  const int kb_end = min(kb_total, kb_begin + a.k_blocks_per_split);
+  const int nkb = kb_end - kb_begin;  // >= 1 by construction of the grid
+  const uint32_t a_bytes = kTileM * kBlockK * 2, b_bytes = (uint32_t)a.C * kBlockK * 2;
+  // 1024-byte aligned stage buffers (128B swizzle atoms repeat every 1024 B)
+  unsigned char* smem = (unsigned char*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  unsigned char* smem_a = smem;
+  unsigned char* smem_b = smem + (size_t)kStages * a_bytes;
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&a.tma_a[row]) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&a.tma_b[row]) : "memory");
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    mbar_init(&tmem_full_bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  if (warp == 1) {  // one warp allocates TMEM and later frees it
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_addr(&tmem_base_s)),
+                 "r"((uint32_t)a.tmem_cols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_d = tmem_base_s;
+
+  if (warp == 0) {
+    // ===== TMA producer
+    if (lane == 0) {
+      for (int i = 0; i < nkb; ++i) {
+        const int s = i % kStages;
+        if (i >= kStages) mbar_wait(&empty_bar[s], ((i / kStages) - 1) & 1);
+        mbar_expect_tx(&full_bar[s], a_bytes + b_bytes);
+        const int k0 = (kb_begin + i) * kBlockK;
+        tma_load_2d(smem_a + (size_t)s * a_bytes, &a.tma_a[row], k0, tile_m * kTileM, &full_bar[s]);
+        tma_load_2d(smem_b + (size_t)s * b_bytes, &a.tma_b[row], k0, 0, &full_bar[s]);
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer: a single thread drives the tensor core
+    if (lane == 0) {
+      const uint32_t idesc = umma_idesc_bf16(a.C);
+      for (int i = 0; i < nkb; ++i) {
+        const int s = i % kStages;
+        mbar_wait(&full_bar[s], (i / kStages) & 1);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+#pragma unroll
+        for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+          const uint64_t da = umma_desc_sw128(smem_a + (size_t)s * a_bytes, k * kUmmaK * 2);
+          const uint64_t db = umma_desc_sw128(smem_b + (size_t)s * b_bytes, k * kUmmaK * 2);
+          umma_bf16(tmem_d, da, db, idesc, (i > 0 || k > 0) ? 1u : 0u);
+        }
+        umma_commit(&empty_bar[s]);  // frees the smem stage once these MMAs have read it
+      }
+      umma_commit(&tmem_full_bar);   // accumulator complete
+    }
+  } else {
+    // ===== epilogue warps 2..5: TMEM -> registers -> red.add into the owner's shard
+    const int quarter = warp & 3;  // a warp may only touch TMEM lanes [32*(warp%4), +32)
+    mbar_wait(&tmem_full_bar, 0);
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const int f = tile_m * kTileM + quarter * 32 + lane;  // global feature row of this thread
+    const int owner = min(f / a.feats_per_rank, tab.world - 1);
+    const int local_row = f - owner * a.feats_per_rank;
+    float* dst_row = (float*)(tab.heap[owner] + a.out_off) + (size_t)local_row * a.C;
+    for (int c0 = 0; c0 < a.C; c0 += 32) {
+      uint32_t v[32];
+      const uint32_t taddr = tmem_d + ((uint32_t)(quarter * 32) << 16) + (uint32_t)c0;
+      asm volatile(
+          "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+          "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
+          "%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+          : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+            "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
+            "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
+            "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+          : "r"(taddr)
+          : "memory");
+      asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+      if (f < a.F) {
+#pragma unroll
+        for (int j = 0; j < 32; j += 4) {
+          if (c0 + j < a.C)
+            asm volatile("red.relaxed.sys.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst_row + c0 + j),
+                         "f"(__uint_as_float(v[j])), "f"(__uint_as_float(v[j + 1])), "f"(__uint_as_float(v[j + 2])),
+                         "f"(__uint_as_float(v[j + 3]))
+                         : "memory");
+        }
+      }
+    }
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"((uint32_t)a.tmem_cols)
+                 : "memory");
+  }
+}
+
+// one-block cross-rank barrier between the phases (zero shard | accumulate | consume)
+constexpr int kLrCtrlRow = kMaxBlocks - 2;
+__global__ void lr_peer_barrier_kernel(PeerTable tab) {
+  const int rank = tab.emulate ? (int)blockIdx.y : tab.rank;
+  uint32_t* eslot = (uint32_t*)((char*)tab.sig[rank] + kSigEpochOff) + kLrCtrlRow;
+  __shared__ uint32_t e_s;
+  if (threadIdx.x == 0) e_s = *(volatile uint32_t*)eslot + 1;
+  __syncthreads();
+  const uint32_t e = e_s;
+  if (threadIdx.x < (unsigned)tab.world) {
+    st_release_sys(tab.sig[threadIdx.x] + kLrCtrlRow * kMaxRanks + rank, e);
+    wait_flag(tab, tab.sig[rank] + kLrCtrlRow * kMaxRanks + threadIdx.x, e);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) *(volatile uint32_t*)eslot = e;
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_tiled() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult st;
+    cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &st);
+    if (e != cudaSuccess || st != cudaDriverEntryPointSuccess || !p) throw Error("cuTensorMapEncodeTiled not available");
+    fn = (EncodeTiledFn)p;
+  }
+  return fn;
+}
+
+// row-major [rows x K] bf16, K contiguous; box = [box_rows x 64]
+void make_map(CUtensorMap* m, const void* base, long long rows, long long K, int box_rows) {
+  cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)K * 2};
+  cuuint32_t box[2] = {(cuuint32_t)kBlockK, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = encode_tiled()(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, (void*)base, dims, strides, box, estr,
+                              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                              CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) throw Error("cuTensorMapEncodeTiled failed (" + std::to_string((int)r) + ")");
+}
+
+}  // namespace
+
+// Host entry: G shards are plane-owned symmetric buffers; returns their address for every local rank.
+void GpuPlane::lr_xtr_reduce_scatter(const void* const* xt, const void* const* rt, int F, int C, long long K,
+                                     float** shard_out, int* feats_per_rank_out, cudaStream_t s) {
+  const int p = world();
+  const int L = local_ranks();
+  if (F <= 0 || K <= 0) throw Error("lr_xtr_reduce_scatter: bad shape");
+  if (C < 16 || C > kMaxC || C % 16 != 0) throw Error("lr_xtr_reduce_scatter: C must be a multiple of 16 in [16, 256]");
+  if (K % 8 != 0) throw Error("lr_xtr_reduce_scatter: K (rows) must be a multiple of 8 (16-byte TMA row pitch)");
+  const int fpr = (F + p - 1) / p;
+  const size_t shard_bytes = (size_t)fpr * C * 4;
+  if (lr_shard_bytes_ < shard_bytes) {
+    MP4J_CUDA(cudaStreamSynchronize(s));
+    if (lr_shard_bytes_) free(lr_shard_off_);
+    lr_shard_off_ = alloc(shard_bytes);
+    lr_shard_bytes_ = shard_bytes;
+  }
+  LrArgs a{};
+  a.tab = table();
+  a.out_off = lr_shard_off_;
+  a.F = F;
+  a.C = C;
+  a.K = (int)K;
+  a.feats_per_rank = fpr;
+  int cols = 32;
+  while (cols < C) cols <<= 1;
+  a.tmem_cols = cols;
+  for (int i = 0; i < L; ++i) {
+    make_map(&a.tma_a[i], xt[i], F, K, kTileM);
+    make_map(&a.tma_b[i], rt[i], C, K, C);
+  }
+  const int tiles_m = (F + kTileM - 1) / kTileM;
+  const int kb_total = (int)((K + kBlockK - 1) / kBlockK);
+  // split K so that about two waves of CTAs cover the SMs
+  int splits = std::max(1, std::min(kb_total, (2 * sms_ + tiles_m - 1) / tiles_m));
+  a.k_blocks_per_split = (kb_total + splits - 1) / splits;
+  splits = (kb_total + a.k_blocks_per_split - 1) / a.k_blocks_per_split;
+  const size_t smem = (size_t)kStages * (kTileM * kBlockK * 2 + (size_t)C * kBlockK * 2) + 1024;
+  static bool attr_set = false;
+  if (!attr_set) {
+    MP4J_CUDA(cudaFuncSetAttribute(lr_xtr_rs_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+    attr_set = true;
+  }
+  // zero my shard | everyone zeroed | accumulate into owners | everyone done
+  for (int i = 0; i < L; ++i) {
+    const int r = emulated() ? i : rank();
+    MP4J_CUDA(cudaMemsetAsync(heap_.base(r) + lr_shard_off_, 0, shard_bytes, s));
+    shard_out[i] = (float*)(heap_.base(r) + lr_shard_off_);
+  }
+  *feats_per_rank_out = fpr;
+  PeerTable tab = a.tab;
+  if (p > 1) lr_peer_barrier_kernel<<<dim3(1, emulated() ? p : 1), 32, 0, s>>>(tab);
+  lr_xtr_rs_kernel<<<dim3(tiles_m, splits, emulated() ? p : 1), kGemmThreads, smem, s>>>(a);
+  MP4J_CUDA(cudaGetLastError());
+  if (p > 1) lr_peer_barrier_kernel<<<dim3(1, emulated() ? p : 1), 32, 0, s>>>(tab);
+  MP4J_CUDA(cudaGetLastError());
+  last_ = CollStat{"lr_xtr_reduce_scatter", "tcgen05+red.add", (size_t)F * K * 2, tiles_m * splits, false};
+}
+
+}  // namespace mp4j

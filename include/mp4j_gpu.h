@@ -65,6 +65,16 @@ int mp4j_gpu_map_collective(mp4j_gpu* g, int mode, const int64_t* const* keys, c
                             const int64_t* n, int64_t max_n, int64_t out_cap, int dtype, int op, int partition,
                             int64_t** out_keys, void** out_vals, uint64_t** info, void* stream);
 
+/* Logistic-regression gradient fused with its reduce-scatter (consumer of reduceScatterArray in
+ * ytk-learn's distributed L-BFGS, reference README.md:268-278): G = sum over ranks of
+ * Xt[F x K] * Rt[C x K]^T with bf16 K-major operands (K = local rows), fp32 result. The GEMM runs on
+ * the tcgen05 tensor cores (TMA-fed, TMEM accumulator); every output tile is added straight into
+ * the shard of the rank that owns its rows, over NVLink. C must be a multiple of 16 in [16, 256],
+ * K a multiple of 8. shard_out[i] receives this rank's [feats_per_rank x C] fp32 shard (rows
+ * [rank*fpr, ...) of G; plane-owned, valid until the next call). One pointer per LOCAL rank. */
+int mp4j_gpu_lr_xtr_reduce_scatter(mp4j_gpu* g, const void* const* xt, const void* const* rt, int F, int C, int64_t K,
+                                   float** shard_out, int* feats_per_rank, void* stream);
+
 /* Local reduce-by-key on one GPU: the thread-level map merge (DOP:458-477) on device arrays.
  * out_keys/out_vals (capacity out_cap pairs) receive the unique keys with equal keys reduced by
  * `op` (SUM/MAX/MIN; float/double/int/long values), *out_count (device uint64) their number.

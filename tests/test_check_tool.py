@@ -1,0 +1,16 @@
+"""CommCheckTool equivalent: the whole check matrix through the launcher (CPU, loopback)."""
+import subprocess
+import sys
+
+import pytest
+
+
+@pytest.mark.parametrize("mode,threads,nproc", [("process", 1, 2), ("thread", 2, 2)])
+def test_check_matrix_via_launcher(mode, threads, nproc, tmp_path):
+    cmd = [sys.executable, "-m", "ytk_mp4j_b200.parallel.launch", "--nproc", str(nproc), "--threads", str(threads),
+           "--log-dir", str(tmp_path / "log"), "--timeout", "240", "--check", "arr_size=2000", "obj_size=30",
+           "run_time=1", "mode=%s" % mode, "threads=%d" % threads, "test_rpc=true", "compress=true"]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr[-3000:]
+    log = (tmp_path / "log" / "master.log").read_text()
+    assert "all checks passed" in log and "allreduce takes:" in log

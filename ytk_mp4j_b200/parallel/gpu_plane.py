@@ -46,6 +46,9 @@ _P("mp4j_gpu_map_collective", C.c_int, C.c_void_p, C.c_int, N.c_vpp, N.c_vpp, N.
 _P("mp4j_gpu_map_reduce_local", C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_int,
    C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p)
 
+_P("mp4j_gpu_lr_xtr_reduce_scatter", C.c_int, C.c_void_p, N.c_vpp, N.c_vpp, C.c_int, C.c_int, C.c_int64, N.c_vpp,
+   C.POINTER(C.c_int), C.c_void_p)
+
 MAP_MODES = {"allreduce": 0, "reduce_scatter": 1, "allgather": 2}
 MAP_PARTITIONS = {"mix": 0, "java32": 1}
 
@@ -172,6 +175,27 @@ class _PlaneBase:
                                               1 if local_only else 0, thread_algo, algo, _stream_ptr(stream)))
 
 
+    def _lr_xtr_reduce_scatter(self, xts, rts, stream=None):
+        """xts[i]: [F, K] bf16, rts[i]: [C, K] bf16 (one pair per local rank). Returns per local rank the
+        [fpr, C] fp32 shard (view of plane memory) of G = sum_ranks Xt @ Rt^T, and fpr."""
+        F, K = xts[0].shape
+        Cc = rts[0].shape[0]
+        for x, r in zip(xts, rts):
+            if x.dtype != torch.bfloat16 or r.dtype != torch.bfloat16 or not x.is_contiguous() or not r.is_contiguous():
+                raise Mp4jException("lr_xtr_reduce_scatter needs contiguous bf16 [F,K] and [C,K] tensors")
+            if tuple(x.shape) != (F, K) or tuple(r.shape) != (Cc, K):
+                raise Mp4jException("lr_xtr_reduce_scatter: shape mismatch between ranks")
+        L = len(xts)
+        shards = (C.c_void_p * L)()
+        fpr = C.c_int(0)
+        check(N.lib.mp4j_gpu_lr_xtr_reduce_scatter(self._g, _ptr_array(xts), _ptr_array(rts), int(F), int(Cc), int(K),
+                                                   shards, C.byref(fpr), _stream_ptr(stream)))
+        out = []
+        for i in range(L):
+            t = torch.as_tensor(_RawCuda(shards[i], fpr.value * Cc, N.F32, self), device="cuda:%d" % self.device)
+            out.append(t.view(fpr.value, Cc))
+        return out, fpr.value
+
     def map_reduce_local(self, keys, vals, op=N.SUM, local_rank=0, stream=None):
         """Reduce-by-key on one GPU (thread-level map merge, DOP:458-477): concatenate the maps of
         the threads of a process into (keys, vals) and get back unique keys with reduced values."""
@@ -275,6 +299,12 @@ class GpuPlane(_PlaneBase):
         _check_tensor(t)
         self._reduce([t], _code_of(t, operand), _native_op(operator), f, to, root, algo, stream)
 
+    def lr_xtr_reduce_scatter(self, xt, rt, stream=None):
+        """Fused LR gradient + reduce-scatter (K12): returns this rank's [fpr, C] fp32 shard of
+        G = sum over ranks of xt @ rt.T (xt: [F, rows] bf16, rt: [C, rows] bf16) and fpr."""
+        shards, fpr = self._lr_xtr_reduce_scatter([xt], [rt], stream)
+        return shards[0], fpr
+
     # --- sparse maps on (int64 keys, values) tensors
     def _map_sizes(self, n, out_cap):
         from ..operands import Operands
@@ -372,6 +402,9 @@ class EmuPlane(_PlaneBase):
 
     def reduce(self, ts, op, f, t, root, algo=N.ALGO_AUTO, stream=None):
         self._reduce(ts, _code_of(ts[0]), op, f, t, root, algo, stream)
+
+    def lr_xtr_reduce_scatter(self, xts, rts, stream=None):
+        return self._lr_xtr_reduce_scatter(xts, rts, stream)
 
     def map_collective(self, mode, keys, vals, op=N.SUM, out_cap=None, partition="mix", stream=None):
         """keys/vals: one tensor per emulated rank. Returns [(keys, vals, owned)] per rank."""

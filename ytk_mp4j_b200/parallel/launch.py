@@ -1,0 +1,73 @@
+"""mp4j-launch: start a master plus N local slaves (one per GPU), optionally T threads each.
+
+Replaces bin/comm_cluster_error_check.sh (kill the previous run, scp artefacts, start the master,
+ssh-start one JVM per host; R/bin/comm_cluster_error_check.sh:1-61) for the single-node case, and
+prints the ssh command lines for multi-node use.
+
+  python -m ytk_mp4j_b200.parallel.launch --nproc 8 [--port 61235] [--threads 1] script.py [args...]
+  python -m ytk_mp4j_b200.parallel.launch --nproc 4 --check arr_size=1000000 mode=thread threads=2 device=cuda
+
+Each slave process gets MP4J_MASTER_HOST, MP4J_MASTER_PORT, MP4J_RANK (rank hint), MP4J_WORLD,
+LOCAL_RANK and CUDA device = LOCAL_RANK. The launcher's exit code is the master's job code
+(0 iff every slave closed with 0), exactly what CommMaster.main returns (CommMaster.java:127-130).
+"""
+import argparse
+import os
+import subprocess
+import sys
+
+from ..master import CommMaster
+
+
+def main(argv=None):
+    ap = argparse.ArgumentParser(prog="mp4j-launch")
+    ap.add_argument("--nproc", type=int, required=True)
+    ap.add_argument("--port", type=int, default=0)
+    ap.add_argument("--host", default="127.0.0.1")
+    ap.add_argument("--threads", type=int, default=1)
+    ap.add_argument("--log-dir", default="log")
+    ap.add_argument("--timeout", type=float, default=None)
+    ap.add_argument("--check", action="store_true", help="run the CommCheckTool matrix instead of a script")
+    ap.add_argument("--print-ssh", nargs="*", metavar="HOST", help="only print per-host ssh command lines")
+    ap.add_argument("rest", nargs=argparse.REMAINDER)
+    a = ap.parse_args(argv)
+
+    master = CommMaster(a.nproc, a.port, log_dir=a.log_dir, quiet=False).start()
+    port = master.port
+    if a.check:
+        kv = dict(x.split("=", 1) for x in a.rest if "=" in x)
+        cmd = [sys.executable, "-m", "ytk_mp4j_b200.check.comm_check_tool", os.environ.get("USER", "mp4j"), a.host,
+               str(port), kv.get("arr_size", "1000000"), kv.get("obj_size", "1000"), kv.get("run_time", "1"),
+               kv.get("threads", str(a.threads)), kv.get("mode", "process"), kv.get("compress", "false"),
+               kv.get("test_rpc", "false"), kv.get("device", "cpu")]
+    else:
+        if not a.rest:
+            ap.error("give a script to run (or --check)")
+        cmd = [sys.executable] + [x for x in a.rest if x != "--"]
+    if a.print_ssh is not None:
+        for i, h in enumerate(a.print_ssh or ["<host>"] * a.nproc):
+            print("ssh %s 'MP4J_MASTER_HOST=%s MP4J_MASTER_PORT=%d MP4J_RANK=%d MP4J_WORLD=%d %s'" %
+                  (h, a.host, port, i, a.nproc, " ".join(cmd)))
+        master.close()
+        return 0
+    procs = []
+    for i in range(a.nproc):
+        env = dict(os.environ, MP4J_MASTER_HOST=a.host, MP4J_MASTER_PORT=str(port), MP4J_RANK=str(i),
+                   MP4J_WORLD=str(a.nproc), LOCAL_RANK=str(i), MP4J_HOST="127.0.0.1", MP4J_THREADS=str(a.threads))
+        procs.append(subprocess.Popen(cmd, env=env))
+    code = master.stop(timeout_s=a.timeout)
+    for p in procs:
+        try:
+            p.wait(timeout=30 if code is not None else 1)
+        except subprocess.TimeoutExpired:
+            p.kill()  # the exact children this launcher started
+    master.close()
+    if code is None:
+        print("mp4j-launch: timeout, job killed", file=sys.stderr)
+        return 124
+    print("mp4j-launch: job exit code %d" % code, file=sys.stderr)
+    return code
+
+
+if __name__ == "__main__":
+    sys.exit(main())
