@@ -32,7 +32,7 @@ namespace {
 constexpr int kTileM = 128;    // features per CTA tile (UMMA M)
 constexpr int kBlockK = 64;    // bf16 elements per stage row = 128 bytes = one swizzle atom
 constexpr int kUmmaK = 16;
-constexpr int kStages = 4;
+constexpr int kMaxStages = 8;  // ring depth is a launch parameter: as deep as 200 KB of smem allows
 constexpr int kGemmThreads = 192;
 constexpr int kMaxC = 256;
 
@@ -45,6 +45,7 @@ struct LrArgs {
   int feats_per_rank;            // ceil(F / p)
   int k_blocks_per_split;        // 64-element K blocks handled by one CTA
   int tmem_cols;                 // power of two >= max(32, C)
+  int stages;                    // smem ring depth (2..kMaxStages)
 };
 
 __device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -119,7 +120,7 @@ __device__ __forceinline__ void umma_commit(uint64_t* bar) {
 
 __global__ void __launch_bounds__(kGemmThreads, 1) lr_xtr_rs_kernel(const __grid_constant__ LrArgs a) {
   extern __shared__ __align__(1024) unsigned char smem_raw[];
-  __shared__ __align__(8) uint64_t full_bar[kStages], empty_bar[kStages], tmem_full_bar;
+  __shared__ __align__(8) uint64_t full_bar[kMaxStages], empty_bar[kMaxStages], tmem_full_bar;
   __shared__ uint32_t tmem_base_s;
   const PeerTable& tab = a.tab;
   const int rank = tab.emulate ? (int)blockIdx.z : tab.rank;
@@ -134,12 +135,12 @@ __global__ void __launch_bounds__(kGemmThreads, 1) lr_xtr_rs_kernel(const __grid
   // 1024-byte aligned stage buffers (128B swizzle atoms repeat every 1024 B)
   unsigned char* smem = (unsigned char*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   unsigned char* smem_a = smem;
-  unsigned char* smem_b = smem + (size_t)kStages * a_bytes;
+  unsigned char* smem_b = smem + (size_t)a.stages * a_bytes;
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&a.tma_a[row]) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&a.tma_b[row]) : "memory");
-    for (int s = 0; s < kStages; ++s) {
+    for (int s = 0; s < a.stages; ++s) {
       mbar_init(&full_bar[s], 1);
       mbar_init(&empty_bar[s], 1);
     }
@@ -162,8 +163,8 @@ __global__ void __launch_bounds__(kGemmThreads, 1) lr_xtr_rs_kernel(const __grid
     // ===== TMA producer
     if (lane == 0) {
       for (int i = 0; i < nkb; ++i) {
-        const int s = i % kStages;
-        if (i >= kStages) mbar_wait(&empty_bar[s], ((i / kStages) - 1) & 1);
+        const int s = i % a.stages;
+        if (i >= a.stages) mbar_wait(&empty_bar[s], ((i / a.stages) - 1) & 1);
         mbar_expect_tx(&full_bar[s], a_bytes + b_bytes);
         const int k0 = (kb_begin + i) * kBlockK;
         tma_load_2d(smem_a + (size_t)s * a_bytes, &a.tma_a[row], k0, tile_m * kTileM, &full_bar[s]);
@@ -175,8 +176,8 @@ __global__ void __launch_bounds__(kGemmThreads, 1) lr_xtr_rs_kernel(const __grid
     if (lane == 0) {
       const uint32_t idesc = umma_idesc_bf16(a.C);
       for (int i = 0; i < nkb; ++i) {
-        const int s = i % kStages;
-        mbar_wait(&full_bar[s], (i / kStages) & 1);
+        const int s = i % a.stages;
+        mbar_wait(&full_bar[s], (i / a.stages) & 1);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 #pragma unroll
         for (int k = 0; k < kBlockK / kUmmaK; ++k) {
@@ -310,11 +311,31 @@ void GpuPlane::lr_xtr_reduce_scatter(const void* const* xt, const void* const* r
   }
   const int tiles_m = (F + kTileM - 1) / kTileM;
   const int kb_total = (int)((K + kBlockK - 1) / kBlockK);
-  // split K so that about two waves of CTAs cover the SMs
-  int splits = std::max(1, std::min(kb_total, (2 * sms_ + tiles_m - 1) / tiles_m));
+  // Ring depth: as deep as ~200 KB of shared memory allows (one CTA per SM): HBM latency under load is
+  // 2-3 us, so a 4-stage ring (64 KB of A in flight) left DRAM at 53 % (profiles/README.md §4).
+  const size_t stage_bytes = (size_t)kTileM * kBlockK * 2 + (size_t)C * kBlockK * 2;
+  a.stages = (int)std::max<size_t>(2, std::min<size_t>(kMaxStages, (200 * 1024) / stage_bytes));
+  // Split K so the grid is close to a whole number of waves of 148 CTAs (one CTA per SM): the first
+  // version launched 320 CTAs = 2.16 waves, i.e. a third wave at 16 % occupancy.
+  int best_splits = 1;
+  double best_eff = 0.0;
+  const int max_splits = std::max(1, std::min(kb_total / 4, 64));
+  for (int sp = 1; sp <= max_splits; ++sp) {
+    const int kps = (kb_total + sp - 1) / sp;
+    const int real = (kb_total + kps - 1) / kps;
+    const long long ctas = (long long)tiles_m * real;
+    const long long waves = (ctas + sms_ - 1) / sms_;
+    const double eff = (double)ctas / (double)(waves * sms_);
+    if (eff > best_eff + 0.02 || (ctas >= 2 * sms_ && best_eff < 0.9 && eff > best_eff)) {
+      best_eff = eff;
+      best_splits = real;
+    }
+    if (best_eff >= 0.95 && ctas >= sms_) break;
+  }
+  int splits = best_splits;
   a.k_blocks_per_split = (kb_total + splits - 1) / splits;
   splits = (kb_total + a.k_blocks_per_split - 1) / a.k_blocks_per_split;
-  const size_t smem = (size_t)kStages * (kTileM * kBlockK * 2 + (size_t)C * kBlockK * 2) + 1024;
+  const size_t smem = (size_t)a.stages * stage_bytes + 1024;
   static bool attr_set = false;
   if (!attr_set) {
     MP4J_CUDA(cudaFuncSetAttribute(lr_xtr_rs_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));

@@ -1,0 +1,94 @@
+"""Data-parallel multinomial logistic regression on top of the communicator - the consumer the
+reference names first (ytk-learn LR / L-BFGS: instance counts, gradients, R/README.md:268-278).
+
+Per step, on every rank (one GPU each):
+  logits = X @ W                       bf16 GEMM (cuBLAS: a plain library GEMM)
+  R      = softmax(logits) - onehot(y) fp32, written transposed as bf16 [C, rows]
+  G_r    = reduce-scatter over ranks of X^T R    ONE fused kernel: tcgen05 GEMM whose output tiles
+                                                  are added into the owner rank's shard (K12)
+  W_r   -= lr * G_r / N                 sharded update: rank r owns rows [r*fpr, (r+1)*fpr) of W
+  W      = allgather(W_r)               our allgather kernel on the symmetric weight tensor
+The weights stay sharded between the reduce-scatter and the allgather, exactly the shape the
+reference gets from reduceScatterArray + allgatherArray (PCS:1174, 620). X is kept twice, row-major
+for the forward pass and feature-major (Xt) for the gradient, so both GEMMs are K-major.
+
+Sparse variant (`SparseLR`): hashed features, gradient as a sparse map reduced with allreduce_map.
+"""
+import torch
+
+from .. import Operands, Operators
+from .. import _native as N
+
+
+class DenseLR:
+    def __init__(self, comm, n_features, n_classes, lr=0.1, dtype=torch.bfloat16):
+        self.comm = comm
+        self.p, self.r = comm.getSlaveNum(), comm.getRank()
+        self.F, self.C, self.lr = n_features, n_classes, lr
+        self.plane = comm.init_gpu()
+        self.fpr = (n_features + self.p - 1) // self.p
+        # full weights live in the symmetric heap so the allgather is zero-copy
+        self.W = comm.empty(self.fpr * self.p * n_classes, Operands.FLOAT_OPERAND()).view(self.fpr * self.p, n_classes)
+        self.W.zero_()
+        self.dtype = dtype
+
+    def set_data(self, X, y):
+        """X: [rows, F] float tensor on this rank's GPU, y: [rows] int64 labels."""
+        rows = X.shape[0]
+        pad = (-rows) % 8  # TMA row pitch of Xt must be a multiple of 16 bytes
+        if pad:
+            X = torch.cat([X, X.new_zeros(pad, X.shape[1])])
+            y = torch.cat([y, y.new_full((pad,), -1)])
+        self.X = X.to(self.dtype).contiguous()
+        self.Xt = self.X.t().contiguous()
+        self.y = y
+        self.valid = (y >= 0)
+        self.n_local = int(self.valid.sum())
+        self.n_total = self.comm.allreduce(self.n_local, Operands.LONG_OPERAND(), Operators.Long.SUM)
+
+    def step(self):
+        W = self.W[: self.F]
+        logits = (self.X @ W.to(self.dtype)).float()
+        logp = torch.log_softmax(logits, dim=1)
+        probs = logp.exp()
+        onehot = torch.zeros_like(probs)
+        idx = self.y.clamp(min=0)
+        onehot.scatter_(1, idx[:, None], 1.0)
+        R = (probs - onehot) * self.valid[:, None]
+        loss_local = -(logp.gather(1, idx[:, None])[:, 0] * self.valid).sum()
+        Rt = R.t().contiguous().to(self.dtype)
+        shard, fpr = self.plane.lr_xtr_reduce_scatter(self.Xt, Rt)     # fused GEMM + reduce-scatter
+        lo = self.r * fpr
+        self.W[lo:lo + fpr].add_(shard, alpha=-self.lr / self.n_total)  # sharded update
+        flat = self.W.view(-1)
+        froms = [q * fpr * self.C for q in range(self.p)]
+        tos = [(q + 1) * fpr * self.C for q in range(self.p)]
+        self.comm.allgatherArray(flat, Operands.FLOAT_OPERAND(), froms, tos)
+        return loss_local
+
+    def loss(self, loss_local):
+        total = self.comm.allreduce(float(loss_local), Operands.DOUBLE_OPERAND(), Operators.Double.SUM)
+        return total / self.n_total
+
+
+class SparseLR:
+    """Binary LR over hashed sparse features: the gradient of a minibatch touches few of the
+    n_features weights, so it travels as a sparse map (keys = feature ids) through allreduce_map
+    (the GPU form of the reference's allreduceMap, PCS:2053)."""
+
+    def __init__(self, comm, n_features, lr=0.1):
+        self.comm, self.lr, self.F = comm, lr, n_features
+        self.plane = comm.init_gpu()
+        self.w = torch.zeros(n_features, device="cuda")
+
+    def step(self, rows, cols, vals, y):
+        """COO minibatch: rows/cols int64, vals float32, y float32 in {0,1} of length n_rows."""
+        n = y.numel()
+        z = torch.zeros(n, device="cuda").index_add_(0, rows, vals * self.w[cols])
+        r = torch.sigmoid(z) - y
+        g_vals = vals * r[rows]
+        keys, g = self.plane.map_reduce_local(cols, g_vals, N.SUM)       # local pre-aggregation by feature
+        keys, g = self.plane.allreduce_map(keys, g, Operators.Float.SUM)  # sparse allreduce over ranks
+        n_total = self.comm.allreduce(n, Operands.LONG_OPERAND(), Operators.Long.SUM)
+        self.w.index_add_(0, keys, g, alpha=-self.lr / n_total)
+        return torch.nn.functional.binary_cross_entropy_with_logits(z, y, reduction="sum")
