@@ -180,6 +180,20 @@ int mp4j_gpu_lr_xtr_reduce_scatter(mp4j_gpu* g, const void* const* xt, const voi
   MP4J_API_END
 }
 
+int mp4j_gpu_gbdt_hist_reduce_scatter(mp4j_gpu* g, const uint8_t* const* bins, const int64_t* pitch,
+                                      const float* const* grad, const float* const* hess, const int64_t* rows, int F,
+                                      float** shard_out, int* feats_per_rank, void* stream) {
+  MP4J_API_BEGIN
+  const int L = g->g->emulated() ? g->g->world() : 1;
+  long long pp[MP4J_MAX_RANKS], rr[MP4J_MAX_RANKS];
+  for (int i = 0; i < L; ++i) {
+    pp[i] = pitch[i];
+    rr[i] = rows[i];
+  }
+  g->g->gbdt_hist_reduce_scatter(bins, pp, grad, hess, rr, F, shard_out, feats_per_rank, (cudaStream_t)stream);
+  MP4J_API_END
+}
+
 int mp4j_gpu_map_reduce_local(mp4j_gpu* g, int local_rank, const int64_t* keys, const void* vals, int64_t n,
                               int dtype, int op, int64_t* out_keys, void* out_vals, int64_t out_cap,
                               uint64_t* out_count, void* stream) {

@@ -94,6 +94,13 @@ class GpuPlane {
   void lr_xtr_reduce_scatter(const void* const* xt, const void* const* rt, int F, int C, long long K,
                              float** shard_out, int* feats_per_rank_out, cudaStream_t s);
 
+  // K13: GBDT histogram build fused with the reduce-scatter. bins: feature-major uint8 [F][pitch]
+  // (256 bins), grad/hess fp32 [rows]; one pointer per local rank. shard_out[i] = this rank's
+  // [fpr][256][2] fp32 (grad, hess) histogram shard of features [rank*fpr, ...), summed over ranks.
+  void gbdt_hist_reduce_scatter(const uint8_t* const* bins, const long long* pitch, const float* const* grad,
+                                const float* const* hess, const long long* rows, int F, float** shard_out,
+                                int* feats_per_rank_out, cudaStream_t s);
+
   // Local reduce-by-key (the thread-level map merge of DOP:458-477 on device arrays, also usable
   // as pre-aggregation): out = unique keys of (keys, vals) with equal keys reduced by `op`.
   // *out_count (device u64) receives the number of unique keys (clamped to out_cap). The hash
@@ -133,6 +140,7 @@ class GpuPlane {
   std::map<size_t, size_t> used_;  // off -> bytes
   CollStat last_;
   size_t lr_shard_off_ = 0, lr_shard_bytes_ = 0;
+  size_t hist_shard_off_ = 0, hist_shard_bytes_ = 0;
   struct MapWork;
   MapWork* map_ = nullptr;
   void map_release();

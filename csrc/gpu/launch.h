@@ -28,6 +28,11 @@ int thread_ws_max_blocks();
 
 }  // namespace mp4j
 
+namespace mp4j {
+// lr_gemm.cu: one-block cross-rank barrier enqueued on a stream (between the phases of K12 / K13)
+void launch_peer_barrier(const PeerTable& tab, cudaStream_t s);
+}  // namespace mp4j
+
 #include "map_kernels.cuh"
 
 namespace mp4j {

@@ -249,6 +249,16 @@ __global__ void lr_peer_barrier_kernel(PeerTable tab) {
   if (threadIdx.x == 0) *(volatile uint32_t*)eslot = e;
 }
 
+}  // namespace
+
+// shared by the fused consumers (K12, K13): one-block cross-rank barrier on the stream
+void launch_peer_barrier(const PeerTable& tab, cudaStream_t s) {
+  lr_peer_barrier_kernel<<<dim3(1, tab.emulate ? tab.world : 1), 32, 0, s>>>(tab);
+  MP4J_CUDA(cudaGetLastError());
+}
+
+namespace {
+
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);

@@ -75,6 +75,16 @@ int mp4j_gpu_map_collective(mp4j_gpu* g, int mode, const int64_t* const* keys, c
 int mp4j_gpu_lr_xtr_reduce_scatter(mp4j_gpu* g, const void* const* xt, const void* const* rt, int F, int C, int64_t K,
                                    float** shard_out, int* feats_per_rank, void* stream);
 
+/* GBDT histogram build fused with its reduce-scatter (consumer of reduceScatterArray in ytk-learn's
+ * GBDT, reference README.md:278). bins: feature-major uint8 [F][pitch] (256 bins per feature, pitch
+ * >= rows and a multiple of 16, base 16-byte aligned), grad/hess: fp32 [rows]. Every CTA adds its
+ * shared-memory partial histograms straight into the owner rank's shard over NVLink. shard_out[i]
+ * receives this rank's [feats_per_rank][256][2] fp32 (sum grad, sum hess) shard, summed over all
+ * ranks (plane-owned, valid until the next call). One pointer / size per LOCAL rank. */
+int mp4j_gpu_gbdt_hist_reduce_scatter(mp4j_gpu* g, const uint8_t* const* bins, const int64_t* pitch,
+                                      const float* const* grad, const float* const* hess, const int64_t* rows, int F,
+                                      float** shard_out, int* feats_per_rank, void* stream);
+
 /* Local reduce-by-key on one GPU: the thread-level map merge (DOP:458-477) on device arrays.
  * out_keys/out_vals (capacity out_cap pairs) receive the unique keys with equal keys reduced by
  * `op` (SUM/MAX/MIN; float/double/int/long values), *out_count (device uint64) their number.

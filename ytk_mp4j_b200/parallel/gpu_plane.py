@@ -49,6 +49,9 @@ _P("mp4j_gpu_map_reduce_local", C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_vo
 _P("mp4j_gpu_lr_xtr_reduce_scatter", C.c_int, C.c_void_p, N.c_vpp, N.c_vpp, C.c_int, C.c_int, C.c_int64, N.c_vpp,
    C.POINTER(C.c_int), C.c_void_p)
 
+_P("mp4j_gpu_gbdt_hist_reduce_scatter", C.c_int, C.c_void_p, N.c_vpp, N.c_i64p, N.c_vpp, N.c_vpp, N.c_i64p, C.c_int,
+   N.c_vpp, C.POINTER(C.c_int), C.c_void_p)
+
 MAP_MODES = {"allreduce": 0, "reduce_scatter": 1, "allgather": 2}
 MAP_PARTITIONS = {"mix": 0, "java32": 1}
 
@@ -196,6 +199,27 @@ class _PlaneBase:
             out.append(t.view(fpr.value, Cc))
         return out, fpr.value
 
+    def _gbdt_hist_reduce_scatter(self, bins, grads, hesss, stream=None):
+        """bins[i]: uint8 [F, pitch] feature-major, grads/hesss[i]: fp32 [rows] (one set per local rank).
+        Returns per local rank the [fpr, 256, 2] fp32 histogram shard (plane memory) and fpr."""
+        F = bins[0].shape[0]
+        for b, g, h in zip(bins, grads, hesss):
+            if b.dtype != torch.uint8 or b.dim() != 2 or b.stride(1) != 1 or b.shape[0] != F:
+                raise Mp4jException("gbdt_hist: bins must be uint8 [F, rows] with unit stride along rows")
+            if g.dtype != torch.float32 or h.dtype != torch.float32 or g.numel() != h.numel():
+                raise Mp4jException("gbdt_hist: grad/hess must be fp32 of equal length")
+        L = len(bins)
+        shards = (C.c_void_p * L)()
+        fpr = C.c_int(0)
+        check(N.lib.mp4j_gpu_gbdt_hist_reduce_scatter(
+            self._g, _ptr_array(bins), N.i64_array([b.stride(0) for b in bins]), _ptr_array(grads), _ptr_array(hesss),
+            N.i64_array([g.numel() for g in grads]), int(F), shards, C.byref(fpr), _stream_ptr(stream)))
+        out = []
+        for i in range(L):
+            t = torch.as_tensor(_RawCuda(shards[i], fpr.value * 512, N.F32, self), device="cuda:%d" % self.device)
+            out.append(t.view(fpr.value, 256, 2))
+        return out, fpr.value
+
     def map_reduce_local(self, keys, vals, op=N.SUM, local_rank=0, stream=None):
         """Reduce-by-key on one GPU (thread-level map merge, DOP:458-477): concatenate the maps of
         the threads of a process into (keys, vals) and get back unique keys with reduced values."""
@@ -305,6 +329,12 @@ class GpuPlane(_PlaneBase):
         shards, fpr = self._lr_xtr_reduce_scatter([xt], [rt], stream)
         return shards[0], fpr
 
+    def gbdt_hist_reduce_scatter(self, bins_t, grad, hess, stream=None):
+        """Fused GBDT histogram + reduce-scatter (K13): this rank's [fpr, 256, 2] (sum grad, sum hess)
+        shard over features [rank*fpr, ...), summed over all ranks, and fpr."""
+        shards, fpr = self._gbdt_hist_reduce_scatter([bins_t], [grad], [hess], stream)
+        return shards[0], fpr
+
     # --- sparse maps on (int64 keys, values) tensors
     def _map_sizes(self, n, out_cap):
         from ..operands import Operands
@@ -405,6 +435,9 @@ class EmuPlane(_PlaneBase):
 
     def lr_xtr_reduce_scatter(self, xts, rts, stream=None):
         return self._lr_xtr_reduce_scatter(xts, rts, stream)
+
+    def gbdt_hist_reduce_scatter(self, bins, grads, hesss, stream=None):
+        return self._gbdt_hist_reduce_scatter(bins, grads, hesss, stream)
 
     def map_collective(self, mode, keys, vals, op=N.SUM, out_cap=None, partition="mix", stream=None):
         """keys/vals: one tensor per emulated rank. Returns [(keys, vals, owned)] per rank."""
