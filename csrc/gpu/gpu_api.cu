@@ -116,6 +116,11 @@ int mp4j_gpu_allreduce(mp4j_gpu* g, void* const* arrs, int dtype, int op, int64_
   g->g->allreduce(arrs, dtype, op, from, to, algo, (cudaStream_t)stream);
   MP4J_API_END
 }
+int mp4j_gpu_allreduce_wire(mp4j_gpu* g, void* const* arrs, int64_t from, int64_t to, int wire, void* stream) {
+  MP4J_API_BEGIN
+  g->g->allreduce_wire((float* const*)arrs, from, to, wire, (cudaStream_t)stream);
+  MP4J_API_END
+}
 int mp4j_gpu_reduce_scatter(mp4j_gpu* g, void* const* arrs, int dtype, int op, int64_t from,
                             const int64_t* counts, int algo, void* stream) {
   MP4J_API_BEGIN

@@ -73,6 +73,8 @@ class GpuPlane {
   // local_only: skip the inter-GPU step (intra-process thread reduce, DOP:441-457).
   void thread_allreduce(void* const* bufs, int T, int dtype, int op, int64_t from, int64_t to, int fanout, int dst,
                         bool local_only, int algo, cudaStream_t s);
+  // K8: fp32 SUM allreduce whose payload crosses NVLink as bf16 or block-scaled fp8 (lossy, opt-in).
+  void allreduce_wire(float* const* arrs, int64_t from, int64_t to, int wire, cudaStream_t s);
   // Raises if a kernel reported a peer-wait timeout since the last check.
   void check_error();
 

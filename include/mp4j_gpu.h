@@ -45,6 +45,11 @@ int mp4j_gpu_scatter(mp4j_gpu* g, void* const* arrs, int dtype, const int64_t* f
                      int root, void* stream);                                            /* PCS:900 */
 int mp4j_gpu_reduce(mp4j_gpu* g, void* const* arrs, int dtype, int op, int64_t from, int64_t to, int root,
                     int algo, void* stream);                                             /* PCS:1390 */
+/* fp32 SUM allreduce with a compressed wire format (mp4j_wire: BF16 or block-scaled FP8), fp32
+ * accumulation. The GPU-side replacement of the reference's Deflate `compress` flag (DOP:267-269);
+ * lossy, therefore never chosen implicitly. All ranks end with bit-identical results. */
+int mp4j_gpu_allreduce_wire(mp4j_gpu* g, void* const* arrs, int64_t from, int64_t to, int wire, void* stream);
+
 /* ThreadCommSlave.allreduceArray on device buffers (TCS:1915): bufs[local_rank * T + t].
  * fanout = 1 writes the result to all T buffers, 0 only to thread `dst`; local_only = 1 skips the
  * inter-GPU step (the thread-level reduce of TCS:259-303 alone). thread_algo: 0 register, 1

@@ -52,6 +52,8 @@ _P("mp4j_gpu_lr_xtr_reduce_scatter", C.c_int, C.c_void_p, N.c_vpp, N.c_vpp, C.c_
 _P("mp4j_gpu_gbdt_hist_reduce_scatter", C.c_int, C.c_void_p, N.c_vpp, N.c_i64p, N.c_vpp, N.c_vpp, N.c_i64p, C.c_int,
    N.c_vpp, C.POINTER(C.c_int), C.c_void_p)
 
+_P("mp4j_gpu_allreduce_wire", C.c_int, C.c_void_p, N.c_vpp, C.c_int64, C.c_int64, C.c_int, C.c_void_p)
+
 MAP_MODES = {"allreduce": 0, "reduce_scatter": 1, "allgather": 2}
 MAP_PARTITIONS = {"mix": 0, "java32": 1}
 
@@ -150,6 +152,9 @@ class _PlaneBase:
     # raw collectives on lists of tensors (one per local rank)
     def _allreduce(self, ts, code, op, f, t, algo, stream):
         check(N.lib.mp4j_gpu_allreduce(self._g, _ptr_array(ts), code, op, f, t, algo, _stream_ptr(stream)))
+
+    def _allreduce_wire(self, ts, f, t, wire, stream):
+        check(N.lib.mp4j_gpu_allreduce_wire(self._g, _ptr_array(ts), f, t, wire, _stream_ptr(stream)))
 
     def _reduce_scatter(self, ts, code, op, f, counts, algo, stream):
         check(N.lib.mp4j_gpu_reduce_scatter(self._g, _ptr_array(ts), code, op, f, N.i64_array(counts), algo,
@@ -297,6 +302,11 @@ class GpuPlane(_PlaneBase):
     # --- ProcessCommSlave dispatch targets
     def allreduce(self, t, operand, operator, f, to, algo=N.ALGO_AUTO, stream=None):
         _check_tensor(t)
+        if (operand.wire != N.WIRE_LOSSLESS and operand.code == N.F32 and _native_op(operator) == N.SUM
+                and (t.data_ptr() + 4 * f) % 16 == 0):
+            # opt-in lossy wire format (Operands.FLOAT_OPERAND(wire="bf16"|"fp8")): K8
+            self._allreduce_wire([t], f, to, operand.wire, stream)
+            return
         self._allreduce([t], _code_of(t, operand), _native_op(operator), f, to, algo, stream)
 
     def reduce_scatter(self, t, operand, operator, f, counts, algo=N.ALGO_AUTO, stream=None):
@@ -414,6 +424,9 @@ class EmuPlane(_PlaneBase):
 
     def allreduce(self, ts, op, f, t, algo=N.ALGO_AUTO, stream=None):
         self._allreduce(ts, _code_of(ts[0]), op, f, t, algo, stream)
+
+    def allreduce_wire(self, ts, f, t, wire, stream=None):
+        self._allreduce_wire(ts, f, t, wire, stream)
 
     def reduce_scatter(self, ts, op, f, counts, algo=N.ALGO_AUTO, stream=None):
         self._reduce_scatter(ts, _code_of(ts[0]), op, f, counts, algo, stream)
