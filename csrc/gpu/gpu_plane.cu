@@ -63,7 +63,8 @@ void GpuPlane::finish_init(GpuOptions opt) {
   err_dev_ = (uint32_t*)d;
   // heap layout
   size_t off = kSigPadBytes;
-  const size_t one = align_up(opt_.oneshot_max_bytes + 256, 256);
+  oneshot_slot_bytes_ = std::max<size_t>(opt_.oneshot_max_bytes, 256u << 10);  // capacity is not the AUTO threshold
+  const size_t one = align_up(oneshot_slot_bytes_ + 256, 256);
   oneshot_off_[0] = off;
   oneshot_off_[1] = off + one;
   off += 2 * one;
@@ -259,7 +260,7 @@ void GpuPlane::allreduce(void* const* arrs, int dtype, int op, int64_t from, int
   if (!op_valid_for(dtype, op) || op == MP4J_COPY) throw Error("operator is not defined for this dtype");
   const unsigned full = (1u << p) - 1u;
   const bool oneshot = algo == MP4J_ALGO_ONESHOT || (algo == MP4J_ALGO_AUTO && bytes <= opt_.oneshot_max_bytes);
-  if (oneshot && bytes <= opt_.oneshot_max_bytes) {
+  if (oneshot && bytes <= oneshot_slot_bytes_) {
     // every rank copies its input into a double-buffered symmetric slot, then reads all p slots
     GrsArgs a{};
     a.tab = table();

@@ -133,6 +133,7 @@ class GpuPlane {
   uint32_t* err_dev_ = nullptr;
   // heap layout (byte offsets)
   size_t oneshot_off_[2] = {0, 0};
+  size_t oneshot_slot_bytes_ = 0;
   int oneshot_next_ = 0;
   size_t thread_off_ = 0, thread_bytes_ = 0;
   size_t staging_off_ = 0;

@@ -69,6 +69,23 @@ _ES = {N.F64: 8, N.F32: 4, N.I64: 8, N.I32: 4, N.I16: 2, N.I8: 1, N.BF16: 2, N.F
 THREAD_ALGO = {"auto": 0, "cluster": 1, "register": 3}
 
 
+def _apply_tuning_table(world):
+    """K0, runtime half: AUTO's thresholds come from the measured table tuning/b200_p<world>.json
+    (written by tools/make_tuning.py from a bench/sweep.py run). Explicit environment variables win."""
+    import json
+    path = os.environ.get("MP4J_TUNE_FILE") or os.path.join(
+        os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))), "tuning", "b200_p%d.json" % world)
+    try:
+        table = json.load(open(path))
+    except Exception:
+        return None
+    for key, env in (("oneshot_max_bytes", "MP4J_ONE_SHOT_MAX_BYTES"), ("nvls_min_bytes", "MP4J_NVLS_MIN_BYTES"),
+                     ("nvls_min_world", "MP4J_NVLS_MIN_WORLD")):
+        if key in table and env not in os.environ:
+            os.environ[env] = str(int(min(table[key], 1 << 62)))
+    return table
+
+
 class _RawCuda:
     """Minimal __cuda_array_interface__ carrier so torch can wrap symmetric-heap memory."""
 
@@ -285,6 +302,7 @@ class GpuPlane(_PlaneBase):
         torch.cuda.init()
         self._comm = comm
         self._g = C.c_void_p()
+        self.tuning = _apply_tuning_table(comm.getSlaveNum())
         check(N.lib.mp4j_gpu_init(comm._h, self.device, int(heap_bytes or 0), int(staging_bytes or 0),
                                   C.byref(self._g)))
         self.thread_algo = THREAD_ALGO[os.environ.get("MP4J_THREAD_ALGO", "auto")]
