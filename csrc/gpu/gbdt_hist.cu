@@ -35,10 +35,41 @@ struct HistArgs {
   long long pitch[kMaxRanks];   // bytes between features in bins (>= rows, multiple of 16)
   int F, fpr;
   long long rows_per_split;     // multiple of 16
+  const float* amax[kMaxRanks]; // device float[2]: max |grad|, max |hess| of this rank's rows
 };
 
+// max |x| of grad and hess (non-negative floats order like their bit patterns)
+__global__ void gbdt_amax_kernel(const float* grad, const float* hess, long long n, float* out) {
+  float mg = 0.f, mh = 0.f;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    mg = fmaxf(mg, fabsf(grad[i]));
+    mh = fmaxf(mh, fabsf(hess[i]));
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    mg = fmaxf(mg, __shfl_xor_sync(0xffffffffu, mg, o));
+    mh = fmaxf(mh, __shfl_xor_sync(0xffffffffu, mh, o));
+  }
+  if ((threadIdx.x & 31) == 0) {
+    atomicMax((unsigned*)&out[0], __float_as_uint(mg));
+    atomicMax((unsigned*)&out[1], __float_as_uint(mh));
+  }
+}
+
+// power-of-two quantisation step such that rows_per_split values of magnitude amax cannot overflow
+// an int32 partial sum; integers (and dyadic fractions) above the step are represented exactly
+__device__ __forceinline__ float quant_step(float amax, long long rows_per_split) {
+  if (!(amax > 0.f)) return 1.f;
+  const float qmax = 2147483000.f / (float)rows_per_split;
+  return exp2f(ceilf(log2f(amax / qmax)));
+}
+
 __global__ void __launch_bounds__(kHistThreads) gbdt_hist_rs_kernel(const __grid_constant__ HistArgs a) {
-  __shared__ float2 hist[kFB][kBins];
+  // Partial histograms are accumulated as fixed-point int32: shared-memory integer atomics are
+  // native (ATOMS.ADD) while float ones compile to a CAS spin loop (ATOMS.CAST.SPIN), which made the
+  // first version 4x slower (profiles/README.md §5). Sums of the quantised values are exact, so the
+  // result does not depend on the order of the atomics.
+  __shared__ int2 hist[kFB][kBins];
   const PeerTable& tab = a.tab;
   const int rank = tab.emulate ? (int)blockIdx.z : tab.rank;
   const int row = tab.emulate ? rank : 0;
@@ -46,12 +77,14 @@ __global__ void __launch_bounds__(kHistThreads) gbdt_hist_rs_kernel(const __grid
   const long long rows = a.rows[row];
   const long long r0 = (long long)blockIdx.y * a.rows_per_split;
   const long long r1 = min(rows, r0 + a.rows_per_split);
-  for (int i = threadIdx.x; i < kFB * kBins; i += blockDim.x) ((float2*)hist)[i] = make_float2(0.f, 0.f);
+  for (int i = threadIdx.x; i < kFB * kBins; i += blockDim.x) ((int2*)hist)[i] = make_int2(0, 0);
   __syncthreads();
   const uint8_t* bins = a.bins[row];
   const float* grad = a.grad[row];
   const float* hess = a.hess[row];
   const long long pitch = a.pitch[row];
+  const float step_g = quant_step(a.amax[row][0], a.rows_per_split), step_h = quant_step(a.amax[row][1], a.rows_per_split);
+  const float inv_g = 1.f / step_g, inv_h = 1.f / step_h;
   for (long long i = r0 + (long long)threadIdx.x * 16; i < r1; i += (long long)blockDim.x * 16) {
     float g[16], h[16];
     if (i + 16 <= rows) {
@@ -70,6 +103,12 @@ __global__ void __launch_bounds__(kHistThreads) gbdt_hist_rs_kernel(const __grid
       }
     }
     const int nvalid = (int)min(16ll, r1 - i);
+    int qg[16], qh[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      qg[j] = __float2int_rn(g[j] * inv_g);
+      qh[j] = __float2int_rn(h[j] * inv_h);
+    }
 #pragma unroll
     for (int ff = 0; ff < kFB; ++ff) {
       if (f0 + ff >= a.F) break;
@@ -80,8 +119,8 @@ __global__ void __launch_bounds__(kHistThreads) gbdt_hist_rs_kernel(const __grid
       for (int j = 0; j < 16; ++j) {
         if (j < nvalid) {
           const int b = (w[j >> 2] >> ((j & 3) * 8)) & 0xff;
-          atomicAdd(&hist[ff][b].x, g[j]);
-          atomicAdd(&hist[ff][b].y, h[j]);
+          atomicAdd(&hist[ff][b].x, qg[j]);
+          atomicAdd(&hist[ff][b].y, qh[j]);
         }
       }
     }
@@ -92,8 +131,9 @@ __global__ void __launch_bounds__(kHistThreads) gbdt_hist_rs_kernel(const __grid
     const int ff = i / kBins, b = i % kBins;
     const int f = f0 + ff;
     if (f >= a.F) break;
-    const float2 v = hist[ff][b];
-    if (v.x == 0.f && v.y == 0.f) continue;
+    const int2 q = hist[ff][b];
+    if (q.x == 0 && q.y == 0) continue;
+    const float2 v = make_float2((float)q.x * step_g, (float)q.y * step_h);
     const int owner = min(f / a.fpr, tab.world - 1);
     float* dst = (float*)(tab.heap[owner] + a.out_off) + ((size_t)(f - owner * a.fpr) * kBins + b) * 2;
     asm volatile("red.relaxed.sys.global.add.v2.f32 [%0], {%1, %2};" ::"l"(dst), "f"(v.x), "f"(v.y) : "memory");
@@ -141,6 +181,13 @@ void GpuPlane::gbdt_hist_reduce_scatter(const uint8_t* const* bins, const long l
   rps = std::max<long long>(16, (rps + 15) / 16 * 16);
   splits = std::max<long long>(1, (max_rows + rps - 1) / rps);
   a.rows_per_split = rps;
+  for (int i = 0; i < L; ++i) {  // quantisation range of this call's gradients
+    if (!hist_amax_[i]) MP4J_CUDA(cudaMalloc(&hist_amax_[i], 64));
+    MP4J_CUDA(cudaMemsetAsync(hist_amax_[i], 0, 8, s));
+    if (rows[i] > 0) gbdt_amax_kernel<<<std::max(1, std::min(sms_ * 2, (int)((rows[i] + 255) / 256))), 256, 0, s>>>(
+        grad[i], hess[i], rows[i], hist_amax_[i]);
+    a.amax[i] = hist_amax_[i];
+  }
   for (int i = 0; i < L; ++i) {
     const int r = emulated() ? i : rank();
     MP4J_CUDA(cudaMemsetAsync(heap_.base(r) + hist_shard_off_, 0, shard_bytes, s));

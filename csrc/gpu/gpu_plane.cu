@@ -86,6 +86,8 @@ void GpuPlane::finish_init(GpuOptions opt) {
 GpuPlane::~GpuPlane() {
   cudaDeviceSynchronize();
   map_release();
+  for (float* a : hist_amax_)
+    if (a) cudaFree(a);
   if (err_host_) cudaFreeHost(err_host_);
 }
 

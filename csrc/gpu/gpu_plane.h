@@ -144,6 +144,7 @@ class GpuPlane {
   CollStat last_;
   size_t lr_shard_off_ = 0, lr_shard_bytes_ = 0;
   size_t hist_shard_off_ = 0, hist_shard_bytes_ = 0;
+  float* hist_amax_[kMaxRanks] = {};
   struct MapWork;
   MapWork* map_ = nullptr;
   void map_release();
