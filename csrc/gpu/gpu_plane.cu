@@ -37,6 +37,7 @@ GpuPlane* GpuPlane::create_real(ProcessComm* pc, int device, GpuOptions opt) {
   std::unique_ptr<GpuPlane> g(new GpuPlane());
   g->device_ = device;
   MP4J_CUDA(cudaSetDevice(device));
+  g->pc_ = pc;
   g->heap_.init_real(pc, device, opt.heap_bytes, opt.want_multicast);
   g->finish_init(opt);
   return g.release();
@@ -81,6 +82,11 @@ void GpuPlane::finish_init(GpuOptions opt) {
   if (user_off_ > heap_.bytes())
     throw Error("symmetric heap too small: need at least " + std::to_string(user_off_) + " bytes for pads+staging, have " +
                 std::to_string(heap_.bytes()));
+}
+
+// all ranks of the communicator meet on the host (master barrier); no-op for emulated planes
+void GpuPlane::host_barrier() {
+  if (pc_) pc_->barrier();
 }
 
 GpuPlane::~GpuPlane() {

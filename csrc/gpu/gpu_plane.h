@@ -127,6 +127,8 @@ class GpuPlane {
   bool offsets_symmetric(void* const* arrs, size_t* off) const;
 
   SymmHeap heap_;
+  ProcessComm* pc_ = nullptr;  // real mode: for the rare host-side barriers (buffer re-creation)
+  void host_barrier();
   GpuOptions opt_;
   int device_ = 0, sms_ = 0;
   uint32_t* err_host_ = nullptr;

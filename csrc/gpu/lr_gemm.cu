@@ -17,13 +17,19 @@
 // splits. Roles per CTA (192 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA
 // issuer, warps 2-5 = epilogue.
 #include <cuda.h>
+#include <cooperative_groups.h>
 #include <cuda_bf16.h>
+
+#include <stdlib.h>
+#include <string.h>
 
 #include <algorithm>
 
 #include "cuda_check.h"
 #include "gpu_plane.h"
 #include "launch.h"
+
+namespace cg = cooperative_groups;
 
 namespace mp4j {
 
@@ -46,6 +52,7 @@ struct LrArgs {
   int k_blocks_per_split;        // 64-element K blocks handled by one CTA
   int tmem_cols;                 // power of two >= max(32, C)
   int stages;                    // smem ring depth (2..kMaxStages)
+  int cluster;                   // CTAs per cluster along split-K (1 = none): partials meet in DSMEM
 };
 
 __device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -212,7 +219,15 @@ __global__ void __launch_bounds__(kGemmThreads, 1) lr_xtr_rs_kernel(const __grid
           : "r"(taddr)
           : "memory");
       asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-      if (f < a.F) {
+      if (a.cluster > 1) {
+        // stash this CTA's partial tile in (now idle) stage memory; the cluster sums it below
+        float* prow = (float*)smem + (size_t)(quarter * 32 + lane) * (a.C + 4) + c0;
+#pragma unroll
+        for (int j = 0; j < 32; j += 4)
+          if (c0 + j < a.C)
+            *(float4*)(prow + j) = make_float4(__uint_as_float(v[j]), __uint_as_float(v[j + 1]),
+                                               __uint_as_float(v[j + 2]), __uint_as_float(v[j + 3]));
+      } else if (f < a.F) {
 #pragma unroll
         for (int j = 0; j < 32; j += 4) {
           if (c0 + j < a.C)
@@ -229,6 +244,44 @@ __global__ void __launch_bounds__(kGemmThreads, 1) lr_xtr_rs_kernel(const __grid
   if (warp == 1) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"((uint32_t)a.tmem_cols)
                  : "memory");
+  }
+  if (a.cluster > 1) {
+    // Split-K partials of one output tile live in the shared memory of the CTAs of one cluster:
+    // CTA j sums row slice j over all of them through DSMEM (fixed order) and sends ONE contribution
+    // per rank to the owner, instead of `splits` remote atomics per element.
+    cg::cluster_group cluster = cg::this_cluster();
+    cluster.sync();
+    const int cs = a.cluster;
+    const int cr = (int)cluster.block_rank();
+    const int rows_per = kTileM / cs;
+    const int c4n = a.C / 4;
+    const int pitch = a.C + 4;
+    const uint32_t base = smem_addr(smem);
+    for (int idx = threadIdx.x; idx < rows_per * c4n; idx += blockDim.x) {
+      const int r = cr * rows_per + idx / c4n;
+      const int c = (idx % c4n) * 4;
+      const uint32_t local = base + (uint32_t)((r * pitch + c) * 4);
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int j = 0; j < cs; ++j) {
+        uint32_t remote;
+        asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local), "r"(j));
+        float4 x;
+        asm volatile("ld.shared::cluster.v4.f32 {%0,%1,%2,%3}, [%4];"
+                     : "=f"(x.x), "=f"(x.y), "=f"(x.z), "=f"(x.w)
+                     : "r"(remote)
+                     : "memory");
+        acc.x += x.x; acc.y += x.y; acc.z += x.z; acc.w += x.w;
+      }
+      const int f = tile_m * kTileM + r;
+      if (f < a.F) {
+        const int owner = min(f / a.feats_per_rank, tab.world - 1);
+        float* dst = (float*)(tab.heap[owner] + a.out_off) + (size_t)(f - owner * a.feats_per_rank) * a.C + c;
+        asm volatile("red.relaxed.sys.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst), "f"(acc.x), "f"(acc.y),
+                     "f"(acc.z), "f"(acc.w)
+                     : "memory");
+      }
+    }
+    cluster.sync();  // nobody leaves while a peer may still read its shared memory
   }
 }
 
@@ -345,6 +398,25 @@ void GpuPlane::lr_xtr_reduce_scatter(const void* const* xt, const void* const* r
   int splits = best_splits;
   a.k_blocks_per_split = (kb_total + splits - 1) / splits;
   splits = (kb_total + a.k_blocks_per_split - 1) / a.k_blocks_per_split;
+  // Optional (MP4J_LR_SPLIT=cluster): put the CTAs of one output tile into one thread-block cluster
+  // (2, 4 or 8 along K) and let them sum their partial tiles through distributed shared memory, so a
+  // tile costs one remote contribution per rank instead of one per split. Measured on B200 it loses
+  // to plain atomics (0.294 vs 0.209 ms at F=8192, C=128, K=65536): gang-scheduling 8-CTA clusters at
+  // one CTA per SM strands SMs and serialises tile completion, so atomics stay the default.
+  a.cluster = 1;
+  const char* mode = getenv("MP4J_LR_SPLIT");
+  if (splits > 1 && mode && strcmp(mode, "cluster") == 0) {
+    for (int cs : {8, 4, 2}) {
+      if (cs > splits + 1 && cs != 2) continue;  // do not split far more than the grid needs
+      const int kps = (kb_total + cs - 1) / cs;
+      if (kps < 1 || (kb_total + kps - 1) / kps != cs) continue;
+      if ((size_t)a.stages * stage_bytes < (size_t)kTileM * (C + 4) * 4) continue;
+      a.cluster = cs;
+      a.k_blocks_per_split = kps;
+      splits = cs;
+      break;
+    }
+  }
   const size_t smem = (size_t)a.stages * stage_bytes + 1024;
   static bool attr_set = false;
   if (!attr_set) {
@@ -360,11 +432,25 @@ void GpuPlane::lr_xtr_reduce_scatter(const void* const* xt, const void* const* r
   *feats_per_rank_out = fpr;
   PeerTable tab = a.tab;
   if (p > 1) lr_peer_barrier_kernel<<<dim3(1, emulated() ? p : 1), 32, 0, s>>>(tab);
-  lr_xtr_rs_kernel<<<dim3(tiles_m, splits, emulated() ? p : 1), kGemmThreads, smem, s>>>(a);
+  {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(tiles_m, splits, emulated() ? p : 1);
+    cfg.blockDim = dim3(kGemmThreads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 1;
+    attr[0].val.clusterDim.y = a.cluster;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    MP4J_CUDA(cudaLaunchKernelEx(&cfg, lr_xtr_rs_kernel, a));
+  }
   MP4J_CUDA(cudaGetLastError());
   if (p > 1) lr_peer_barrier_kernel<<<dim3(1, emulated() ? p : 1), 32, 0, s>>>(tab);
   MP4J_CUDA(cudaGetLastError());
-  last_ = CollStat{"lr_xtr_reduce_scatter", "tcgen05+red.add", (size_t)F * K * 2, tiles_m * splits, false};
+  last_ = CollStat{"lr_xtr_reduce_scatter", a.cluster > 1 ? "tcgen05+dsmem-splitk+red.add" : "tcgen05+red.add", (size_t)F * K * 2, tiles_m * splits, false};
 }
 
 }  // namespace mp4j

@@ -144,8 +144,11 @@ void GpuPlane::map_collective(int mode, const long long* const* keys, const void
       MP4J_CUDA(cudaMemsetAsync(heap_.base(r) + w.ocnt_off, 0, 256, s));
     }
     MP4J_CUDA(cudaStreamSynchronize(s));
-    // every rank re-created its buffers in the same order, so offsets agree; nobody may push into
-    // a peer's old buffers any more: the caller's collective call order guarantees that
+    // Every rank re-created its buffers in the same order, so offsets agree. A peer must not push
+    // pairs or counts into them before this rank's zeroing has completed (it would be wiped out:
+    // found at 8 GPUs x 2M keys, where a fast rank's counts arrived before a slow rank's memset),
+    // so the ranks meet on the host once per (re)allocation.
+    host_barrier();
   }
   // ---- local scratch
   const unsigned long long recv_upper = (unsigned long long)p * (unsigned long long)w.cap;

@@ -28,7 +28,9 @@ def planes():
     (4, 1024, 256, 1024),
     (8, 4096, 16, 8192),
 ])
-def test_lr_xtr_reduce_scatter(planes, world, F, C, K):
+@pytest.mark.parametrize("split", ["atomic", "cluster"])
+def test_lr_xtr_reduce_scatter(planes, world, F, C, K, split, monkeypatch):
+    monkeypatch.setenv("MP4J_LR_SPLIT", split)  # read by the launcher at every call
     plane = planes(world)
     g = torch.Generator().manual_seed(F + C + K)
     xts = [(torch.randn(F, K, generator=g) * 0.5).to(torch.bfloat16) for _ in range(world)]

@@ -67,6 +67,16 @@ def process_gpu(comm):
         assert k.numel() == obj + p
         d = dict(zip(k.tolist(), v.tolist()))
         assert all(d[i] == p for i in range(0, obj, 97)) and all(d[-(q + 1)] == 1 for q in range(p))
+    # larger, randomly overlapping key sets: forces buffer re-creation (the allocation race found at
+    # 8 GPUs) and checks the result against a reference every rank can compute from the seeds
+    big = 300000
+    sets = [torch.randperm(1000000, generator=torch.Generator().manual_seed(100 + q))[:big] for q in range(p)]
+    cnt = torch.zeros(1000000, dtype=torch.float32)
+    for sq in sets:
+        cnt[sq] += 1.0
+    k, v = comm.gpu.allreduce_map(sets[r].to(torch.int64).cuda(), torch.ones(big, device="cuda"), Operators.Float.SUM)
+    assert k.numel() == int((cnt > 0).sum()), (k.numel(), int((cnt > 0).sum()))
+    assert torch.equal(v.cpu(), cnt[k.cpu()])
     k, v = comm.gpu.reduce_scatter_map(keys, vals, Operators.Float.SUM)
     tot = comm.allreduce(int(k.numel()), Operands.LONG_OPERAND(), Operators.Long.SUM)
     assert tot == obj + p
