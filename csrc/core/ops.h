@@ -9,10 +9,11 @@
 //    broken by the LOWER location instead of "first argument wins", which makes the operator
 //    commutative+associative so every rank/reduction order yields the same bits.
 #pragma once
+#ifndef __CUDACC_RTC__
 #include <stdint.h>
 #include <string.h>
-#include <type_traits>
 #include "../../include/mp4j_types.h"
+#endif  // NVRTC (custom device operators, csrc/gpu/custom_op.cu) gets these from a generated prelude
 
 #if defined(__CUDACC__)
 #define MP4J_HD __host__ __device__ __forceinline__
@@ -46,6 +47,10 @@ MP4J_HD int32_t composite_long_val(int64_t c) { return (int32_t)((uint64_t)c >> 
 MP4J_HD int32_t composite_long_loc(int64_t c) { return (int32_t)(uint32_t)(uint64_t)c; }
 
 template <typename T>
+struct bits_of { typedef uint32_t type; };
+template <> struct bits_of<double> { typedef uint64_t type; };
+
+template <typename T>
 struct is_fp { static constexpr bool value = false; };
 template <> struct is_fp<float> { static constexpr bool value = true; };
 template <> struct is_fp<double> { static constexpr bool value = true; };
@@ -56,8 +61,7 @@ MP4J_HD T java_max(T a, T b) {
   if (a != a) return a;
   if (b != b) return b;
   if (a == T(0) && b == T(0)) {  // distinguish signed zeros
-    return (bit_cast<typename std::conditional<sizeof(T) == 8, uint64_t, uint32_t>::type>(a) >>
-            (sizeof(T) * 8 - 1))
+    return (bit_cast<typename bits_of<T>::type>(a) >> (sizeof(T) * 8 - 1))
                ? b
                : a;
   }
@@ -68,8 +72,7 @@ MP4J_HD T java_min(T a, T b) {
   if (a != a) return a;
   if (b != b) return b;
   if (a == T(0) && b == T(0)) {
-    return (bit_cast<typename std::conditional<sizeof(T) == 8, uint64_t, uint32_t>::type>(a) >>
-            (sizeof(T) * 8 - 1))
+    return (bit_cast<typename bits_of<T>::type>(a) >> (sizeof(T) * 8 - 1))
                ? a
                : b;
   }

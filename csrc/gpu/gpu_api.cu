@@ -4,6 +4,7 @@
 #include "../../include/mp4j.h"
 #include "../capi/capi_util.h"
 #include "../host/process_comm.h"
+#include "custom_op.h"
 #include "gpu_plane.h"
 
 using namespace mp4j;
@@ -116,6 +117,20 @@ int mp4j_gpu_allreduce(mp4j_gpu* g, void* const* arrs, int dtype, int op, int64_
   g->g->allreduce(arrs, dtype, op, from, to, algo, (cudaStream_t)stream);
   MP4J_API_END
 }
+int mp4j_gpu_custom_op(mp4j_gpu* g, int dtype, const char* expr, int* op_out) {
+  MP4J_API_BEGIN
+  *op_out = custom_op_register(dtype, expr, g->g->world());
+  MP4J_API_END
+}
+
+int mp4j_rtc_compile(int dtype, const char* expr, int world, long long* cubin_bytes) {
+  MP4J_API_BEGIN
+  size_t n = 0;
+  custom_op_compile_only(dtype, expr, world, &n);
+  if (cubin_bytes) *cubin_bytes = (long long)n;
+  MP4J_API_END
+}
+
 int mp4j_gpu_allreduce_wire(mp4j_gpu* g, void* const* arrs, int64_t from, int64_t to, int wire, void* stream) {
   MP4J_API_BEGIN
   g->g->allreduce_wire((float* const*)arrs, from, to, wire, (cudaStream_t)stream);

@@ -7,6 +7,7 @@
 
 #include "../host/process_comm.h"
 #include "cuda_check.h"
+#include "custom_op.h"
 #include "launch.h"
 
 namespace mp4j {
@@ -17,6 +18,11 @@ size_t env_size(const char* name, size_t dflt) {
   return (v && *v) ? (size_t)strtoull(v, nullptr, 10) : dflt;
 }
 size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+// predefined operators are checked against the dtype table; a custom one against the type it was compiled for
+bool plane_op_ok(int dtype, int op) {
+  if (is_custom_op(op)) return custom_op_dtype(op) == dtype;
+  return op_valid_for(dtype, op);
+}
 }  // namespace
 
 void GpuOptions::load_env() {
@@ -180,7 +186,7 @@ void GpuPlane::run_grs(const char* name, void* const* arrs, int dtype, int op, c
   const int L = local_ranks();
   const size_t es = dtype_size(dtype);
   if (es == 0) throw Error("unknown dtype");
-  if (op != MP4J_COPY && !op_valid_for(dtype, op)) throw Error("operator is not defined for this dtype");
+  if (op != MP4J_COPY && !plane_op_ok(dtype, op)) throw Error("operator is not defined for this dtype");
   // unit conversion: COPY kernels work on bytes
   const long long scale = (op == MP4J_COPY) ? (long long)es : 1;
   const size_t kes = (op == MP4J_COPY) ? 1 : es;
@@ -265,7 +271,7 @@ void GpuPlane::allreduce(void* const* arrs, int dtype, int op, int64_t from, int
   if (p == 1 || from == to) return;
   const size_t es = dtype_size(dtype);
   const size_t bytes = (size_t)(to - from) * es;
-  if (!op_valid_for(dtype, op) || op == MP4J_COPY) throw Error("operator is not defined for this dtype");
+  if (!plane_op_ok(dtype, op) || op == MP4J_COPY) throw Error("operator is not defined for this dtype");
   const unsigned full = (1u << p) - 1u;
   const bool oneshot = algo == MP4J_ALGO_ONESHOT || (algo == MP4J_ALGO_AUTO && bytes <= opt_.oneshot_max_bytes);
   if (oneshot && bytes <= oneshot_slot_bytes_) {
@@ -402,12 +408,32 @@ void GpuPlane::thread_allreduce(void* const* bufs, int T, int dtype, int op, int
   check_from_to(from, to);
   if (T < 1 || T > MP4J_MAX_THREADS) throw Error("thread count out of range");
   if (dst < 0 || dst >= T) throw Error("dst thread out of range");
-  if (!op_valid_for(dtype, op) || op == MP4J_COPY) throw Error("operator is not defined for this dtype");
+  if (!plane_op_ok(dtype, op) || op == MP4J_COPY) throw Error("operator is not defined for this dtype");
   if (from == to) return;
   const size_t es = dtype_size(dtype);
   const size_t nbytes = (size_t)(to - from) * es;
   const int p = local_only ? 1 : world();
   const int L = local_ranks();
+  if (is_custom_op(op)) {
+    // custom operators: thread-id-ordered fold into one buffer per rank (DOP:441-457), the fused
+    // inter-GPU kernel on that buffer, then the fan-out copies (TCS:1915-1963 shape, all on the stream)
+    const int acc = fanout ? 0 : dst;
+    void* accs[kMaxRanks];
+    for (int i = 0; i < L; ++i) {
+      char* a = (char*)bufs[(size_t)i * T + acc] + (size_t)from * es;
+      for (int t = 0; t < T; ++t)
+        if (t != acc) launch_custom_fold(op, a, (const char*)bufs[(size_t)i * T + t] + (size_t)from * es, to - from, sms_, s);
+      accs[i] = bufs[(size_t)i * T + acc];
+    }
+    if (p > 1) allreduce(accs, dtype, op, from, to, algo, s);
+    if (fanout)
+      for (int i = 0; i < L; ++i)
+        for (int t = 1; t < T; ++t)
+          MP4J_CUDA(cudaMemcpyAsync((char*)bufs[(size_t)i * T + t] + (size_t)from * es, (char*)accs[i] + (size_t)from * es,
+                                    nbytes, cudaMemcpyDeviceToDevice, s));
+    last_ = CollStat{"thread_allreduce", "custom-fold+grs", nbytes, 0, false};
+    return;
+  }
   bool vec = (nbytes % 16) == 0;
   for (int i = 0; i < L * T; ++i)
     if ((((uintptr_t)bufs[i] + (size_t)from * es) & 15) != 0) vec = false;

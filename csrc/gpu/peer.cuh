@@ -6,10 +6,12 @@
 // barrier RPC per phase (PCS:391-425, 503, 731, 1153, 1367): kernels load/store peer HBM directly
 // over NVLink and synchronise through signal pads in symmetric memory.
 #pragma once
+#ifndef __CUDACC_RTC__
 #include <cuda_runtime.h>
 #include <stdint.h>
 
 #include "../../include/mp4j_types.h"
+#endif
 #include "../core/ops.h"
 
 namespace mp4j {

@@ -45,6 +45,18 @@ int mp4j_gpu_scatter(mp4j_gpu* g, void* const* arrs, int dtype, const int64_t* f
                      int root, void* stream);                                            /* PCS:900 */
 int mp4j_gpu_reduce(mp4j_gpu* g, void* const* arrs, int dtype, int op, int64_t from, int64_t to, int root,
                     int algo, void* stream);                                             /* PCS:1390 */
+/* Custom device operator: the GPU form of implementing I<T>Operator.apply (J/operator/I*Operator.java:29-30).
+ * `expr` is a C++ expression over `a` (accumulated so far, ascending rank / thread order) and `b` (next
+ * value), both of the element type of `dtype` (one of the six primitive operands); e.g. "a + 2 * b",
+ * "a > b ? a : b", "fmaxf(fabsf(a), fabsf(b))". It is compiled with NVRTC for sm_100a into the same
+ * gather-reduce-scatter kernel as the predefined operators; *op_out (>= MP4J_CUSTOM_OP_BASE) is accepted by
+ * mp4j_gpu_allreduce / _reduce_scatter / _reduce / _thread_allreduce of planes with this world size.
+ * Every rank must register the same expression. Non-commutative expressions are evaluated in ascending
+ * rank order on every rank, so results stay bit-identical everywhere. */
+int mp4j_gpu_custom_op(mp4j_gpu* g, int dtype, const char* expr, int* op_out);
+/* Compile only (needs NVRTC but no GPU): 0 if `expr` compiles for `dtype` at this world size; the
+ * compiler's diagnostics are in mp4j_last_error() otherwise. *cubin_bytes = size of the sm_100a image. */
+int mp4j_rtc_compile(int dtype, const char* expr, int world, long long* cubin_bytes);
 /* fp32 SUM allreduce with a compressed wire format (mp4j_wire: BF16 or block-scaled FP8), fp32
  * accumulation. The GPU-side replacement of the reference's Deflate `compress` flag (DOP:267-269);
  * lossy, therefore never chosen implicitly. All ranks end with bit-identical results. */

@@ -43,6 +43,11 @@ typedef enum mp4j_op {
   MP4J_COPY = 15
 } mp4j_op;
 
+/* Custom device operators (mp4j_gpu_custom_op): run-time codes start here; the kernels see them as
+ * the one template value below. */
+#define MP4J_CUSTOM_OP_BASE 64
+#define MP4J_CUSTOM_OP_TEMPLATE 63
+
 typedef enum mp4j_collective {
   MP4J_GATHER = 0,
   MP4J_SCATTER = 1,

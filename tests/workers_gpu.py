@@ -57,6 +57,15 @@ def process_gpu(comm):
     x = torch.ones(7, dtype=torch.float32, device="cuda")
     comm.allreduceArrayRpc(x, fop, Operators.Float.SUM)
     assert torch.all(x == p)
+    # custom device operator through the public API: NVRTC-compiled into the same fused kernel,
+    # evaluated in ascending rank order on every rank (non-commutative on purpose)
+    halfsum = Operators.device_expr("a * 0.5f + b", host_fn=lambda a, b: a * 0.5 + b)
+    x = torch.full((100003,), float(r + 1), device="cuda")
+    comm.allreduceArray(x, fop, halfsum, 0, 100003)
+    want = 1.0
+    for q in range(1, p):
+        want = want * 0.5 + (q + 1)
+    assert torch.all(x == want), (x[:3], want)
     # sparse map allreduce on tensors: shared keys + one private key per rank
     # (ProcessAllReduceCheck.java:86-116), twice to exercise buffer reuse
     obj = 20000
@@ -105,6 +114,22 @@ def thread_gpu(comm, tid):
         torch.cuda.synchronize()
         total = p * T * (p * T + 1) / 2
         assert torch.all(x == total), (n, x[:4])
+    # custom device operator on the thread path: thread-id-ordered fold, inter-GPU kernel, fan-out
+    halfsum = Operators.device_expr("a * 0.5f + b")
+    x = torch.full((5001,), float(r * T + tid + 1), device="cuda")
+    torch.cuda.synchronize()
+    comm.allreduceArray(x, fop, halfsum, 0, 5001)
+    torch.cuda.synchronize()
+    per_rank = []
+    for q in range(p):
+        acc = float(q * T + 1)
+        for t in range(1, T):
+            acc = acc * 0.5 + (q * T + t + 1)
+        per_rank.append(acc)
+    want = per_rank[0]
+    for q in range(1, p):
+        want = want * 0.5 + per_rank[q]
+    assert torch.all(x == want), (x[:3], want)
     # reduce to (root, rootThread) through the generic thread path on CUDA tensors
     n = 4099
     x = torch.ones(n, device="cuda")

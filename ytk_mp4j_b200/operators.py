@@ -13,11 +13,12 @@ from . import _native as N
 class Operator:
     """A reduction operator. `code` is the native enum or None for custom operators."""
 
-    def __init__(self, name, code=None, fn=None, vectorized=False):
+    def __init__(self, name, code=None, fn=None, vectorized=False, expr=None):
         self.name = name
         self.code = code
         self.fn = fn
         self.vectorized = vectorized
+        self.expr = expr  # C++ expression over a, b: compiled for the GPU path (device_expr)
 
     def apply(self, a, b):
         if self.fn is not None:
@@ -38,6 +39,20 @@ def custom(fn, name="custom", vectorized=False):
     """Custom operator from a Python callable (I<T>Operator.apply). With vectorized=True the
     callable receives whole numpy segments instead of scalars."""
     return Operator(name, None, fn, vectorized)
+
+
+def device_expr(expr, name=None, host_fn=None, vectorized=False):
+    """Custom operator for CUDA tensors: `expr` is a C++ expression over `a` (accumulated so far, in
+    ascending rank / thread order) and `b` (the next value), both of the operand's element type, e.g.
+    "a + 2 * b" or "fabs(a) > fabs(b) ? a : b". It is compiled once per (element type, world size) with
+    NVRTC into the same fused peer-memory kernels as the predefined operators
+    (csrc/gpu/custom_op.cu) - the GPU form of implementing I<T>Operator.apply. `host_fn(a, b)` is the
+    Python equivalent used when the same operator meets numpy arrays / lists on the host path."""
+    def _no_host(a, b):
+        from .exception import Mp4jException
+        raise Mp4jException("operator %r was given as a device expression without host_fn: "
+                            "it only applies to CUDA tensors" % (name or expr))
+    return Operator(name or "expr(%s)" % expr, None, host_fn or _no_host, vectorized, expr)
 
 
 def _maxloc_d(a, b):
@@ -154,3 +169,4 @@ class Operators:
     Short = Short
     Byte = Byte
     custom = staticmethod(custom)
+    device_expr = staticmethod(device_expr)

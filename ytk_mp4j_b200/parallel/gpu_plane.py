@@ -53,6 +53,8 @@ _P("mp4j_gpu_gbdt_hist_reduce_scatter", C.c_int, C.c_void_p, N.c_vpp, N.c_i64p, 
    N.c_vpp, C.POINTER(C.c_int), C.c_void_p)
 
 _P("mp4j_gpu_allreduce_wire", C.c_int, C.c_void_p, N.c_vpp, C.c_int64, C.c_int64, C.c_int, C.c_void_p)
+_P("mp4j_gpu_custom_op", C.c_int, C.c_void_p, C.c_int, C.c_char_p, C.POINTER(C.c_int))
+_P("mp4j_rtc_compile", C.c_int, C.c_int, C.c_char_p, C.c_int, C.POINTER(C.c_longlong))
 
 MAP_MODES = {"allreduce": 0, "reduce_scatter": 1, "allgather": 2}
 MAP_PARTITIONS = {"mix": 0, "java32": 1}
@@ -122,8 +124,8 @@ def _native_op(operator):
     if operator is None:
         return N.COPY
     if not operator.is_native:
-        raise Mp4jException("custom Python operators run on the host path only; "
-                            "move the tensor to the CPU or use a predefined operator")
+        raise Mp4jException("custom Python operators run on the host path only; move the tensor to the CPU, "
+                            "use a predefined operator, or (dense array collectives) Operators.device_expr")
     return operator.code
 
 
@@ -149,6 +151,24 @@ class _PlaneBase:
     @property
     def has_multicast(self):
         return bool(N.lib.mp4j_gpu_has_multicast(self._g))
+
+    def _op(self, operator, code):
+        """Native op code of `operator` for element type `code` on this plane; device expressions
+        (Operators.device_expr) are compiled and loaded on first use."""
+        if operator is not None and operator.code is None and getattr(operator, "expr", None):
+            return self.custom_op(operator.expr, code)
+        return _native_op(operator)
+
+    def custom_op(self, expr, code):
+        """Compiles (NVRTC, sm_100a) and loads the device expression `expr` for element type `code`;
+        returns the op code the dense reducing collectives of this plane accept."""
+        cache = self.__dict__.setdefault("_custom_ops", {})
+        key = (code, expr)
+        if key not in cache:
+            out = C.c_int()
+            check(N.lib.mp4j_gpu_custom_op(self._g, code, expr.encode(), C.byref(out)))
+            cache[key] = out.value
+        return cache[key]
 
     def check(self):
         """Raises if a kernel hit the device-side peer-wait watchdog since the last call."""
@@ -320,16 +340,16 @@ class GpuPlane(_PlaneBase):
     # --- ProcessCommSlave dispatch targets
     def allreduce(self, t, operand, operator, f, to, algo=N.ALGO_AUTO, stream=None):
         _check_tensor(t)
-        if (operand.wire != N.WIRE_LOSSLESS and operand.code == N.F32 and _native_op(operator) == N.SUM
+        if (operand.wire != N.WIRE_LOSSLESS and operand.code == N.F32 and operator.code == N.SUM
                 and (t.data_ptr() + 4 * f) % 16 == 0):
             # opt-in lossy wire format (Operands.FLOAT_OPERAND(wire="bf16"|"fp8")): K8
             self._allreduce_wire([t], f, to, operand.wire, stream)
             return
-        self._allreduce([t], _code_of(t, operand), _native_op(operator), f, to, algo, stream)
+        self._allreduce([t], _code_of(t, operand), self._op(operator, operand.code), f, to, algo, stream)
 
     def reduce_scatter(self, t, operand, operator, f, counts, algo=N.ALGO_AUTO, stream=None):
         _check_tensor(t)
-        self._reduce_scatter([t], _code_of(t, operand), _native_op(operator), f, counts, algo, stream)
+        self._reduce_scatter([t], _code_of(t, operand), self._op(operator, operand.code), f, counts, algo, stream)
 
     def allgather(self, t, operand, froms, tos, algo=N.ALGO_AUTO, stream=None):
         _check_tensor(t)
@@ -349,7 +369,7 @@ class GpuPlane(_PlaneBase):
 
     def reduce(self, t, operand, operator, f, to, root, algo=N.ALGO_AUTO, stream=None):
         _check_tensor(t)
-        self._reduce([t], _code_of(t, operand), _native_op(operator), f, to, root, algo, stream)
+        self._reduce([t], _code_of(t, operand), self._op(operator, operand.code), f, to, root, algo, stream)
 
     def lr_xtr_reduce_scatter(self, xt, rt, stream=None):
         """Fused LR gradient + reduce-scatter (K12): returns this rank's [fpr, C] fp32 shard of
@@ -401,14 +421,14 @@ class GpuPlane(_PlaneBase):
         for t in ts:
             _check_tensor(t)
         local = self.world == 1
-        self._thread_allreduce(ts, len(ts), _code_of(ts[0], operand), _native_op(operator), f, to, True, 0, local,
+        self._thread_allreduce(ts, len(ts), _code_of(ts[0], operand), self._op(operator, operand.code), f, to, True, 0, local,
                                self.thread_algo if local else 0, algo, stream)
 
     def thread_reduce(self, ts, operand, operator, f, to, dst, stream=None):
         """Intra-process reduce of the T buffers into ts[dst] (thread path of DOP:441-457)."""
         for t in ts:
             _check_tensor(t)
-        self._thread_allreduce(ts, len(ts), _code_of(ts[0], operand), _native_op(operator), f, to, False, dst, True,
+        self._thread_allreduce(ts, len(ts), _code_of(ts[0], operand), self._op(operator, operand.code), f, to, False, dst, True,
                                0, N.ALGO_AUTO, stream)
 
 
