@@ -33,6 +33,8 @@ def main():
     ap.add_argument("--out", default=None)
     ap.add_argument("--dtype", default="float", choices=["float", "double"])
     ap.add_argument("--no-nccl", action="store_true")
+    ap.add_argument("--custom", action="store_true",
+                    help="also time allreduce with the NVRTC-compiled custom operator `a + b` (two-shot P2P)")
     a = ap.parse_args()
     rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
     lr = int(os.environ.get("LOCAL_RANK", 0))
@@ -97,6 +99,16 @@ def main():
                         plane.allgather(x, operand, froms, tos, algo=ALGOS[algo])
                 us = timed(ours, size)
                 rows.append({"impl": "ours", "coll": coll, "algo": algo, "bytes": size, "us": round(us, 2),
+                             "algbw_GBps": round(size / us / 1e3, 2), "busbw_GBps": round(size / us / 1e3 * factor, 2),
+                             "picked": plane.last()})
+            if a.custom and coll == "allreduce":
+                cop = Operators.device_expr("a + b")
+
+                def ours_custom(i):
+                    x = pool[i * stride:i * stride + n]
+                    plane.allreduce(x, operand, cop, 0, n, algo=N.ALGO_TWOSHOT if size > (256 << 10) else N.ALGO_AUTO)
+                us = timed(ours_custom, size)
+                rows.append({"impl": "ours", "coll": coll, "algo": "custom", "bytes": size, "us": round(us, 2),
                              "algbw_GBps": round(size / us / 1e3, 2), "busbw_GBps": round(size / us / 1e3 * factor, 2),
                              "picked": plane.last()})
             if not a.no_nccl and world > 1:

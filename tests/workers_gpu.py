@@ -1,4 +1,5 @@
 """GPU worker bodies for tests/test_gpu_multiproc.py (public API end to end on CUDA tensors)."""
+import numpy as np
 import torch
 
 from ytk_mp4j_b200 import CommUtils, Operands, Operators
@@ -62,10 +63,10 @@ def process_gpu(comm):
     halfsum = Operators.device_expr("a * 0.5f + b", host_fn=lambda a, b: a * 0.5 + b)
     x = torch.full((100003,), float(r + 1), device="cuda")
     comm.allreduceArray(x, fop, halfsum, 0, 100003)
-    want = 1.0
+    want = np.float32(1.0)
     for q in range(1, p):
-        want = want * 0.5 + (q + 1)
-    assert torch.all(x == want), (x[:3], want)
+        want = np.float32(want * np.float32(0.5)) + np.float32(q + 1)
+    assert torch.all(x == float(want)), (x[:3], want)
     # sparse map allreduce on tensors: shared keys + one private key per rank
     # (ProcessAllReduceCheck.java:86-116), twice to exercise buffer reuse
     obj = 20000
@@ -122,14 +123,14 @@ def thread_gpu(comm, tid):
     torch.cuda.synchronize()
     per_rank = []
     for q in range(p):
-        acc = float(q * T + 1)
+        acc = np.float32(q * T + 1)
         for t in range(1, T):
-            acc = acc * 0.5 + (q * T + t + 1)
+            acc = np.float32(acc * np.float32(0.5)) + np.float32(q * T + t + 1)
         per_rank.append(acc)
     want = per_rank[0]
     for q in range(1, p):
-        want = want * 0.5 + per_rank[q]
-    assert torch.all(x == want), (x[:3], want)
+        want = np.float32(want * np.float32(0.5)) + per_rank[q]
+    assert torch.all(x == float(want)), (x[:3], want)
     # reduce to (root, rootThread) through the generic thread path on CUDA tensors
     n = 4099
     x = torch.ones(n, device="cuda")
