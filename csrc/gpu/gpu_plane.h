@@ -21,8 +21,11 @@ class ProcessComm;
 struct GpuOptions {
   size_t heap_bytes = 1ull << 30;       // MP4J_HEAP_BYTES
   size_t staging_bytes = 128ull << 20;  // general staging window for non-symmetric tensors
-  size_t thread_slot_bytes = 128 << 10; // per-block slot of the fused thread kernel (MP4J_THREAD_SLOT_BYTES)
-  int thread_slots = 3;                 // ring depth of the warp-specialised kernel (MP4J_THREAD_SLOTS)
+  // fused thread kernel: per-block slot (MP4J_THREAD_SLOT_BYTES) and ring depth (MP4J_THREAD_SLOTS).
+  // Measured (profiles/README.md §1): 64 KiB x 4 is the best trade between pipeline fill/drain and
+  // L2 footprint (small) and per-chunk cross-GPU flag latency (large) at 2 and 8 GPUs.
+  size_t thread_slot_bytes = 64 << 10;
+  int thread_slots = 4;
   size_t oneshot_max_bytes = 256 << 10; // <= : one-shot allreduce (MP4J_ONE_SHOT_MAX_BYTES)
   size_t nvls_min_bytes = 512 << 10;    // >= : NVLS when available (MP4J_NVLS_MIN_BYTES)
   int nvls_min_world = 2;               // AUTO uses NVLS only when world > this (MP4J_NVLS_MIN_WORLD)

@@ -20,13 +20,17 @@ constexpr int kMaxRanks = MP4J_MAX_RANKS;
 constexpr int kMaxBlocks = 1024;                      // flag rows per signal pad
 constexpr size_t kSigFlagsBytes = kMaxBlocks * kMaxRanks * sizeof(uint32_t);
 constexpr size_t kSigEpochOff = kSigFlagsBytes;       // per-block epoch counters (local use only)
-// warp-specialised fused thread kernel: its own chunk counters and two flag arrays (phase A done,
-// phase B done), rows = blocks (<= kWsMaxBlocks), columns = source rank
-constexpr int kWsMaxBlocks = 512;
+// warp-specialised fused thread kernel: its own chunk counters and two flag arrays. FA (phase A of
+// chunk k done): [block][source rank], monotonic in k. FB (phase B done): [block][ring slot][source
+// rank] - phase B of different chunks runs concurrently in different warps and may finish out of order.
+constexpr int kWsMaxBlocks = 256;
+constexpr int kWsMaxSlots = 8;
 constexpr size_t kSigWsEpochOff = kSigEpochOff + 4096;
 constexpr size_t kSigWsFaOff = kSigWsEpochOff + 4096;
 constexpr size_t kSigWsFbOff = kSigWsFaOff + kWsMaxBlocks * kMaxRanks * sizeof(uint32_t);
+constexpr size_t kSigWsEnd = kSigWsFbOff + (size_t)kWsMaxBlocks * kWsMaxSlots * kMaxRanks * sizeof(uint32_t);
 constexpr size_t kSigPadBytes = 128 * 1024;           // everything above, zero-initialised once
+static_assert(kSigWsEnd <= kSigPadBytes, "signal pad layout overflows");
 
 struct PeerTable {
   int world;

@@ -1,19 +1,26 @@
 // Warp-specialised fused ThreadCommSlave allreduce (world > 1): the production path of
 // "T thread buffers per GPU x p GPUs" (TCS:1915-1963 on CUDA tensors).
 //
-// One persistent CTA per SM, three warp groups that run CONCURRENTLY on a ring of staging slots:
+// One persistent CTA per SM, three warp groups plus a signal warp that run CONCURRENTLY on a ring
+// of staging slots:
 //   group A (HBM read)   : slot[k] = reduce_t bufs[t][chunk k]          (256-bit loads, T static)
+//   signal warp          : publishes "A(k) done" to every peer (the system-scope release costs ~us
+//                          under load; keeping it out of group A keeps the HBM read stream running)
 //   group B (NVLink)     : rank r reduces sub-slice r of slot[k] over all peers and pushes it back
-//                          to every peer - multimem.ld_reduce + multimem.st (NVLS) or P2P ld/st
+//                          to every peer - multimem.ld_reduce + multimem.st (NVLS) or P2P ld/st.
+//                          Each WARP owns every WB-th chunk, so WB chunks are in their NVLink round
+//                          trips at once
 //   group C (HBM write)  : bufs[t][chunk k] = slot[k] for all t         (256-bit stores)
 // Dependencies are flags, never a CTA-wide or grid-wide barrier:
 //   A(k) needs C(k - kSlots) done (local shared-memory counter)
 //   B(k) needs A(k) of block b on EVERY rank   (flag array FA in the peers' signal pads)
-//   C(k) needs B(k) of block b on EVERY rank   (flag array FB)
+//   C(k) needs B(k) of block b on EVERY rank   (flag array FB, indexed by ring slot: B finishes out of order)
 // so the HBM read stream, the NVLink exchange and the HBM write stream of different chunks overlap
 // inside every SM, and 1/T of the bytes cross NVLink. The chunk-synchronous kernel in
 // thread_kernels.cu (phases in lock-step) is kept as the generic fallback (odd alignments, other
 // thread counts / operators).
+#include <stdlib.h>
+
 #include <algorithm>
 
 #include "cuda_check.h"
@@ -24,18 +31,24 @@ namespace mp4j {
 
 namespace {
 
-constexpr int kWarpsA = 6, kWarpsB = 4, kWarpsC = 6;
-constexpr int kThreadsA = kWarpsA * 32, kThreadsB = kWarpsB * 32, kThreadsC = kWarpsC * 32;
-constexpr int kWsThreads = kThreadsA + kThreadsB + kThreadsC;  // 512
-constexpr int kMaxSlots = 8;  // ring depth is a launch parameter (ThreadArgs::slots), 2..kMaxSlots
+// warp split of the CTA between the three groups
+template <int WA, int WB, int WC>
+struct Split {
+  static constexpr int kThreadsA = WA * 32, kThreadsB = WB * 32, kThreadsC = WC * 32;
+  static constexpr int kWsThreads = kThreadsA + kThreadsB + kThreadsC + 32;  // + the signal warp
+};
+typedef Split<6, 4, 5> SplitDefault;  // 512 threads with the signal warp
+constexpr int kMaxSlots = kWsMaxSlots;  // ring depth is a launch parameter (ThreadArgs::slots), 2..kMaxSlots
 
 __device__ __forceinline__ void named_bar(int id, int nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
 
-template <typename T, int OP, bool NVLS, int NT>
-__global__ void __launch_bounds__(kWsThreads, 1) thread_fused_ws_kernel(const __grid_constant__ ThreadArgs a) {
+template <typename T, int OP, bool NVLS, int NT, typename SP>
+__global__ void __launch_bounds__(SP::kWsThreads, 1) thread_fused_ws_kernel(const __grid_constant__ ThreadArgs a) {
+  constexpr int kThreadsA = SP::kThreadsA, kThreadsB = SP::kThreadsB, kThreadsC = SP::kThreadsC;
   __shared__ volatile unsigned c_done;  // chunks finished by group C (slot recycling)
+  __shared__ unsigned a_cnt;            // (warp, chunk) pairs finished by group A (consumed by the signal warp)
   const PeerTable& tab = a.tab;
   const int rank = my_rank(tab);
   const int world = tab.world;
@@ -50,21 +63,28 @@ __global__ void __launch_bounds__(kWsThreads, 1) thread_fused_ws_kernel(const __
   const uint32_t base = *(volatile uint32_t*)ws_epoch;
   const int kSlots = a.slots;
   const unsigned long long ring_off = a.stg_off + (unsigned long long)blockIdx.x * kSlots * a.slot_bytes;
-  if (threadIdx.x == 0) c_done = 0;
+  if (threadIdx.x == 0) {
+    c_done = 0;
+    a_cnt = 0;
+  }
   __syncthreads();
 
   const int tid = threadIdx.x;
   if (tid < kThreadsA) {
-    // ================= group A: T-way reduce of the local thread buffers into the slot ring
+    // ================= group A: T-way reduce of the local thread buffers into the slot ring.
+    // The warps free-run (no group barrier): each finishes its share of chunk k, bumps a shared
+    // counter and moves on; publishing the chunk to the peers (a system-scope release, ~us) is the
+    // signal warp's job, so the HBM read stream never waits for a fence.
+    const int lane = tid & 31;
     for (long long k = 0; k < mine; ++k) {
       const long long c = blockIdx.x + k * gridDim.x;
       const long long off = c * ch;
       const int nv = (int)(min(ch, nbytes - off) / 32);
       if (k >= kSlots) {
-        if (tid == 0)
+        if (lane == 0)
           while (c_done < (unsigned)(k - kSlots + 1)) {
           }
-        named_bar(1, kThreadsA);
+        __syncwarp();
       }
       char* slot = tab.heap[rank] + ring_off + (unsigned long long)(k % kSlots) * a.slot_bytes;
       for (int v = tid; v < nv; v += kThreadsA) {
@@ -79,38 +99,58 @@ __global__ void __launch_bounds__(kWsThreads, 1) thread_fused_ws_kernel(const __
         }
         st_keep32(slot + (unsigned long long)v * 32, x[0]);
       }
-      named_bar(1, kThreadsA);  // all of A's stores precede the release below
-      if (tid < world)
-        st_release_sys((uint32_t*)((char*)tab.sig[tid] + kSigWsFaOff) + blockIdx.x * kMaxRanks + rank,
+      __syncwarp();
+      if (lane == 0) {
+        __threadfence_block();  // the warp's slot stores are ordered before the count
+        atomicAdd(&a_cnt, 1u);
+      }
+    }
+  } else if (tid >= kThreadsA + kThreadsB + kThreadsC) {
+    // ================= signal warp: FA(k) to every peer once all A warps finished chunk k
+    const int lane = tid & 31;
+    constexpr unsigned WA = kThreadsA / 32;
+    for (long long k = 0; k < mine; ++k) {
+      if (lane < world) {
+        while (*(volatile unsigned*)&a_cnt < WA * (unsigned)(k + 1)) {
+        }
+        __threadfence_block();
+        st_release_sys((uint32_t*)((char*)tab.sig[lane] + kSigWsFaOff) + blockIdx.x * kMaxRanks + rank,
                        base + (uint32_t)k + 1u);
+      }
     }
   } else if (tid < kThreadsA + kThreadsB) {
-    // ================= group B: inter-GPU reduce-scatter + allgather of the slot over NVLink
-    const int bt = tid - kThreadsA;
-    for (long long k = 0; k < mine; ++k) {
+    // ================= group B: inter-GPU reduce-scatter + allgather of the slot over NVLink.
+    // Every WARP owns the chunks k = warp, warp + WB, ... of this block, so WB chunks are in their
+    // NVLink round trips at once: the per-chunk latency (flag hop + load RTT + store + flag hop, ~10 us)
+    // is hidden by chunk-level parallelism instead of by large chunks, which keeps the ring small
+    // (L2-resident) and the pipeline fill/drain short.
+    constexpr int WB = kThreadsB / 32;
+    const int bw = (tid - kThreadsA) >> 5, lane = tid & 31;
+    for (long long k = bw; k < mine; k += WB) {
       const long long c = blockIdx.x + k * gridDim.x;
       const long long off = c * ch;
       const int nv16 = (int)(min(ch, nbytes - off) / 16);
-      if (bt < world)
-        wait_flag(tab, (uint32_t*)((char*)tab.sig[rank] + kSigWsFaOff) + blockIdx.x * kMaxRanks + bt,
+      if (lane < world)
+        wait_flag(tab, (uint32_t*)((char*)tab.sig[rank] + kSigWsFaOff) + blockIdx.x * kMaxRanks + lane,
                   base + (uint32_t)k + 1u);
-      named_bar(2, kThreadsB);
-      const unsigned long long so = ring_off + (unsigned long long)(k % kSlots) * a.slot_bytes;
+      __syncwarp();
+      const int sl = (int)(k % kSlots);
+      const unsigned long long so = ring_off + (unsigned long long)sl * a.slot_bytes;
       const int lo = (int)((long long)nv16 * rank / world), hi = (int)((long long)nv16 * (rank + 1) / world);
       // An NVLink round trip is ~2-3 us: keep kBatch independent 16-byte requests in flight per
       // thread (the asm volatile accessors are never reordered, so batching is explicit).
       constexpr int kBatch = 8;
-      for (int v0 = lo + bt; v0 < hi; v0 += kThreadsB * kBatch) {
+      for (int v0 = lo + lane; v0 < hi; v0 += 32 * kBatch) {
         Vec16 acc[kBatch];
         if constexpr (NVLS) {
 #pragma unroll
           for (int j = 0; j < kBatch; ++j) {
-            const int v = v0 + j * kThreadsB;
+            const int v = v0 + j * 32;
             if (v < hi) acc[j] = Nvls<T, OP>::ld_reduce(tab.mc_heap + so + (unsigned long long)v * 16);
           }
 #pragma unroll
           for (int j = 0; j < kBatch; ++j) {
-            const int v = v0 + j * kThreadsB;
+            const int v = v0 + j * 32;
             if (v < hi) multimem_st(tab.mc_heap + so + (unsigned long long)v * 16, acc[j]);
           }
         } else {
@@ -118,7 +158,7 @@ __global__ void __launch_bounds__(kWsThreads, 1) thread_fused_ws_kernel(const __
             Vec16 x[kBatch];
 #pragma unroll
             for (int j = 0; j < kBatch; ++j) {
-              const int v = v0 + j * kThreadsB;
+              const int v = v0 + j * 32;
               if (v < hi) x[j] = ld_coherent(tab.heap[q] + so + (unsigned long long)v * 16);
             }
 #pragma unroll
@@ -127,15 +167,16 @@ __global__ void __launch_bounds__(kWsThreads, 1) thread_fused_ws_kernel(const __
           for (int q = 0; q < world; ++q) {
 #pragma unroll
             for (int j = 0; j < kBatch; ++j) {
-              const int v = v0 + j * kThreadsB;
+              const int v = v0 + j * 32;
               if (v < hi) st_stream(tab.heap[q] + so + (unsigned long long)v * 16, acc[j]);
             }
           }
         }
       }
-      named_bar(2, kThreadsB);
-      if (bt < world)
-        st_release_sys((uint32_t*)((char*)tab.sig[bt] + kSigWsFbOff) + blockIdx.x * kMaxRanks + rank,
+      __syncwarp();  // the warp's stores precede the release below
+      if (lane < world)
+        st_release_sys((uint32_t*)((char*)tab.sig[lane] + kSigWsFbOff) +
+                           ((size_t)blockIdx.x * kWsMaxSlots + sl) * kMaxRanks + rank,
                        base + (uint32_t)k + 1u);
     }
   } else {
@@ -146,7 +187,8 @@ __global__ void __launch_bounds__(kWsThreads, 1) thread_fused_ws_kernel(const __
       const long long off = c * ch;
       const int nv = (int)(min(ch, nbytes - off) / 32);
       if (ct < world)
-        wait_flag(tab, (uint32_t*)((char*)tab.sig[rank] + kSigWsFbOff) + blockIdx.x * kMaxRanks + ct,
+        wait_flag(tab, (uint32_t*)((char*)tab.sig[rank] + kSigWsFbOff) +
+                           ((size_t)blockIdx.x * kWsMaxSlots + (int)(k % kSlots)) * kMaxRanks + ct,
                   base + (uint32_t)k + 1u);
       named_bar(3, kThreadsC);
       const char* slot = tab.heap[rank] + ring_off + (unsigned long long)(k % kSlots) * a.slot_bytes;
@@ -168,17 +210,31 @@ __global__ void __launch_bounds__(kWsThreads, 1) thread_fused_ws_kernel(const __
   if (threadIdx.x == 0) *(volatile uint32_t*)ws_epoch = base + (uint32_t)mine;
 }
 
-template <typename T, int OP, bool NVLS, int NT>
-void launch_ws_nt(const ThreadArgs& args, int grid, cudaStream_t stream) {
-  auto kfn = thread_fused_ws_kernel<T, OP, NVLS, NT>;
+template <typename T, int OP, bool NVLS, int NT, typename SP>
+void launch_ws_sp(const ThreadArgs& args, int grid, cudaStream_t stream) {
+  auto kfn = thread_fused_ws_kernel<T, OP, NVLS, NT, SP>;
   if (args.tab.emulate) {
     void* params[] = {(void*)&args};
-    MP4J_CUDA(cudaLaunchCooperativeKernel((const void*)kfn, dim3(grid, args.tab.world), dim3(kWsThreads), params, 0,
-                                          stream));
+    MP4J_CUDA(cudaLaunchCooperativeKernel((const void*)kfn, dim3(grid, args.tab.world), dim3(SP::kWsThreads), params,
+                                          0, stream));
   } else {
-    kfn<<<grid, kWsThreads, 0, stream>>>(args);
+    kfn<<<grid, SP::kWsThreads, 0, stream>>>(args);
     MP4J_CUDA(cudaGetLastError());
   }
+}
+
+template <typename T, int OP, bool NVLS, int NT>
+void launch_ws_nt(const ThreadArgs& args, int grid, cudaStream_t stream) {
+  if constexpr (sizeof(T) == 4 && OP == MP4J_SUM && NT == 8) {  // experiment: alternative warp splits
+    static const int split = getenv("MP4J_WS_SPLIT") ? atoi(getenv("MP4J_WS_SPLIT")) : 0;
+    switch (split) {
+      case 1: return launch_ws_sp<T, OP, NVLS, NT, Split<8, 2, 5>>(args, grid, stream);
+      case 2: return launch_ws_sp<T, OP, NVLS, NT, Split<7, 3, 5>>(args, grid, stream);
+      case 3: return launch_ws_sp<T, OP, NVLS, NT, Split<8, 3, 4>>(args, grid, stream);
+      case 4: return launch_ws_sp<T, OP, NVLS, NT, Split<6, 5, 4>>(args, grid, stream);
+    }
+  }
+  launch_ws_sp<T, OP, NVLS, NT, SplitDefault>(args, grid, stream);
 }
 
 template <typename T, int OP, bool NVLS>
