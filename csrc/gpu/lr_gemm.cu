@@ -53,6 +53,7 @@ struct LrArgs {
   int tmem_cols;                 // power of two >= max(32, C)
   int stages;                    // smem ring depth (2..kMaxStages)
   int cluster;                   // CTAs per cluster along split-K (1 = none): partials meet in DSMEM
+  int mt;                        // 128-row M tiles per CTA (1 or 2) sharing every staged B tile
 };
 
 __device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -125,7 +126,7 @@ __device__ __forceinline__ void umma_commit(uint64_t* bar) {
                : "memory");
 }
 
-__global__ void __launch_bounds__(kGemmThreads, 1) lr_xtr_rs_kernel(const __grid_constant__ LrArgs a) {
+__global__ void __launch_bounds__(kGemmThreads, 2) lr_xtr_rs_kernel(const __grid_constant__ LrArgs a) {
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   __shared__ __align__(8) uint64_t full_bar[kMaxStages], empty_bar[kMaxStages], tmem_full_bar;
   __shared__ uint32_t tmem_base_s;
@@ -138,7 +139,10 @@ __global__ void __launch_bounds__(kGemmThreads, 1) lr_xtr_rs_kernel(const __grid
   const int kb_begin = blockIdx.y * a.k_blocks_per_split;
   const int kb_end = min(kb_total, kb_begin + a.k_blocks_per_split);
   const int nkb = kb_end - kb_begin;  // >= 1 by construction of the grid
-  const uint32_t a_bytes = kTileM * kBlockK * 2, b_bytes = (uint32_t)a.C * kBlockK * 2;
+  // mt M tiles share one staged B tile: B is re-read from L2 by every CTA, so at mt = 1 the
+  // L2 -> SM bytes are twice the DRAM bytes (profiles/README.md §4); mt = 2 cuts that to 1.5x
+  constexpr uint32_t a_tile_bytes = kTileM * kBlockK * 2;
+  const uint32_t a_bytes = (uint32_t)a.mt * a_tile_bytes, b_bytes = (uint32_t)a.C * kBlockK * 2;
   // 1024-byte aligned stage buffers (128B swizzle atoms repeat every 1024 B)
   unsigned char* smem = (unsigned char*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   unsigned char* smem_a = smem;
@@ -174,7 +178,9 @@ __global__ void __launch_bounds__(kGemmThreads, 1) lr_xtr_rs_kernel(const __grid
         if (i >= a.stages) mbar_wait(&empty_bar[s], ((i / a.stages) - 1) & 1);
         mbar_expect_tx(&full_bar[s], a_bytes + b_bytes);
         const int k0 = (kb_begin + i) * kBlockK;
-        tma_load_2d(smem_a + (size_t)s * a_bytes, &a.tma_a[row], k0, tile_m * kTileM, &full_bar[s]);
+        for (int t = 0; t < a.mt; ++t)
+          tma_load_2d(smem_a + (size_t)s * a_bytes + (size_t)t * a_tile_bytes, &a.tma_a[row], k0,
+                      (tile_m * a.mt + t) * kTileM, &full_bar[s]);
         tma_load_2d(smem_b + (size_t)s * b_bytes, &a.tma_b[row], k0, 0, &full_bar[s]);
       }
     }
@@ -186,11 +192,14 @@ __global__ void __launch_bounds__(kGemmThreads, 1) lr_xtr_rs_kernel(const __grid
         const int s = i % a.stages;
         mbar_wait(&full_bar[s], (i / a.stages) & 1);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        for (int t = 0; t < a.mt; ++t) {
 #pragma unroll
-        for (int k = 0; k < kBlockK / kUmmaK; ++k) {
-          const uint64_t da = umma_desc_sw128(smem_a + (size_t)s * a_bytes, k * kUmmaK * 2);
-          const uint64_t db = umma_desc_sw128(smem_b + (size_t)s * b_bytes, k * kUmmaK * 2);
-          umma_bf16(tmem_d, da, db, idesc, (i > 0 || k > 0) ? 1u : 0u);
+          for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+            const uint64_t da =
+                umma_desc_sw128(smem_a + (size_t)s * a_bytes + (size_t)t * a_tile_bytes, k * kUmmaK * 2);
+            const uint64_t db = umma_desc_sw128(smem_b + (size_t)s * b_bytes, k * kUmmaK * 2);
+            umma_bf16(tmem_d + (uint32_t)(t * a.C), da, db, idesc, (i > 0 || k > 0) ? 1u : 0u);
+          }
         }
         umma_commit(&empty_bar[s]);  // frees the smem stage once these MMAs have read it
       }
@@ -201,13 +210,14 @@ __global__ void __launch_bounds__(kGemmThreads, 1) lr_xtr_rs_kernel(const __grid
     const int quarter = warp & 3;  // a warp may only touch TMEM lanes [32*(warp%4), +32)
     mbar_wait(&tmem_full_bar, 0);
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    const int f = tile_m * kTileM + quarter * 32 + lane;  // global feature row of this thread
+   for (int t = 0; t < a.mt; ++t) {
+    const int f = (tile_m * a.mt + t) * kTileM + quarter * 32 + lane;  // global feature row of this thread
     const int owner = min(f / a.feats_per_rank, tab.world - 1);
     const int local_row = f - owner * a.feats_per_rank;
     float* dst_row = (float*)(tab.heap[owner] + a.out_off) + (size_t)local_row * a.C;
     for (int c0 = 0; c0 < a.C; c0 += 32) {
       uint32_t v[32];
-      const uint32_t taddr = tmem_d + ((uint32_t)(quarter * 32) << 16) + (uint32_t)c0;
+      const uint32_t taddr = tmem_d + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(t * a.C + c0);
       asm volatile(
           "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
           "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
@@ -238,6 +248,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) lr_xtr_rs_kernel(const __grid
         }
       }
     }
+   }
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
@@ -329,14 +340,15 @@ EncodeTiledFn encode_tiled() {
 }
 
 // row-major [rows x K] bf16, K contiguous; box = [box_rows x 64]
-void make_map(CUtensorMap* m, const void* base, long long rows, long long K, int box_rows) {
+void make_map(CUtensorMap* m, const void* base, long long rows, long long K, int box_rows, bool promo256 = false) {
   cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)rows};
   cuuint64_t strides[1] = {(cuuint64_t)K * 2};
   cuuint32_t box[2] = {(cuuint32_t)kBlockK, (cuuint32_t)box_rows};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = encode_tiled()(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, (void*)base, dims, strides, box, estr,
                               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
-                              CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                              promo256 ? CU_TENSOR_MAP_L2_PROMOTION_L2_256B : CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) throw Error("cuTensorMapEncodeTiled failed (" + std::to_string((int)r) + ")");
 }
 
@@ -365,19 +377,33 @@ void GpuPlane::lr_xtr_reduce_scatter(const void* const* xt, const void* const* r
   a.C = C;
   a.K = (int)K;
   a.feats_per_rank = fpr;
+  // two M tiles per CTA when the problem is large enough to still fill the GPU (MP4J_LR_MT=1|2 overrides)
+  const char* mt_env = getenv("MP4J_LR_MT");
+  const char* mode = getenv("MP4J_LR_SPLIT");
+  const bool want_cluster = mode && strcmp(mode, "cluster") == 0;
+  a.mt = mt_env ? atoi(mt_env) : ((F >= 2 * kTileM * 16 && !want_cluster) ? 2 : 1);
+  if (a.mt != 2 || want_cluster) a.mt = 1;
   int cols = 32;
-  while (cols < C) cols <<= 1;
+  while (cols < a.mt * C) cols <<= 1;
   a.tmem_cols = cols;
   for (int i = 0; i < L; ++i) {
-    make_map(&a.tma_a[i], xt[i], F, K, kTileM);
+    // 256-byte L2 promotion on the streamed operand: the neighbouring 128 B of every row is the next
+    // k-block's data, so DRAM sees 256-byte bursts per row (MP4J_LR_L2PROMO=128 restores the default)
+    static const bool promo256 = !(getenv("MP4J_LR_L2PROMO") && atoi(getenv("MP4J_LR_L2PROMO")) == 128);
+    make_map(&a.tma_a[i], xt[i], F, K, kTileM, promo256);
     make_map(&a.tma_b[i], rt[i], C, K, C);
   }
-  const int tiles_m = (F + kTileM - 1) / kTileM;
+  const int tiles_m = (F + a.mt * kTileM - 1) / (a.mt * kTileM);
   const int kb_total = (int)((K + kBlockK - 1) / kBlockK);
   // Ring depth: as deep as ~200 KB of shared memory allows (one CTA per SM): HBM latency under load is
   // 2-3 us, so a 4-stage ring (64 KB of A in flight) left DRAM at 53 % (profiles/README.md §4).
-  const size_t stage_bytes = (size_t)kTileM * kBlockK * 2 + (size_t)C * kBlockK * 2;
-  a.stages = (int)std::max<size_t>(2, std::min<size_t>(kMaxStages, (200 * 1024) / stage_bytes));
+  const size_t stage_bytes = (size_t)a.mt * kTileM * kBlockK * 2 + (size_t)C * kBlockK * 2;
+  // Two CTAs per SM with half the ring each (MP4J_LR_CTAS_PER_SM=1 disables): one CTA's prologue /
+  // epilogue (TMEM round trip + atomics, no loads in flight) overlaps the other's main loop.
+  const char* cps_env = getenv("MP4J_LR_CTAS_PER_SM");
+  const int cps = (!(cps_env && atoi(cps_env) == 1) && (size_t)a.tmem_cols * 2 <= 512 && a.cluster <= 1 && !want_cluster) ? 2 : 1;
+  a.stages = (int)std::max<size_t>(2, std::min<size_t>(kMaxStages, ((cps == 2 ? 108 : 200) * 1024) / stage_bytes));
+  const int wave = sms_ * cps;
   // Split K so the grid is close to a whole number of waves of 148 CTAs (one CTA per SM): the first
   // version launched 320 CTAs = 2.16 waves, i.e. a third wave at 16 % occupancy.
   int best_splits = 1;
@@ -387,13 +413,13 @@ void GpuPlane::lr_xtr_reduce_scatter(const void* const* xt, const void* const* r
     const int kps = (kb_total + sp - 1) / sp;
     const int real = (kb_total + kps - 1) / kps;
     const long long ctas = (long long)tiles_m * real;
-    const long long waves = (ctas + sms_ - 1) / sms_;
-    const double eff = (double)ctas / (double)(waves * sms_);
-    if (eff > best_eff + 0.02 || (ctas >= 2 * sms_ && best_eff < 0.9 && eff > best_eff)) {
+    const long long waves = (ctas + wave - 1) / wave;
+    const double eff = (double)ctas / (double)(waves * wave);
+    if (eff > best_eff + 0.02 || (ctas >= 2 * wave && best_eff < 0.9 && eff > best_eff)) {
       best_eff = eff;
       best_splits = real;
     }
-    if (best_eff >= 0.95 && ctas >= sms_) break;
+    if (best_eff >= 0.95 && ctas >= wave) break;
   }
   int splits = best_splits;
   a.k_blocks_per_split = (kb_total + splits - 1) / splits;
@@ -404,8 +430,7 @@ void GpuPlane::lr_xtr_reduce_scatter(const void* const* xt, const void* const* r
   // to plain atomics (0.294 vs 0.209 ms at F=8192, C=128, K=65536): gang-scheduling 8-CTA clusters at
   // one CTA per SM strands SMs and serialises tile completion, so atomics stay the default.
   a.cluster = 1;
-  const char* mode = getenv("MP4J_LR_SPLIT");
-  if (splits > 1 && mode && strcmp(mode, "cluster") == 0) {
+  if (splits > 1 && want_cluster) {
     for (int cs : {8, 4, 2}) {
       if (cs > splits + 1 && cs != 2) continue;  // do not split far more than the grid needs
       const int kps = (kb_total + cs - 1) / cs;
@@ -450,7 +475,7 @@ void GpuPlane::lr_xtr_reduce_scatter(const void* const* xt, const void* const* r
   MP4J_CUDA(cudaGetLastError());
   if (p > 1) lr_peer_barrier_kernel<<<dim3(1, emulated() ? p : 1), 32, 0, s>>>(tab);
   MP4J_CUDA(cudaGetLastError());
-  last_ = CollStat{"lr_xtr_reduce_scatter", a.cluster > 1 ? "tcgen05+dsmem-splitk+red.add" : "tcgen05+red.add", (size_t)F * K * 2, tiles_m * splits, false};
+  last_ = CollStat{"lr_xtr_reduce_scatter", a.cluster > 1 ? "tcgen05+dsmem-splitk+red.add" : (a.mt == 2 ? "tcgen05-2mt+red.add" : "tcgen05+red.add"), (size_t)F * K * 2, tiles_m * splits, false};
 }
 
 }  // namespace mp4j

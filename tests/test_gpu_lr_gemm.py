@@ -28,9 +28,11 @@ def planes():
     (4, 1024, 256, 1024),
     (8, 4096, 16, 8192),
 ])
-@pytest.mark.parametrize("split", ["atomic", "cluster"])
+@pytest.mark.parametrize("split", ["atomic", "cluster", "atomic-2mt"])
 def test_lr_xtr_reduce_scatter(planes, world, F, C, K, split, monkeypatch):
-    monkeypatch.setenv("MP4J_LR_SPLIT", split)  # read by the launcher at every call
+    # read by the launcher at every call; "2mt" = two 128-row tiles per CTA sharing each staged B tile
+    monkeypatch.setenv("MP4J_LR_SPLIT", split.split("-")[0])
+    monkeypatch.setenv("MP4J_LR_MT", "2" if split.endswith("2mt") else "1")
     plane = planes(world)
     g = torch.Generator().manual_seed(F + C + K)
     xts = [(torch.randn(F, K, generator=g) * 0.5).to(torch.bfloat16) for _ in range(world)]
