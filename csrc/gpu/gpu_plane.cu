@@ -100,6 +100,10 @@ GpuPlane::~GpuPlane() {
   map_release();
   for (float* a : hist_amax_)
     if (a) cudaFree(a);
+  for (float* a : lr_scratch_)
+    if (a) cudaFree(a);
+  for (int* a : lr_tile_cnt_)
+    if (a) cudaFree(a);
   if (err_host_) cudaFreeHost(err_host_);
 }
 

@@ -148,6 +148,12 @@ class GpuPlane {
   std::map<size_t, size_t> used_;  // off -> bytes
   CollStat last_;
   size_t lr_shard_off_ = 0, lr_shard_bytes_ = 0;
+  size_t lr_recv_off_ = 0, lr_recv_bytes_ = 0;
+  int lr_recv_next_ = 0;  // K12: store-forwarded contributions [src rank][fpr x C]
+  float* lr_scratch_[kMaxRanks] = {};   // K12: local split-K merge buffers (per local rank)
+  size_t lr_scratch_bytes_[kMaxRanks] = {};
+  int* lr_tile_cnt_[kMaxRanks] = {};
+  int lr_tiles_[kMaxRanks] = {};
   size_t hist_shard_off_ = 0, hist_shard_bytes_ = 0;
   float* hist_amax_[kMaxRanks] = {};
   struct MapWork;

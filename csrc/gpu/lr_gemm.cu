@@ -54,6 +54,16 @@ struct LrArgs {
   int stages;                    // smem ring depth (2..kMaxStages)
   int cluster;                   // CTAs per cluster along split-K (1 = none): partials meet in DSMEM
   int mt;                        // 128-row M tiles per CTA (1 or 2) sharing every staged B tile
+  // world > 1: rows owned by OTHER ranks are first merged over the split-K CTAs in a local fp32
+  // scratch [F x C] (L2-resident atomics); the last CTA of a tile forwards the merged rows to their
+  // owners, so a remote shard receives one contribution per rank instead of one per split
+  float* scratch[kMaxRanks];     // per local rank; nullptr = add straight into the owner's shard
+  int* tile_cnt[kMaxRanks];      // per local rank: arrivals per M tile (reset by the last CTA)
+  int splits;
+  // the forwarded rows are STORED (coalesced 128-byte NVLink writes, ~5x the throughput of 16-byte
+  // remote atomics) into the owner's receive area [source rank][feats_per_rank x C]; the owner adds
+  // the p-1 areas to its shard after the closing barrier (lr_sum_recv_kernel)
+  unsigned long long recv_off;
 };
 
 __device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -215,6 +225,7 @@ __global__ void __launch_bounds__(kGemmThreads, 2) lr_xtr_rs_kernel(const __grid
     const int owner = min(f / a.feats_per_rank, tab.world - 1);
     const int local_row = f - owner * a.feats_per_rank;
     float* dst_row = (float*)(tab.heap[owner] + a.out_off) + (size_t)local_row * a.C;
+    if (a.scratch[row] != nullptr && owner != rank) dst_row = a.scratch[row] + (size_t)f * a.C;
     for (int c0 = 0; c0 < a.C; c0 += 32) {
       uint32_t v[32];
       const uint32_t taddr = tmem_d + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(t * a.C + c0);
@@ -248,6 +259,42 @@ __global__ void __launch_bounds__(kGemmThreads, 2) lr_xtr_rs_kernel(const __grid
         }
       }
     }
+   }
+   if (a.scratch[row] != nullptr) {
+     // ---- split-K fix-up: the last CTA of this tile forwards the locally merged foreign rows
+     __shared__ int last_s;
+     const int et = threadIdx.x - 64;  // 0..127 within the epilogue warps
+     __threadfence();                  // my adds are performed before the arrival is counted
+     asm volatile("bar.sync 1, 128;" ::: "memory");
+     if (et == 0) {
+       const int old = atomicAdd(&a.tile_cnt[row][tile_m], 1);
+       last_s = (old == a.splits - 1);
+       if (last_s) a.tile_cnt[row][tile_m] = 0;  // ready for the next call
+     }
+     asm volatile("bar.sync 1, 128;" ::: "memory");
+     if (last_s) {
+       __threadfence();
+       const int c4n = a.C / 4;
+       const int rows = a.mt * kTileM;
+       for (int idx = et; idx < rows * c4n; idx += 128) {
+         const int f2 = tile_m * rows + idx / c4n;
+         if (f2 >= a.F) break;
+         const int owner2 = min(f2 / a.feats_per_rank, tab.world - 1);
+         if (owner2 == rank) continue;
+         const int c = (idx % c4n) * 4;
+         const float* src = a.scratch[row] + (size_t)f2 * a.C + c;
+         float4 x;
+         asm volatile("ld.relaxed.gpu.global.v4.f32 {%0,%1,%2,%3}, [%4];"
+                      : "=f"(x.x), "=f"(x.y), "=f"(x.z), "=f"(x.w)
+                      : "l"(src)
+                      : "memory");
+         float* dst = (float*)(tab.heap[owner2] + a.recv_off) +
+                      ((size_t)rank * a.feats_per_rank + (size_t)(f2 - owner2 * a.feats_per_rank)) * a.C + c;
+         asm volatile("st.global.L1::no_allocate.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst), "f"(x.x), "f"(x.y),
+                      "f"(x.z), "f"(x.w)
+                      : "memory");
+       }
+     }
    }
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -293,6 +340,26 @@ __global__ void __launch_bounds__(kGemmThreads, 2) lr_xtr_rs_kernel(const __grid
       }
     }
     cluster.sync();  // nobody leaves while a peer may still read its shared memory
+  }
+}
+
+// owner side of the store-forwarded contributions: shard += sum over source ranks of recv[src]
+__global__ void lr_sum_recv_kernel(PeerTable tab, unsigned long long out_off, unsigned long long recv_off,
+                                   int feats_per_rank, int F, int C) {
+  const int rank = tab.emulate ? (int)blockIdx.y : tab.rank;
+  const int rows = max(0, min(feats_per_rank, F - rank * feats_per_rank));
+  const long long n4 = (long long)rows * C / 4;
+  float4* shard = (float4*)(tab.heap[rank] + out_off);
+  const float4* recv = (const float4*)(tab.heap[rank] + recv_off);
+  const long long per_src4 = (long long)feats_per_rank * C / 4;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
+    float4 acc = shard[i];
+    for (int q = 0; q < tab.world; ++q) {
+      if (q == rank) continue;
+      const float4 x = recv[(long long)q * per_src4 + i];
+      acc.x += x.x; acc.y += x.y; acc.z += x.z; acc.w += x.w;
+    }
+    shard[i] = acc;
   }
 }
 
@@ -442,6 +509,45 @@ void GpuPlane::lr_xtr_reduce_scatter(const void* const* xt, const void* const* r
       break;
     }
   }
+  a.splits = splits;
+  // local-first merge of the split-K partials of foreign rows (MP4J_LR_REMOTE=direct disables)
+  const char* rm = getenv("MP4J_LR_REMOTE");
+  const bool local_first = p > 1 && splits > 1 && a.cluster == 1 && !(rm && strcmp(rm, "direct") == 0);
+  // Two receive areas used alternately: call n may write area n%2 of a peer without asking, because
+  // the peer finished reading it (sum of call n-2) before it entered the closing barrier of call n-1,
+  // which this rank has passed. That removes the opening cross-GPU barrier from this path.
+  if (local_first && lr_recv_bytes_ < shard_bytes * p) {
+    MP4J_CUDA(cudaStreamSynchronize(s));
+    host_barrier();  // nobody may still be writing into the old area of a peer
+    if (lr_recv_bytes_) free(lr_recv_off_);
+    lr_recv_off_ = alloc(2 * shard_bytes * p);
+    lr_recv_bytes_ = shard_bytes * p;
+    host_barrier();
+  }
+  if (local_first) lr_recv_next_ ^= 1;
+  a.recv_off = lr_recv_off_ + (size_t)lr_recv_next_ * lr_recv_bytes_;
+  for (int i = 0; i < L; ++i) {
+    a.scratch[i] = nullptr;
+    a.tile_cnt[i] = nullptr;
+    if (!local_first) continue;
+    const size_t need = (size_t)F * C * 4;
+    if (lr_scratch_bytes_[i] < need) {
+      MP4J_CUDA(cudaStreamSynchronize(s));
+      if (lr_scratch_[i]) MP4J_CUDA(cudaFree(lr_scratch_[i]));
+      MP4J_CUDA(cudaMalloc(&lr_scratch_[i], need));
+      lr_scratch_bytes_[i] = need;
+    }
+    if (lr_tiles_[i] < tiles_m) {
+      MP4J_CUDA(cudaStreamSynchronize(s));
+      if (lr_tile_cnt_[i]) MP4J_CUDA(cudaFree(lr_tile_cnt_[i]));
+      MP4J_CUDA(cudaMalloc(&lr_tile_cnt_[i], (size_t)tiles_m * sizeof(int)));
+      MP4J_CUDA(cudaMemset(lr_tile_cnt_[i], 0, (size_t)tiles_m * sizeof(int)));
+      lr_tiles_[i] = tiles_m;
+    }
+    MP4J_CUDA(cudaMemsetAsync(lr_scratch_[i], 0, need, s));
+    a.scratch[i] = lr_scratch_[i];
+    a.tile_cnt[i] = lr_tile_cnt_[i];
+  }
   const size_t smem = (size_t)a.stages * stage_bytes + 1024;
   static bool attr_set = false;
   if (!attr_set) {
@@ -456,7 +562,9 @@ void GpuPlane::lr_xtr_reduce_scatter(const void* const* xt, const void* const* r
   }
   *feats_per_rank_out = fpr;
   PeerTable tab = a.tab;
-  if (p > 1) lr_peer_barrier_kernel<<<dim3(1, emulated() ? p : 1), 32, 0, s>>>(tab);
+  // direct mode adds into remote shards: everyone must have zeroed first. The store-forwarding mode
+  // never touches a remote shard and double-buffers its receive areas, so it needs no opening barrier.
+  if (p > 1 && !local_first) lr_peer_barrier_kernel<<<dim3(1, emulated() ? p : 1), 32, 0, s>>>(tab);
   {
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(tiles_m, splits, emulated() ? p : 1);
@@ -474,8 +582,13 @@ void GpuPlane::lr_xtr_reduce_scatter(const void* const* xt, const void* const* r
   }
   MP4J_CUDA(cudaGetLastError());
   if (p > 1) lr_peer_barrier_kernel<<<dim3(1, emulated() ? p : 1), 32, 0, s>>>(tab);
+  if (local_first) {
+    const long long n4 = (long long)fpr * C / 4;
+    const int blocks = (int)std::max<long long>(1, std::min<long long>(2 * sms_, (n4 + 255) / 256));
+    lr_sum_recv_kernel<<<dim3(blocks, emulated() ? p : 1), 256, 0, s>>>(tab, a.out_off, a.recv_off, fpr, F, C);
+  }
   MP4J_CUDA(cudaGetLastError());
-  last_ = CollStat{"lr_xtr_reduce_scatter", a.cluster > 1 ? "tcgen05+dsmem-splitk+red.add" : (a.mt == 2 ? "tcgen05-2mt+red.add" : "tcgen05+red.add"), (size_t)F * K * 2, tiles_m * splits, false};
+  last_ = CollStat{"lr_xtr_reduce_scatter", a.cluster > 1 ? "tcgen05+dsmem-splitk+red.add" : (local_first ? "tcgen05+local-splitk+red.add" : (a.mt == 2 ? "tcgen05-2mt+red.add" : "tcgen05+red.add")), (size_t)F * K * 2, tiles_m * splits, false};
 }
 
 }  // namespace mp4j
