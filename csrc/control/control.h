@@ -70,7 +70,7 @@ class Master {
 
  private:
   struct Conn;
-  void accept_loop();
+  void accept_loop(int listen_fd);
   void serve(std::shared_ptr<Conn> c);
   void watchdog_loop();
   void finish(int code);

@@ -49,7 +49,7 @@ void Master::start() {
     start_time_ = std::chrono::steady_clock::now();
   }
   listen_fd_ = net::tcp_listen(port_, &port_);
-  accept_thr_ = std::thread([this] { accept_loop(); });
+  accept_thr_ = std::thread([this, lfd = listen_fd_] { accept_loop(lfd); });
   watchdog_thr_ = std::thread([this] { watchdog_loop(); });
   log_line(LOG_INFO, "master started, slave num:" + std::to_string(n_) + ", port:" + std::to_string(port_));
 }
@@ -104,12 +104,12 @@ void Master::shutdown() {
     }
     cv_.notify_all();
   }
+  if (listen_fd_ >= 0) net::shutdown_fd(listen_fd_);  // wakes the acceptor (it owns a copy of the number)
+  if (accept_thr_.joinable()) accept_thr_.join();
   if (listen_fd_ >= 0) {
-    net::shutdown_fd(listen_fd_);
     net::close_fd(listen_fd_);
     listen_fd_ = -1;
   }
-  if (accept_thr_.joinable()) accept_thr_.join();
   if (watchdog_thr_.joinable()) watchdog_thr_.join();
   std::vector<std::shared_ptr<Conn>> conns;
   {
@@ -122,9 +122,9 @@ void Master::shutdown() {
   for (auto& c : conns) net::close_fd(c->fd);
 }
 
-void Master::accept_loop() {
+void Master::accept_loop(int listen_fd) {
   for (;;) {
-    int fd = net::tcp_accept(listen_fd_);
+    int fd = net::tcp_accept(listen_fd);
     if (fd < 0) return;
     auto c = std::make_shared<Conn>();
     c->fd = fd;

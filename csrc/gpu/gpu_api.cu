@@ -114,9 +114,23 @@ int mp4j_gpu_check(mp4j_gpu* g) {
 int mp4j_gpu_allreduce(mp4j_gpu* g, void* const* arrs, int dtype, int op, int64_t from, int64_t to, int algo,
                        void* stream) {
   MP4J_API_BEGIN
+  TraceScope trace_scope(g->g, (cudaStream_t)stream, "mp4j.allreduce");
   g->g->allreduce(arrs, dtype, op, from, to, algo, (cudaStream_t)stream);
   MP4J_API_END
 }
+int mp4j_gpu_trace(mp4j_gpu* g, int on) {
+  MP4J_API_BEGIN
+  g->g->trace().enable(on != 0);
+  MP4J_API_END
+}
+
+int mp4j_gpu_stats(mp4j_gpu* g, char* buf, size_t n, int reset) {
+  MP4J_API_BEGIN
+  copy_out(g->g->trace().stats_json(), buf, n);
+  if (reset) g->g->trace().reset();
+  MP4J_API_END
+}
+
 int mp4j_gpu_custom_op(mp4j_gpu* g, int dtype, const char* expr, int* op_out) {
   MP4J_API_BEGIN
   *op_out = custom_op_register(dtype, expr, g->g->world());
@@ -133,42 +147,49 @@ int mp4j_rtc_compile(int dtype, const char* expr, int world, long long* cubin_by
 
 int mp4j_gpu_allreduce_wire(mp4j_gpu* g, void* const* arrs, int64_t from, int64_t to, int wire, void* stream) {
   MP4J_API_BEGIN
+  TraceScope trace_scope(g->g, (cudaStream_t)stream, "mp4j.allreduce_wire");
   g->g->allreduce_wire((float* const*)arrs, from, to, wire, (cudaStream_t)stream);
   MP4J_API_END
 }
 int mp4j_gpu_reduce_scatter(mp4j_gpu* g, void* const* arrs, int dtype, int op, int64_t from,
                             const int64_t* counts, int algo, void* stream) {
   MP4J_API_BEGIN
+  TraceScope trace_scope(g->g, (cudaStream_t)stream, "mp4j.reduce_scatter");
   g->g->reduce_scatter(arrs, dtype, op, from, counts, algo, (cudaStream_t)stream);
   MP4J_API_END
 }
 int mp4j_gpu_allgather(mp4j_gpu* g, void* const* arrs, int dtype, const int64_t* froms, const int64_t* tos,
                        int algo, void* stream) {
   MP4J_API_BEGIN
+  TraceScope trace_scope(g->g, (cudaStream_t)stream, "mp4j.allgather");
   g->g->allgather(arrs, dtype, froms, tos, algo, (cudaStream_t)stream);
   MP4J_API_END
 }
 int mp4j_gpu_broadcast(mp4j_gpu* g, void* const* arrs, int dtype, int64_t from, int64_t to, int root, int algo,
                        void* stream) {
   MP4J_API_BEGIN
+  TraceScope trace_scope(g->g, (cudaStream_t)stream, "mp4j.broadcast");
   g->g->broadcast(arrs, dtype, from, to, root, algo, (cudaStream_t)stream);
   MP4J_API_END
 }
 int mp4j_gpu_gather(mp4j_gpu* g, void* const* arrs, int dtype, const int64_t* froms, const int64_t* tos,
                     int root, void* stream) {
   MP4J_API_BEGIN
+  TraceScope trace_scope(g->g, (cudaStream_t)stream, "mp4j.gather");
   g->g->gather(arrs, dtype, froms, tos, root, (cudaStream_t)stream);
   MP4J_API_END
 }
 int mp4j_gpu_scatter(mp4j_gpu* g, void* const* arrs, int dtype, const int64_t* froms, const int64_t* tos,
                      int root, void* stream) {
   MP4J_API_BEGIN
+  TraceScope trace_scope(g->g, (cudaStream_t)stream, "mp4j.scatter");
   g->g->scatter(arrs, dtype, froms, tos, root, (cudaStream_t)stream);
   MP4J_API_END
 }
 int mp4j_gpu_reduce(mp4j_gpu* g, void* const* arrs, int dtype, int op, int64_t from, int64_t to, int root,
                     int algo, void* stream) {
   MP4J_API_BEGIN
+  TraceScope trace_scope(g->g, (cudaStream_t)stream, "mp4j.reduce");
   g->g->reduce(arrs, dtype, op, from, to, root, algo, (cudaStream_t)stream);
   MP4J_API_END
 }
@@ -176,6 +197,7 @@ int mp4j_gpu_thread_allreduce(mp4j_gpu* g, void* const* bufs, int T, int dtype, 
                               int64_t to, int fanout, int dst, int local_only, int thread_algo, int algo,
                               void* stream) {
   MP4J_API_BEGIN
+  TraceScope trace_scope(g->g, (cudaStream_t)stream, "mp4j.thread_allreduce");
   g->g->thread_allreduce(bufs, T, dtype, op, from, to, fanout, dst, local_only != 0,
                          (thread_algo & 0xff) | (algo << 16), (cudaStream_t)stream);
   MP4J_API_END
@@ -188,6 +210,7 @@ int mp4j_gpu_map_collective(mp4j_gpu* g, int mode, const int64_t* const* keys, c
   const int L = g->g->emulated() ? g->g->world() : 1;
   long long nn[MP4J_MAX_RANKS];
   for (int i = 0; i < L; ++i) nn[i] = n[i];
+  TraceScope trace_scope(g->g, (cudaStream_t)stream, "mp4j.map_collective");
   g->g->map_collective(mode, (const long long* const*)keys, vals, nn, max_n, out_cap, dtype, op, partition,
                        (long long**)out_keys, out_vals, (unsigned long long**)info, (cudaStream_t)stream);
   MP4J_API_END
@@ -196,6 +219,7 @@ int mp4j_gpu_map_collective(mp4j_gpu* g, int mode, const int64_t* const* keys, c
 int mp4j_gpu_lr_xtr_reduce_scatter(mp4j_gpu* g, const void* const* xt, const void* const* rt, int F, int C, int64_t K,
                                    float** shard_out, int* feats_per_rank, void* stream) {
   MP4J_API_BEGIN
+  TraceScope trace_scope(g->g, (cudaStream_t)stream, "mp4j.lr_xtr_reduce_scatter");
   g->g->lr_xtr_reduce_scatter(xt, rt, F, C, K, shard_out, feats_per_rank, (cudaStream_t)stream);
   MP4J_API_END
 }
@@ -210,6 +234,7 @@ int mp4j_gpu_gbdt_hist_reduce_scatter(mp4j_gpu* g, const uint8_t* const* bins, c
     pp[i] = pitch[i];
     rr[i] = rows[i];
   }
+  TraceScope trace_scope(g->g, (cudaStream_t)stream, "mp4j.gbdt_hist_reduce_scatter");
   g->g->gbdt_hist_reduce_scatter(bins, pp, grad, hess, rr, F, shard_out, feats_per_rank, (cudaStream_t)stream);
   MP4J_API_END
 }

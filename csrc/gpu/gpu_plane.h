@@ -13,6 +13,7 @@
 
 #include "dense.cuh"
 #include "symm_heap.h"
+#include "trace.h"
 
 namespace mp4j {
 
@@ -56,6 +57,7 @@ class GpuPlane {
   bool has_multicast() const { return heap_.mc_base() != nullptr; }
   std::string describe() const;
   const CollStat& last() const { return last_; }
+  CollTrace& trace() { return trace_; }  // per-collective CUDA-event timing + NVTX (MP4J_TRACE=1)
 
   // symmetric allocation: same offset on every rank. Returns the offset; ptr(rank, off) maps it.
   size_t alloc(size_t bytes);
@@ -147,6 +149,7 @@ class GpuPlane {
   std::mutex alloc_mu_;
   std::map<size_t, size_t> used_;  // off -> bytes
   CollStat last_;
+  CollTrace trace_;
   size_t lr_shard_off_ = 0, lr_shard_bytes_ = 0;
   size_t lr_recv_off_ = 0, lr_recv_bytes_ = 0;
   int lr_recv_next_ = 0;  // K12: store-forwarded contributions [src rank][fpr x C]

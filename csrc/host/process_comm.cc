@@ -32,7 +32,7 @@ ProcessComm::ProcessComm(const std::string& login, const std::string& master_hos
   }
   out_fds_.assign(n_, -1);
   in_fds_.assign(n_, -1);
-  accept_thr_ = std::thread([this] { accept_loop(); });
+  accept_thr_ = std::thread([this, lfd = listen_fd_] { accept_loop(lfd); });
   // kill script line: ssh login@host "kill -9 pid" (PCS:178-183)
   master_->kill_me(rank_, "ssh " + login + "@" + host + " \"kill -9 " + std::to_string((int)getpid()) + "\"");
   int period = env_int("MP4J_HEARTBEAT_MS", 15000);
@@ -41,19 +41,21 @@ ProcessComm::ProcessComm(const std::string& login, const std::string& master_hos
 
 ProcessComm::~ProcessComm() {
   master_->stop_heartbeat();
+  // wake the acceptor, let it leave, and only then release the descriptor (it holds its own copy of
+  // the number: closing first would let the kernel hand the same number to somebody else)
+  if (listen_fd_ >= 0) net::shutdown_fd(listen_fd_);
+  if (accept_thr_.joinable()) accept_thr_.join();
   if (listen_fd_ >= 0) {
-    net::shutdown_fd(listen_fd_);
     net::close_fd(listen_fd_);
     listen_fd_ = -1;
   }
-  if (accept_thr_.joinable()) accept_thr_.join();
   for (int fd : out_fds_) net::close_fd(fd);
   for (int fd : in_fds_) net::close_fd(fd);
 }
 
-void ProcessComm::accept_loop() {
+void ProcessComm::accept_loop(int listen_fd) {
   for (;;) {
-    int fd = net::tcp_accept(listen_fd_);
+    int fd = net::tcp_accept(listen_fd);
     if (fd < 0) return;
     int32_t src = -1;
     try {

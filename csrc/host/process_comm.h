@@ -60,7 +60,7 @@ class ProcessComm {
  private:
   int out_fd(int dest);
   int in_fd(int src);
-  void accept_loop();
+  void accept_loop(int listen_fd);
 
   std::unique_ptr<MasterClient> master_;
   int rank_ = -1, n_ = 0;

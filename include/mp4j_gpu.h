@@ -45,6 +45,13 @@ int mp4j_gpu_scatter(mp4j_gpu* g, void* const* arrs, int dtype, const int64_t* f
                      int root, void* stream);                                            /* PCS:900 */
 int mp4j_gpu_reduce(mp4j_gpu* g, void* const* arrs, int dtype, int op, int64_t from, int64_t to, int root,
                     int algo, void* stream);                                             /* PCS:1390 */
+/* Per-collective statistics (the reference only logs wall-clock deltas in its checks).
+ * With tracing on (this call, or MP4J_TRACE=1) every collective is bracketed by a CUDA event pair on
+ * the caller's stream and an NVTX range; mp4j_gpu_stats resolves them (synchronising those events)
+ * and writes a JSON array: one object per (collective, algorithm) with calls, bytes, total/min/max/avg
+ * microseconds and algorithmic GB/s. reset != 0 clears the counters afterwards. */
+int mp4j_gpu_trace(mp4j_gpu* g, int on);
+int mp4j_gpu_stats(mp4j_gpu* g, char* buf, size_t n, int reset);
 /* Custom device operator: the GPU form of implementing I<T>Operator.apply (J/operator/I*Operator.java:29-30).
  * `expr` is a C++ expression over `a` (accumulated so far, ascending rank / thread order) and `b` (next
  * value), both of the element type of `dtype` (one of the six primitive operands); e.g. "a + 2 * b",

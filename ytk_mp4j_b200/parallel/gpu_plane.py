@@ -54,6 +54,8 @@ _P("mp4j_gpu_gbdt_hist_reduce_scatter", C.c_int, C.c_void_p, N.c_vpp, N.c_i64p, 
 
 _P("mp4j_gpu_allreduce_wire", C.c_int, C.c_void_p, N.c_vpp, C.c_int64, C.c_int64, C.c_int, C.c_void_p)
 _P("mp4j_gpu_custom_op", C.c_int, C.c_void_p, C.c_int, C.c_char_p, C.POINTER(C.c_int))
+_P("mp4j_gpu_trace", C.c_int, C.c_void_p, C.c_int)
+_P("mp4j_gpu_stats", C.c_int, C.c_void_p, C.c_char_p, C.c_size_t, C.c_int)
 _P("mp4j_rtc_compile", C.c_int, C.c_int, C.c_char_p, C.c_int, C.POINTER(C.c_longlong))
 
 MAP_MODES = {"allreduce": 0, "reduce_scatter": 1, "allgather": 2}
@@ -169,6 +171,18 @@ class _PlaneBase:
             check(N.lib.mp4j_gpu_custom_op(self._g, code, expr.encode(), C.byref(out)))
             cache[key] = out.value
         return cache[key]
+
+    def trace(self, on=True):
+        """Per-collective CUDA-event timing + NVTX ranges on/off (also MP4J_TRACE=1)."""
+        check(N.lib.mp4j_gpu_trace(self._g, 1 if on else 0))
+
+    def stats(self, reset=False):
+        """Per (collective, algorithm) statistics since tracing was enabled: calls, bytes, total/min/
+        max/avg microseconds on the device, algorithmic GB/s. Synchronises the traced events."""
+        import json
+        buf = C.create_string_buffer(1 << 16)
+        check(N.lib.mp4j_gpu_stats(self._g, buf, len(buf), 1 if reset else 0))
+        return json.loads(buf.value.decode())
 
     def check(self):
         """Raises if a kernel hit the device-side peer-wait watchdog since the last call."""
