@@ -283,7 +283,9 @@ void GpuPlane::allreduce(void* const* arrs, int dtype, int op, int64_t from, int
     GrsArgs a{};
     a.tab = table();
     a.entry_barrier = 1;
-    a.exit_barrier = 0;  // safe: the slot alternates, see DESIGN.md "one-shot slot reuse"
+    // no exit barrier: the slot alternates between calls (DESIGN.md "one-shot slot reuse"). A graph
+    // replay repeats the SAME slot sequence, so under capture the barrier is kept.
+    a.exit_barrier = capturing(s) ? 1 : 0;
     const size_t slot = oneshot_off_[oneshot_next_];
     oneshot_next_ ^= 1;
     a.src_off = a.dst_off = (unsigned long long)slot - (unsigned long long)from * es;

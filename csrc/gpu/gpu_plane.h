@@ -120,6 +120,12 @@ class GpuPlane {
   GpuPlane() {}
   void finish_init(GpuOptions opt);
   int local_ranks() const { return emulated() ? world() : 1; }
+  // True while `s` is being captured into a CUDA graph: host-side alternation of buffers is then
+  // frozen into the graph, so paths that rely on it add the barrier they otherwise save.
+  static bool capturing(cudaStream_t s) {
+    cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+    return cudaStreamIsCapturing(s, &st) == cudaSuccess && st != cudaStreamCaptureStatusNone;
+  }
   PeerTable table() const;
   struct Plan;
   // Generic driver: windows + staging + one GRS launch per window.

@@ -564,7 +564,9 @@ void GpuPlane::lr_xtr_reduce_scatter(const void* const* xt, const void* const* r
   PeerTable tab = a.tab;
   // direct mode adds into remote shards: everyone must have zeroed first. The store-forwarding mode
   // never touches a remote shard and double-buffers its receive areas, so it needs no opening barrier.
-  if (p > 1 && !local_first) lr_peer_barrier_kernel<<<dim3(1, emulated() ? p : 1), 32, 0, s>>>(tab);
+  // (Under graph capture the alternation is frozen into the graph, so the barrier stays.)
+  if (p > 1 && (!local_first || capturing(s)))
+    lr_peer_barrier_kernel<<<dim3(1, emulated() ? p : 1), 32, 0, s>>>(tab);
   {
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(tiles_m, splits, emulated() ? p : 1);
