@@ -39,6 +39,7 @@ def body(comm, n, reps):
             comm.barrier()  # the reference's timing includes the trailing master barrier (PCS:1367)
         out[name] = (time.perf_counter() - t0) / reps * 1e3
     assert np.all(arr == comm.getSlaveNum())
+    out["transport"] = comm.host_transport
     return out
 
 
@@ -57,7 +58,9 @@ def main():
     print(json.dumps({"bench": "host_allreduce_double_sum", "procs": p, "elems": a.elems, "ms": round(ms, 3),
                       "rpc_ms": round(rpc, 3), "busbw_GBps": round(a.elems * 8 / ms / 1e6 * 2 * (p - 1) / p, 3),
                       "published_reference_ms_1GbE": pub, "speedup_vs_published": round(pub / ms, 1) if pub else None,
-                      "transport": "loopback TCP, C++ host plane (ring RS + ring AG)", "master_exit_code": code}))
+                      "transport": {"shm": "shared-memory windows, one gather-reduce-scatter pass (C++ host plane)",
+                                    "tcp": "loopback TCP, ring RS + ring AG (C++ host plane)"}[res[0]["transport"]],
+                      "master_exit_code": code}))
 
 
 if __name__ == "__main__":

@@ -114,6 +114,7 @@ void mp4j_comm_destroy(mp4j_comm* c) {
 }
 int mp4j_comm_rank(mp4j_comm* c) { return c->pc->rank(); }
 int mp4j_comm_size(mp4j_comm* c) { return c->pc->size(); }
+const char* mp4j_comm_host_transport(mp4j_comm* c) { return c->pc->host_transport(); }
 int mp4j_comm_barrier(mp4j_comm* c) {
   MP4J_API_BEGIN
   c->pc->barrier();

@@ -37,6 +37,7 @@ ProcessComm::ProcessComm(const std::string& login, const std::string& master_hos
   master_->kill_me(rank_, "ssh " + login + "@" + host + " \"kill -9 " + std::to_string((int)getpid()) + "\"");
   int period = env_int("MP4J_HEARTBEAT_MS", 15000);
   master_->start_heartbeat(rank_, std::min(period, 5000), period, 4, nullptr, nullptr);
+  shm_ = ShmPlane::create(*master_, rank_, n_);  // collective; null on every rank if unusable
 }
 
 ProcessComm::~ProcessComm() {
@@ -118,6 +119,11 @@ void ProcessComm::reduce_scatter(void* arr, int dtype, int op, int64_t from, con
   const size_t es = dtype_size(dtype);
   std::vector<int64_t> froms(n_), tos(n_);
   froms_tos_from_counts(from, counts, n_, froms.data(), tos.data());
+  if (shm_) {
+    std::vector<uint32_t> sm(n_, all_mask()), dm(n_);
+    for (int q = 0; q < n_; ++q) dm[q] = 1u << q;
+    return shm_->grs(arr, dtype, op, froms.data(), tos.data(), sm.data(), dm.data());
+  }
   int next = (rank_ + 1) % n_, prev = (rank_ - 1 + n_) % n_;
   int sfd = out_fd(next), rfd = in_fd(prev);
   char* base = (char*)arr;
@@ -145,6 +151,11 @@ void ProcessComm::allgather(void* arr, int dtype, const int64_t* froms, const in
   if (n_ == 1) return;  // PCS:630
   std::lock_guard<std::mutex> lk(op_mu_);
   const size_t es = dtype_size(dtype);
+  if (shm_) {
+    std::vector<uint32_t> sm(n_), dm(n_, all_mask());
+    for (int q = 0; q < n_; ++q) sm[q] = 1u << q;
+    return shm_->grs(arr, dtype, MP4J_COPY, froms, tos, sm.data(), dm.data());
+  }
   int next = (rank_ + 1) % n_, prev = (rank_ - 1 + n_) % n_;
   int sfd = out_fd(next), rfd = in_fd(prev);
   char* base = (char*)arr;
@@ -162,6 +173,11 @@ void ProcessComm::gather(void* arr, int dtype, const int64_t* froms, const int64
   if (n_ == 1) return;  // PCS:545
   std::lock_guard<std::mutex> lk(op_mu_);
   const size_t es = dtype_size(dtype);
+  if (shm_) {
+    std::vector<uint32_t> sm(n_), dm(n_, 1u << root);
+    for (int q = 0; q < n_; ++q) sm[q] = 1u << q;
+    return shm_->grs(arr, dtype, MP4J_COPY, froms, tos, sm.data(), dm.data());
+  }
   char* base = (char*)arr;
   int vr = (rank_ - root + n_) % n_;
   auto real = [&](int v) { return (v + root) % n_; };
@@ -190,6 +206,11 @@ void ProcessComm::scatter(void* arr, int dtype, const int64_t* froms, const int6
   if (n_ == 1) return;
   std::lock_guard<std::mutex> lk(op_mu_);
   const size_t es = dtype_size(dtype);
+  if (shm_) {
+    std::vector<uint32_t> sm(n_, 1u << root), dm(n_);
+    for (int q = 0; q < n_; ++q) dm[q] = 1u << q;
+    return shm_->grs(arr, dtype, MP4J_COPY, froms, tos, sm.data(), dm.data());
+  }
   char* base = (char*)arr;
   int vr = (rank_ - root + n_) % n_;
   auto real = [&](int v) { return (v + root) % n_; };
@@ -222,6 +243,12 @@ void ProcessComm::broadcast(void* arr, int dtype, int64_t from, int64_t to, int 
   if (n_ == 1) return;  // PCS:751
   std::vector<int64_t> froms(n_), tos(n_);
   balanced_split(from, to, n_, froms.data(), tos.data());  // PCS:760-767
+  if (shm_) {  // one pass: everybody copies out of the root's window
+    if (root < 0 || root >= n_) throw Error("root rank out of range");
+    std::lock_guard<std::mutex> lk(op_mu_);
+    std::vector<uint32_t> sm(n_, 1u << root), dm(n_, all_mask());
+    return shm_->grs(arr, dtype, MP4J_COPY, froms.data(), tos.data(), sm.data(), dm.data());
+  }
   scatter(arr, dtype, froms.data(), tos.data(), root);
   allgather(arr, dtype, froms.data(), tos.data());
 }
@@ -232,6 +259,13 @@ void ProcessComm::reduce(void* arr, int dtype, int op, int64_t from, int64_t to,
   std::vector<int64_t> froms(n_), tos(n_), counts(n_);
   balanced_split(from, to, n_, froms.data(), tos.data());
   for (int i = 0; i < n_; ++i) counts[i] = tos[i] - froms[i];
+  if (shm_) {  // one pass: owners reduce, the root collects
+    if (root < 0 || root >= n_) throw Error("root rank out of range");
+    if (!op_valid_for(dtype, op) || op == MP4J_COPY) throw Error("invalid operator for dtype");
+    std::lock_guard<std::mutex> lk(op_mu_);
+    std::vector<uint32_t> sm(n_, all_mask()), dm(n_, 1u << root);
+    return shm_->grs(arr, dtype, op, froms.data(), tos.data(), sm.data(), dm.data());
+  }
   reduce_scatter(arr, dtype, op, from, counts.data());
   gather(arr, dtype, froms.data(), tos.data(), root);
 }
@@ -242,6 +276,12 @@ void ProcessComm::allreduce(void* arr, int dtype, int op, int64_t from, int64_t 
   std::vector<int64_t> froms(n_), tos(n_), counts(n_);
   balanced_split(from, to, n_, froms.data(), tos.data());  // PCS:1741-1756
   for (int i = 0; i < n_; ++i) counts[i] = tos[i] - froms[i];
+  if (shm_) {  // one pass: owners reduce, everybody collects
+    if (!op_valid_for(dtype, op) || op == MP4J_COPY) throw Error("invalid operator for dtype");
+    std::lock_guard<std::mutex> lk(op_mu_);
+    std::vector<uint32_t> sm(n_, all_mask()), dm(n_, all_mask());
+    return shm_->grs(arr, dtype, op, froms.data(), tos.data(), sm.data(), dm.data());
+  }
   reduce_scatter(arr, dtype, op, from, counts.data());
   allgather(arr, dtype, froms.data(), tos.data());
 }

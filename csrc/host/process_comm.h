@@ -21,6 +21,7 @@
 #include "../control/control.h"
 #include "../core/ops.h"
 #include "../core/partition.h"
+#include "shm_plane.h"
 
 namespace mp4j {
 
@@ -36,6 +37,9 @@ class ProcessComm {
   const std::vector<std::string>& addresses() const { return addrs_; }
   MasterClient& master() { return *master_; }
   bool closed() const { return closed_; }
+  // "shm" when the ranks share a machine and exchange host arrays through shared-memory windows
+  // (shm_plane.h), "tcp" for the ring / tree algorithms over the socket mesh.
+  const char* host_transport() const { return shm_ ? "shm" : "tcp"; }
 
   void barrier();
   void log(LogLevel lvl, const std::string& msg);  // forwards verbatim; prefixes are the binding's job
@@ -58,6 +62,7 @@ class ProcessComm {
   std::string sendrecv_bytes(int dest, const void* data, size_t n, int src);
 
  private:
+  uint32_t all_mask() const { return n_ >= 32 ? 0xffffffffu : ((1u << n_) - 1u); }
   int out_fd(int dest);
   int in_fd(int src);
   void accept_loop(int listen_fd);
@@ -75,6 +80,7 @@ class ProcessComm {
   std::mutex op_mu_;  // one collective at a time per communicator
   bool closed_ = false;
   std::vector<char> scratch_;
+  std::unique_ptr<ShmPlane> shm_;  // intra-node data plane; null = TCP
 };
 
 }  // namespace mp4j

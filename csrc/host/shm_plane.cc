@@ -1,0 +1,271 @@
+#include "shm_plane.h"
+
+#include <errno.h>
+#include <fcntl.h>
+#include <limits.h>
+#include <linux/futex.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <sys/syscall.h>
+#include <time.h>
+#include <unistd.h>
+
+#include <algorithm>
+#include <atomic>
+#include <chrono>
+#include <random>
+
+#include "../control/control.h"
+#include "../core/error.h"
+#include "../core/ops.h"
+
+namespace mp4j {
+
+namespace {
+
+constexpr size_t kHeaderBytes = 4096;
+
+size_t env_size(const char* name, size_t dflt) {
+  const char* v = getenv(name);
+  return (v && *v) ? (size_t)strtoull(v, nullptr, 10) : dflt;
+}
+
+std::string boot_id() {
+  std::string id;
+  if (FILE* f = fopen("/proc/sys/kernel/random/boot_id", "r")) {
+    char buf[128] = {0};
+    if (fgets(buf, sizeof buf, f)) id = buf;
+    fclose(f);
+  }
+  while (!id.empty() && (id.back() == '\n' || id.back() == ' ')) id.pop_back();
+  if (id.empty()) {
+    char host[256] = {0};
+    gethostname(host, sizeof host - 1);
+    id = std::string("host:") + host;
+  }
+  // POSIX shared memory is per IPC/mount namespace: two containers on one kernel share the boot id
+  // but not /dev/shm, which the mapping attempt below detects.
+  return id;
+}
+
+int futex(std::atomic<uint32_t>* addr, int op, uint32_t val, const struct timespec* ts) {
+  return (int)syscall(SYS_futex, (uint32_t*)addr, op, val, ts, nullptr, 0);
+}
+
+inline void cpu_relax() {
+#if defined(__x86_64__) || defined(__i386__)
+  __builtin_ia32_pause();
+#else
+  std::atomic_signal_fence(std::memory_order_seq_cst);
+#endif
+}
+
+std::vector<std::string> split_lines(const std::string& s) {
+  std::vector<std::string> out;
+  size_t b = 0;
+  for (;;) {
+    size_t e = s.find('\n', b);
+    out.push_back(s.substr(b, e == std::string::npos ? std::string::npos : e - b));
+    if (e == std::string::npos) break;
+    b = e + 1;
+  }
+  return out;
+}
+
+}  // namespace
+
+struct ShmPlane::Header {
+  std::atomic<uint32_t> count;
+  char pad1[60];
+  std::atomic<uint32_t> gen;
+  char pad2[60];
+};
+
+std::unique_ptr<ShmPlane> ShmPlane::create(MasterClient& master, int rank, int n) {
+  if (n < 2 || n > 32) return nullptr;  // masks are 32-bit; identical decision on every rank
+  const bool enabled = env_size("MP4J_SHM", 1) != 0;
+  size_t window = env_size("MP4J_SHM_BYTES", 64ull << 20);
+  window = std::max<size_t>(window, 1 << 16) / 8192 * 8192;  // two page-aligned halves
+  const size_t seg_bytes = kHeaderBytes + window;
+  std::unique_ptr<ShmPlane> p(new ShmPlane());
+  p->rank_ = rank;
+  p->n_ = n;
+  p->seg_bytes_ = seg_bytes;
+  p->half_bytes_ = window / 2;
+  p->timeout_s_ = (double)env_size("MP4J_PEER_TIMEOUT_S", 600);
+  p->seg_.assign(n, nullptr);
+  {
+    // spinning only pays when every rank keeps a core to itself (helpers: master, heartbeats, the caller's threads)
+    const long cores = sysconf(_SC_NPROCESSORS_ONLN);
+    p->spin_us_ = cores >= 2L * n ? 200.0 : (cores >= n + 2 ? 20.0 : 0.0);
+    if (getenv("MP4J_SHM_SPIN_US")) p->spin_us_ = (double)env_size("MP4J_SHM_SPIN_US", 0);
+  }
+
+  // ---- my segment
+  std::string name;
+  if (enabled) {
+    std::random_device rd;
+    char buf[96];
+    snprintf(buf, sizeof buf, "/mp4j-%d-%d-%08x", (int)getpid(), rank, (unsigned)rd());
+    int fd = shm_open(buf, O_CREAT | O_EXCL | O_RDWR, 0600);
+    if (fd >= 0) {
+      if (ftruncate(fd, (off_t)seg_bytes) == 0) {
+        void* m = mmap(nullptr, seg_bytes, PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);
+        if (m != MAP_FAILED) {
+          p->seg_[rank] = (char*)m;
+          memset(m, 0, kHeaderBytes);
+          name = buf;
+        }
+      }
+      ::close(fd);
+      if (name.empty()) shm_unlink(buf);
+    }
+  }
+  // ---- exchange (boot id, name, window) and map the peers
+  const std::string mine = boot_id() + "\n" + name + "\n" + std::to_string(window);
+  std::vector<std::string> parts = master.gather_all(rank, mine.data(), mine.size());
+  bool ok = enabled && !name.empty() && (int)parts.size() == n;
+  std::vector<std::string> names(n);
+  for (int q = 0; ok && q < n; ++q) {
+    std::vector<std::string> f = split_lines(parts[q]);
+    if (f.size() != 3 || f[1].empty() || f[0] != split_lines(mine)[0] || f[2] != std::to_string(window)) ok = false;
+    else names[q] = f[1];
+  }
+  for (int q = 0; ok && q < n; ++q) {
+    if (q == rank) continue;
+    int fd = shm_open(names[q].c_str(), O_RDWR, 0600);
+    if (fd < 0) {
+      ok = false;
+      break;
+    }
+    void* m = mmap(nullptr, seg_bytes, PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);
+    ::close(fd);
+    if (m == MAP_FAILED) ok = false;
+    else p->seg_[q] = (char*)m;
+  }
+  // ---- everybody must agree, otherwise ranks would run different algorithms
+  const char verdict = ok ? '1' : '0';
+  parts = master.gather_all(rank, &verdict, 1);
+  bool all_ok = (int)parts.size() == n;
+  for (const auto& v : parts)
+    if (v.size() != 1 || v[0] != '1') all_ok = false;
+  if (!name.empty()) shm_unlink(name.c_str());  // everyone who could map it has done so: no leftovers on exit
+  if (!all_ok) return nullptr;                  // ~ShmPlane unmaps
+  return p;
+}
+
+ShmPlane::~ShmPlane() {
+  for (char* s : seg_)
+    if (s) munmap(s, seg_bytes_);
+}
+
+void ShmPlane::barrier() {
+  Header* h = (Header*)seg_[0];
+  const uint32_t g = h->gen.load(std::memory_order_acquire);
+  if (h->count.fetch_add(1, std::memory_order_acq_rel) + 1 == (uint32_t)n_) {
+    h->count.store(0, std::memory_order_relaxed);
+    h->gen.fetch_add(1, std::memory_order_release);
+    futex(&h->gen, FUTEX_WAKE, INT_MAX, nullptr);
+    return;
+  }
+  // Phases of one pass take tens to hundreds of microseconds and a futex sleep costs about as much
+  // to wake from, so spin for up to ~200 us (less or not at all when cores are scarce) before sleeping.
+  const auto t0 = std::chrono::steady_clock::now();
+  for (int i = 0; spin_us_ > 0; ++i) {
+    if (h->gen.load(std::memory_order_acquire) != g) return;
+    cpu_relax();
+    if ((i & 255) == 255 &&
+        std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t0).count() > spin_us_)
+      break;
+  }
+  while (h->gen.load(std::memory_order_acquire) == g) {
+    struct timespec ts = {0, 100 * 1000 * 1000};
+    futex(&h->gen, FUTEX_WAIT, g, &ts);  // returns on wake, value change, timeout or signal: re-check
+    if (std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count() > timeout_s_)
+      throw Error("shared-memory barrier timed out: a peer left the collective (MP4J_PEER_TIMEOUT_S)");
+  }
+}
+
+void ShmPlane::grs(void* arr, int dtype, int op, const int64_t* lo, const int64_t* hi, const uint32_t* src_mask,
+                   const uint32_t* dst_mask) {
+  const size_t es = dtype_size(dtype);
+  if (es == 0) throw Error("unknown dtype");
+  int64_t span_lo = INT64_MAX, span_hi = INT64_MIN;
+  bool need_b2 = false;  // some destination reads a reduced slice out of its owner's window
+  for (int q = 0; q < n_; ++q) {
+    if (hi[q] <= lo[q]) continue;
+    span_lo = std::min(span_lo, lo[q]);
+    span_hi = std::max(span_hi, hi[q]);
+    if (op != MP4J_COPY && dst_mask[q] != (1u << q)) need_b2 = true;
+  }
+  if (span_hi <= span_lo) return;
+  char* base = (char*)arr;
+  const int64_t chunk = (int64_t)(half_bytes_ / es);
+  std::vector<char> acc;  // private accumulator for slices whose result goes back into my window
+  for (int64_t c0 = span_lo; c0 < span_hi; c0 += chunk) {
+    const int64_t c1 = std::min(span_hi, c0 + chunk);
+    const size_t hoff = kHeaderBytes + (size_t)half_ * half_bytes_;
+    auto win = [&](int q, int64_t elem) { return seg_[q] + hoff + (size_t)(elem - c0) * es; };
+    // ---- phase 1: publish my contributions
+    for (int q = 0; q < n_; ++q) {
+      if (!((src_mask[q] >> rank_) & 1u)) continue;
+      const int64_t l = std::max(lo[q], c0), h = std::min(hi[q], c1);
+      if (l >= h) continue;
+      if (op == MP4J_COPY && dst_mask[q] == (1u << rank_)) continue;  // my own slice to myself
+      if (op != MP4J_COPY && q == rank_) continue;  // the slice I reduce myself: read from my array in phase 2
+      memcpy(win(rank_, l), base + l * es, (size_t)(h - l) * es);
+    }
+    barrier();
+    // ---- phase 2: the owner reduces its slice over the source windows, ascending rank order
+    if (op != MP4J_COPY) {
+      const int q = rank_;
+      const int64_t l = std::max(lo[q], c0), h = std::min(hi[q], c1);
+      if (l < h && src_mask[q] != 0) {
+        const bool to_me = (dst_mask[q] >> q) & 1u;
+        const bool to_others = (dst_mask[q] & ~(1u << q)) != 0;
+        // Blocked: a 32 KiB accumulator stays in L1 while the p source streams pass over it. My own
+        // contribution comes straight from my array (it was not copied in), the others from their
+        // windows; the result goes to my array and, if others want it, to my window.
+        const int64_t blk = (int64_t)(32768 / es);
+        if (acc.size() < 32768) acc.resize(32768);
+        char* o = acc.data();
+        for (int64_t b0 = l; b0 < h; b0 += blk) {
+          const int64_t b1 = std::min(h, b0 + blk);
+          const size_t bb = (size_t)(b1 - b0) * es;
+          bool first = true;
+          for (int s = 0; s < n_; ++s) {
+            if (!((src_mask[q] >> s) & 1u)) continue;
+            const char* x = (s == rank_) ? base + b0 * es : win(s, b0);
+            if (first) memcpy(o, x, bb);
+            else host_reduce_into(dtype, op, o, x, (size_t)(b1 - b0));  // op(accumulated, next rank)
+            first = false;
+          }
+          if (to_me) memcpy(base + b0 * es, o, bb);
+          if (to_others) memcpy(win(rank_, b0), o, bb);
+        }
+      }
+      if (need_b2) barrier();
+    }
+    // ---- phase 3: fetch the slices I am a destination of
+    for (int q = 0; q < n_; ++q) {
+      if (!((dst_mask[q] >> rank_) & 1u)) continue;
+      const int64_t l = std::max(lo[q], c0), h = std::min(hi[q], c1);
+      if (l >= h || src_mask[q] == 0) continue;
+      int from_rank;
+      if (op != MP4J_COPY) {
+        if (q == rank_) continue;  // written by phase 2
+        from_rank = q;
+      } else {
+        from_rank = __builtin_ctz(src_mask[q]);
+        if (from_rank == rank_) continue;  // my own data
+      }
+      memcpy(base + l * es, win(from_rank, l), (size_t)(h - l) * es);
+    }
+    half_ ^= 1;  // the other half serves the next chunk / call: no closing barrier needed
+  }
+}
+
+}  // namespace mp4j

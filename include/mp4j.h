@@ -48,6 +48,9 @@ int mp4j_comm_create(const char* login, const char* master_host, int master_port
 void mp4j_comm_destroy(mp4j_comm* c);
 int mp4j_comm_rank(mp4j_comm* c);
 int mp4j_comm_size(mp4j_comm* c);
+/* "shm": the ranks share a machine and host arrays move through shared-memory windows (one
+ * gather-reduce-scatter pass per collective); "tcp": ring / tree algorithms over sockets (MP4J_SHM=0). */
+const char* mp4j_comm_host_transport(mp4j_comm* c);
 int mp4j_comm_barrier(mp4j_comm* c);                                   /* PCS:432 */
 int mp4j_comm_log(mp4j_comm* c, int level, const char* msg);            /* PCS:289-353 */
 int mp4j_comm_close(mp4j_comm* c, int code);                            /* PCS:234 */

@@ -19,15 +19,25 @@ from ytk_mp4j_b200.parallel.local_cluster import run_cluster
     (2, "byte", 77, 0),
     (4, "double", 3, 2),      # fewer elements than ranks: empty segments
 ])
-def test_process_arrays(p, dtype, n, root):
-    res, code, _ = run_cluster(p, workers.process_arrays, (dtype, n, root))
+@pytest.mark.parametrize("transport", ["shm", "tcp"])
+def test_process_arrays(p, dtype, n, root, transport, monkeypatch):
+    # shm: one gather-reduce-scatter pass over shared-memory windows (ranks share this machine);
+    # tcp: the reference's ring / tree algorithms over sockets (the multi-host path)
+    monkeypatch.setenv("MP4J_SHM", "1" if transport == "shm" else "0")
+    res, code, _ = run_cluster(p, workers.process_arrays, (dtype, n, root, False, transport))
     assert res == [True] * p and code == 0
 
 
-def test_process_arrays_large_pipelined():
-    # > 1 MiB per segment exercises the chunked reduce-on-receive pipeline
-    res, code, _ = run_cluster(2, workers.process_arrays, ("double", 700_001, 1))
+@pytest.mark.parametrize("transport", ["shm", "tcp"])
+def test_process_arrays_large_pipelined(transport, monkeypatch):
+    # tcp: > 1 MiB per segment exercises the chunked reduce-on-receive pipeline;
+    # shm: a 256 KiB window forces many double-buffered chunks per collective
+    monkeypatch.setenv("MP4J_SHM", "1" if transport == "shm" else "0")
+    monkeypatch.setenv("MP4J_SHM_BYTES", str(256 << 10))
+    res, code, _ = run_cluster(2, workers.process_arrays, ("double", 700_001, 1, False, transport))
     assert res == [True] * 2 and code == 0
+    res, code, _ = run_cluster(3, workers.process_arrays, ("float", 300_007, 2, False, transport))
+    assert res == [True] * 3 and code == 0
 
 
 def test_loc_operators_end_to_end():

@@ -23,8 +23,10 @@ def _expected_owner(n, p):
     return np.minimum(idx // avg, p - 1) if avg > 0 else np.full(n, p - 1)
 
 
-def process_arrays(comm, dtype, n, root, compress=False):
+def process_arrays(comm, dtype, n, root, compress=False, transport=None):
     """All 7 array collectives + scalars for one primitive dtype through the C++ host plane."""
+    if transport is not None and comm.getSlaveNum() > 1:
+        assert comm.host_transport == transport, comm.host_transport
     mk, ops, npdt = DT[dtype]
     operand = mk(compress)
     p, r = comm.getSlaveNum(), comm.getRank()

@@ -63,6 +63,7 @@ _proto("mp4j_comm_create", C.c_int, C.c_char_p, C.c_char_p, C.c_int, C.c_int, C.
 _proto("mp4j_comm_destroy", None, C.c_void_p)
 _proto("mp4j_comm_rank", C.c_int, C.c_void_p)
 _proto("mp4j_comm_size", C.c_int, C.c_void_p)
+_proto("mp4j_comm_host_transport", C.c_char_p, C.c_void_p)
 _proto("mp4j_comm_barrier", C.c_int, C.c_void_p)
 _proto("mp4j_comm_log", C.c_int, C.c_void_p, C.c_int, C.c_char_p)
 _proto("mp4j_comm_close", C.c_int, C.c_void_p, C.c_int)

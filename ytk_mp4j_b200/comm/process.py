@@ -91,6 +91,11 @@ class ProcessCommSlave:
     rank = property(getRank)
     size = property(getSlaveNum)
 
+    @property
+    def host_transport(self):
+        """"shm" (ranks share a machine: host arrays move through shared-memory windows) or "tcp"."""
+        return N.lib.mp4j_comm_host_transport(self._h).decode()
+
     def barrier(self):
         check(N.lib.mp4j_comm_barrier(self._h))
 
