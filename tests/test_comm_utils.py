@@ -53,3 +53,24 @@ def test_scatter_plan_every_rank_receives_once(p):
         # every relative rank 1..p-1 is the head of exactly one delivered range
         heads = sorted(lo for sends in plan.values() for (_, _, lo, _) in sends)
         assert heads == list(range(1, p))
+
+
+def test_reference_halving_scatter_plan_delivers_every_slice():
+    """ScatterAllocate.allocate of the reference (seed rank 0 and rank p/2, then halve): every rank ends
+    up with its own slice, nobody but (possibly) the root receives twice - including the roots for which
+    the root's own slice makes a round trip."""
+    from ytk_mp4j_b200.utils.scatter_allocate import ScatterAllocate, allocate_halving, recv_num
+    assert ScatterAllocate.main() == 0
+    for p in (1, 2, 3, 5, 8, 13):
+        for root in range(p):
+            plan = allocate_halving(p, root)
+            have = {root: set(range(p))}
+            pending = [s for sends in plan.values() for s in sends]
+            while pending:
+                ready = [s for s in pending if s[0] in have and set(range(s[2], s[3] + 1)) <= have[s[0]]]
+                assert ready, (p, root, pending)
+                for s in ready:
+                    have.setdefault(s[1], set()).update(range(s[2], s[3] + 1))
+                    pending.remove(s)
+            assert all(r in have.get(r, ()) for r in range(p)), (p, root)
+            assert all(recv_num(plan, r) <= 1 for r in range(p) if r != root), (p, root)

@@ -29,6 +29,17 @@ class CommMaster:
     def port(self):
         return N.lib.mp4j_master_port(self._h)
 
+    def getHostPort(self):
+        """CommMaster.getHostPort (J/comm/CommMaster.java): the port slaves connect to."""
+        return self.port
+
+    def getHostName(self):
+        """CommMaster.getHostName: the name slaves should use to reach this master."""
+        import socket
+        return socket.gethostname()
+
+    main = staticmethod(lambda argv=None: main(argv))  # CommMaster.main <slave_num> <port> (CommMaster.java:106-132)
+
     def stop(self, timeout_s=None):
         """Blocks until all slaves closed (CommMaster.stop, CommMaster.java:78-86); returns the
         job exit code (0 iff every slave closed with 0). With a timeout returns None if the job is

@@ -99,6 +99,18 @@ class CommUtils:
         return [[x + pf[r] for x in CommUtils.createProcessArrayTos(pt[r] - pf[r], threadNum)]
                 for r in range(slaveNum)]
 
+    @staticmethod
+    def main(argv=None):
+        """Self-check in the spirit of CommUtils.main (J/utils/CommUtils.java:224-238): prints the balanced
+        partitions of a few sizes and asserts they tile the range."""
+        for size, p, t in ((10, 3, 2), (1000, 8, 8), (7, 8, 1)):
+            pf, pt = CommUtils.createProcessArrayFroms(size, p), CommUtils.createProcessArrayTos(size, p)
+            assert pf[0] == 0 and pt[-1] == size and all(pt[i] == pf[i + 1] for i in range(p - 1))
+            tf, tt = CommUtils.createThreadArrayFroms(size, p, t), CommUtils.createThreadArrayTos(size, p, t)
+            CommUtils.isfromsTosLegal(tf, tt, t)  # raises on an illegal partition
+            print("size=%d slaves=%d threads=%d froms=%s tos=%s" % (size, p, t, pf, pt))
+        return 0
+
     # helper shared by the communicators (PCS:1741-1756)
     @staticmethod
     def splitRange(from_, to, n):
