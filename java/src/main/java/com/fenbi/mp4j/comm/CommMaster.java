@@ -15,6 +15,16 @@ public class CommMaster {
         if (Native.masterStart(handle) != 0) throw new Mp4jException(Native.lastError());
     }
     public int getPort() { return Native.masterPort(handle); }
+    /** the port slaves connect to (CommMaster.getHostPort of the reference) */
+    public int getHostPort() { return getPort(); }
+    /** the name slaves should use to reach this master (CommMaster.getHostName of the reference) */
+    public String getHostName() {
+        try {
+            return java.net.InetAddress.getLocalHost().getHostName();
+        } catch (java.net.UnknownHostException e) {
+            return "127.0.0.1";
+        }
+    }
     /** Blocks until every slave closed; returns the aggregated exit code. */
     public int stop() { return Native.masterWait(handle); }
 

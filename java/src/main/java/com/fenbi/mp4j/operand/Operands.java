@@ -1,23 +1,29 @@
 package com.fenbi.mp4j.operand;
 
-/** Factory with the reference's names (Operands.DOUBLE_OPERAND() ...). */
+/** Factory with the reference's names (J/operand/Operands.java:33-111). */
 public final class Operands {
     private Operands() {}
-    public static Operand DOUBLE_OPERAND() { return DOUBLE_OPERAND(false); }
-    public static Operand FLOAT_OPERAND() { return FLOAT_OPERAND(false); }
-    public static Operand LONG_OPERAND() { return LONG_OPERAND(false); }
-    public static Operand INT_OPERAND() { return INT_OPERAND(false); }
-    public static Operand SHORT_OPERAND() { return SHORT_OPERAND(false); }
-    public static Operand BYTE_OPERAND() { return BYTE_OPERAND(false); }
-    public static Operand STRING_OPERAND() { return STRING_OPERAND(false); }
-    public static Operand OBJECT_OPERAND() { return OBJECT_OPERAND(false); }
-    public static Operand DOUBLE_OPERAND(boolean compress) { return new Operand("double", 0, compress); }
-    public static Operand FLOAT_OPERAND(boolean compress) { return new Operand("float", 1, compress); }
-    public static Operand LONG_OPERAND(boolean compress) { return new Operand("long", 2, compress); }
-    public static Operand INT_OPERAND(boolean compress) { return new Operand("int", 3, compress); }
-    public static Operand SHORT_OPERAND(boolean compress) { return new Operand("short", 4, compress); }
-    public static Operand BYTE_OPERAND(boolean compress) { return new Operand("byte", 5, compress); }
-    public static Operand STRING_OPERAND(boolean compress) { return new Operand("string", -1, compress); }
-    /** Object payloads travel as java.io.Serializable bytes (the Kryo role of the reference). */
-    public static Operand OBJECT_OPERAND(boolean compress) { return new Operand("object", -1, compress); }
+    public static DoubleOperand DOUBLE_OPERAND() { return new DoubleOperand(false); }
+    public static DoubleOperand DOUBLE_OPERAND(boolean compress) { return new DoubleOperand(compress); }
+    public static FloatOperand FLOAT_OPERAND() { return new FloatOperand(false); }
+    public static FloatOperand FLOAT_OPERAND(boolean compress) { return new FloatOperand(compress); }
+    public static LongOperand LONG_OPERAND() { return new LongOperand(false); }
+    public static LongOperand LONG_OPERAND(boolean compress) { return new LongOperand(compress); }
+    public static IntOperand INT_OPERAND() { return new IntOperand(false); }
+    public static IntOperand INT_OPERAND(boolean compress) { return new IntOperand(compress); }
+    public static ShortOperand SHORT_OPERAND() { return new ShortOperand(false); }
+    public static ShortOperand SHORT_OPERAND(boolean compress) { return new ShortOperand(compress); }
+    public static ByteOperand BYTE_OPERAND() { return new ByteOperand(false); }
+    public static ByteOperand BYTE_OPERAND(boolean compress) { return new ByteOperand(compress); }
+    public static StringOperand STRING_OPERAND() { return new StringOperand(false); }
+    public static StringOperand STRING_OPERAND(boolean compress) { return new StringOperand(compress); }
+    /** Serializable elements. */
+    public static <T> ObjectOperand<T> OBJECT_OPERAND(Class<T> type) { return new ObjectOperand<T>(null, type, false); }
+    /** Elements with a user codec (the reference passes a Kryo Serializer here). */
+    public static <T> ObjectOperand<T> OBJECT_OPERAND(ObjectOperand.Codec<T> codec, Class<T> type) {
+        return new ObjectOperand<T>(codec, type, false);
+    }
+    public static <T> ObjectOperand<T> OBJECT_OPERAND(ObjectOperand.Codec<T> codec, Class<T> type, boolean compress) {
+        return new ObjectOperand<T>(codec, type, compress);
+    }
 }

@@ -1,3 +1,11 @@
 package com.fenbi.mp4j.operator;
 
-public enum Container { ARRAY, MAP }
+/** Payload container kinds. */
+public enum Container {
+    ARRAY("array"), MAP("map");
+
+    private final String name;
+    Container(String name) { this.name = name; }
+    public String getName() { return name; }
+    @Override public String toString() { return name; }
+}
