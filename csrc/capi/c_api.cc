@@ -2,6 +2,8 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <algorithm>
+
 #include "../../include/mp4j.h"
 #include "../control/control.h"
 #include "../host/process_comm.h"
@@ -19,6 +21,7 @@ struct mp4j_master {
 };
 struct mp4j_tgroup {
   ThreadGroup* g;
+  std::string error;  // message of a failed delegate step, read by the other threads after a barrier
 };
 
 extern "C" {
@@ -233,7 +236,7 @@ int mp4j_comm_sendrecv_bytes(mp4j_comm* c, int dest, const void* data, size_t n,
 int mp4j_tgroup_create(int nthreads, mp4j_tgroup** out) {
   MP4J_API_BEGIN
   if (nthreads < 1) throw Error("threadNum must be >= 1");
-  *out = new mp4j_tgroup{new ThreadGroup(nthreads)};
+  *out = new mp4j_tgroup{new ThreadGroup(nthreads), std::string()};
   MP4J_API_END
 }
 void mp4j_tgroup_destroy(mp4j_tgroup* g) {
@@ -253,6 +256,50 @@ int mp4j_tgroup_set_slot(mp4j_tgroup* g, int tid, int which, uint64_t v) {
   MP4J_API_END
 }
 uint64_t mp4j_tgroup_get_slot(mp4j_tgroup* g, int tid, int which) { return g->g->get_slot(tid, which); }
+
+// ThreadCommSlave.allreduceArray on host arrays (TCS:1915-1963), all T threads call it:
+//   every thread reduces ITS 1/T slice of the range over the T arrays into thread 0's array
+//   (thread-id order, cache-sized blocks) | thread 0 runs the process allreduce | every thread copies
+//   the result into its own array. The reference does lg T serial full-length passes on pairs of
+//   threads and one thread copies for everybody; here both thread-level steps use all T cores.
+int mp4j_thread_allreduce(mp4j_tgroup* g, mp4j_comm* c, int tid, void* arr, int dtype, int op, int64_t from,
+                          int64_t to) {
+  MP4J_API_BEGIN
+  ThreadGroup& tg = *g->g;
+  const int T = tg.size();
+  if (tid < 0 || tid >= T) throw Error("threadId out of range");
+  check_from_to(from, to);
+  if (!op_valid_for(dtype, op) || op == MP4J_COPY) throw Error("invalid operator for dtype");
+  const size_t es = dtype_size(dtype);
+  tg.set_slot(tid, 0, (uint64_t)(uintptr_t)arr);
+  if (tid == 0) tg.set_slot(0, 1, 0);  // error flag of this call
+  tg.barrier();
+  char* acc = (char*)(uintptr_t)tg.get_slot(0, 0);
+  const int64_t n = to - from, per = (n + T - 1) / T;
+  const int64_t lo = from + std::min<int64_t>(n, (int64_t)tid * per), hi = from + std::min<int64_t>(n, (int64_t)(tid + 1) * per);
+  const int64_t blk = (int64_t)(32768 / es);
+  for (int64_t b0 = lo; b0 < hi; b0 += blk) {
+    const int64_t b1 = std::min(hi, b0 + blk);
+    for (int t = 1; t < T; ++t)
+      host_reduce_into(dtype, op, acc + b0 * es, (const char*)(uintptr_t)tg.get_slot(t, 0) + b0 * es, (size_t)(b1 - b0));
+  }
+  tg.barrier();
+  if (tid == 0) {
+    try {
+      c->pc->allreduce(acc, dtype, op, from, to);
+    } catch (const std::exception& e) {
+      tg.set_slot(0, 1, 1);
+      g->error = e.what();
+    }
+  }
+  tg.barrier();
+  const bool failed = tg.get_slot(0, 1) != 0;
+  if (!failed && tid != 0 && n > 0) memcpy((char*)arr + from * es, acc + from * es, (size_t)n * es);
+  std::string err = failed ? g->error : std::string();
+  tg.barrier();  // thread 0's array stays untouched until everybody has copied
+  if (failed) throw Error(err);
+  MP4J_API_END
+}
 
 // ---------------------------------------------------------------- helpers
 double mp4j_composite_double(float val, int32_t loc) { return composite_double(val, loc); }

@@ -91,6 +91,11 @@ void mp4j_tgroup_destroy(mp4j_tgroup* g);
 int mp4j_tgroup_barrier(mp4j_tgroup* g);
 int mp4j_tgroup_set_slot(mp4j_tgroup* g, int tid, int which, uint64_t v);
 uint64_t mp4j_tgroup_get_slot(mp4j_tgroup* g, int tid, int which);
+/* ThreadCommSlave.allreduceArray on host arrays (TCS:1915-1963): called by ALL threads of the group with
+ * their own array. Each thread reduces its 1/T slice over the T arrays (thread-id order), thread 0 runs
+ * the process allreduce, each thread copies the result into its array: both thread-level steps use T cores. */
+int mp4j_thread_allreduce(mp4j_tgroup* g, mp4j_comm* c, int tid, void* arr, int dtype, int op, int64_t from,
+                          int64_t to);
 
 /* ------------------------------------------------------------------ packed LOC helpers (Operators.java:75-88,187-200) */
 double mp4j_composite_double(float val, int32_t loc);

@@ -206,6 +206,25 @@ static void rank_main(int port, int r, int p, int rounds, int64_t n) {
       OK(mp4j_comm_exchange(c, &other));
       CHECK(other >= 0 && other < p && other != r, "exchange partner %d", other);
     }
+    {  // process x thread allreduce: 3 threads per rank, every thread's array ends with the global sum
+      const int T = 3;
+      const int64_t m = n / 3 + 7;
+      mp4j_tgroup* tg = nullptr;
+      OK(mp4j_tgroup_create(T, &tg));
+      std::vector<std::vector<double>> arrs(T);
+      for (int t = 0; t < T; ++t) arrs[t].assign(m, (double)(r * T + t + 1));
+      std::vector<std::thread> tt;
+      for (int t = 0; t < T; ++t)
+        tt.emplace_back([&, t] {
+          if (mp4j_thread_allreduce(tg, c, t, arrs[t].data(), MP4J_F64, MP4J_SUM, 1, m) != 0) g_fail.fetch_add(1);
+        });
+      for (auto& th : tt) th.join();
+      const double want = (double)(p * T) * (p * T + 1) / 2;
+      for (int t = 0; t < T; ++t)
+        CHECK(arrs[t][0] == (double)(r * T + t + 1) && arrs[t][1] == want && arrs[t][m - 1] == want, "thread allreduce t=%d got %f want %f",
+              t, arrs[t][m - 1], want);
+      mp4j_tgroup_destroy(tg);
+    }
     char msg[64];
     snprintf(msg, sizeof msg, "round %d done", it);
     OK(mp4j_comm_log(c, 0, msg));

@@ -280,6 +280,14 @@ class ThreadCommSlave:
         if self._T == 1:
             return self.processCommSlave.allreduceArray(arrData, operand, operator, from_, to)
         CommUtils.isFromToLegal(from_, to)
+        if not _is_cuda(arrData):
+            # host arrays + predefined operator: native path in which ALL T threads take part (each
+            # reduces its 1/T slice, each copies its own result) instead of one delegate doing everything
+            a = self.processCommSlave._native_host(arrData, operand, operator)
+            if a is not None:
+                check(N.lib.mp4j_thread_allreduce(self._tg, self.processCommSlave._h, self.getThreadId(),
+                                                  a.ctypes.data, operand.code, operator.code, from_, to))
+                return arrData
 
         def run(arrs):
             if _is_cuda(arrs[0]):
