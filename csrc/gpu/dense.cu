@@ -26,6 +26,7 @@
 #include "cuda_check.h"
 #include "custom_op.h"
 #include "grs_kernel.cuh"
+#include "half_types.cuh"
 #include "launch.h"
 
 namespace mp4j {
@@ -117,6 +118,8 @@ void launch_grs(int dtype, int op, bool nvls, const GrsArgs& args, int grid, cud
     case MP4J_I32: return by_op<int32_t, true, false>(op, args, nvls, grid, stream);
     case MP4J_I16: return by_op<int16_t, true, false>(op, args, false, grid, stream);
     case MP4J_I8: return by_op<int8_t, true, false>(op, args, false, grid, stream);
+    case MP4J_BF16: return by_op<bf16_t, false, false>(op, args, nvls, grid, stream);  // half_types.cuh
+    case MP4J_F16: return by_op<f16_t, false, false>(op, args, nvls, grid, stream);
   }
   throw Error("dtype " + std::to_string(dtype) + " is not supported on the GPU path");
 }

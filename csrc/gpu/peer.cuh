@@ -268,6 +268,8 @@ inline bool nvls_supported(int dtype, int op) {
   if (op == MP4J_COPY) return true;  // multimem.st broadcast
   switch (dtype) {
     case MP4J_F32: case MP4J_F64: return op == MP4J_SUM;
+    // bf16 / fp16 SUM have multimem forms too (half_types.cuh) but stay on the P2P kernels until the
+    // in-switch path has been verified on a multi-GPU box (it rounds differently: fp32 accumulation)
     case MP4J_I32: case MP4J_I64:
       return op == MP4J_SUM || op == MP4J_MAX || op == MP4J_MIN || op == MP4J_BAND || op == MP4J_BOR ||
              op == MP4J_BXOR;
