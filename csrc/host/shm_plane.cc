@@ -3,6 +3,7 @@
 #include <errno.h>
 #include <fcntl.h>
 #include <limits.h>
+#include <signal.h>
 #include <linux/futex.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -63,6 +64,20 @@ inline void cpu_relax() {
 #endif
 }
 
+// true if the process no longer runs: gone, or a zombie waiting to be reaped
+bool process_gone(int32_t pid) {
+  if (kill((pid_t)pid, 0) != 0) return errno == ESRCH;
+  char path[64], buf[512];
+  snprintf(path, sizeof path, "/proc/%d/stat", (int)pid);
+  FILE* f = fopen(path, "r");
+  if (!f) return false;
+  const size_t k = fread(buf, 1, sizeof buf - 1, f);
+  fclose(f);
+  buf[k] = 0;
+  const char* p = strrchr(buf, ')');  // the state letter follows the parenthesised command name
+  return p && p[1] == ' ' && (p[2] == 'Z' || p[2] == 'X');
+}
+
 std::vector<std::string> split_lines(const std::string& s) {
   std::vector<std::string> out;
   size_t b = 0;
@@ -82,6 +97,7 @@ struct ShmPlane::Header {
   char pad1[60];
   std::atomic<uint32_t> gen;
   char pad2[60];
+  std::atomic<int32_t> pid;  // owner of this segment: lets waiting peers notice a dead process
 };
 
 std::unique_ptr<ShmPlane> ShmPlane::create(MasterClient& master, int rank, int n) {
@@ -117,6 +133,7 @@ std::unique_ptr<ShmPlane> ShmPlane::create(MasterClient& master, int rank, int n
         if (m != MAP_FAILED) {
           p->seg_[rank] = (char*)m;
           memset(m, 0, kHeaderBytes);
+          ((Header*)m)->pid.store((int32_t)getpid(), std::memory_order_release);
           name = buf;
         }
       }
@@ -184,6 +201,12 @@ void ShmPlane::barrier() {
   while (h->gen.load(std::memory_order_acquire) == g) {
     struct timespec ts = {0, 100 * 1000 * 1000};
     futex(&h->gen, FUTEX_WAIT, g, &ts);  // returns on wake, value change, timeout or signal: re-check
+    // fail fast: a peer process that no longer exists will never arrive
+    for (int q = 0; q < n_; ++q) {
+      const int32_t pid = ((Header*)seg_[q])->pid.load(std::memory_order_acquire);
+      if (pid > 0 && pid != (int32_t)getpid() && process_gone(pid) && h->gen.load(std::memory_order_acquire) == g)
+        throw Error("rank " + std::to_string(q) + " (pid " + std::to_string(pid) + ") died during a collective");
+    }
     if (std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count() > timeout_s_)
       throw Error("shared-memory barrier timed out: a peer left the collective (MP4J_PEER_TIMEOUT_S)");
   }

@@ -4,7 +4,7 @@ Thread*Check.java), extended with what it never exercises: non-zero roots, from 
 every operator."""
 import numpy as np
 
-from ytk_mp4j_b200 import CommUtils, Operands, Operators
+from ytk_mp4j_b200 import CommUtils, Mp4jException, Operands, Operators
 from ytk_mp4j_b200.operators import custom
 
 DT = {
@@ -359,3 +359,20 @@ def failing_slave(comm):
             comm.exception(e, sleep_s=0.1)
         return "closed-1"
     return "ok"
+
+
+def dying_peer(comm):
+    """Rank 1 vanishes without closing; rank 0's next collective must fail instead of hanging."""
+    import os
+    import time
+    n = 1000
+    arr = np.ones(n)
+    comm.allreduceArray(arr, Operands.DOUBLE_OPERAND(), Operators.Double.SUM, 0, n)  # everybody is set up
+    if comm.getRank() == 1:
+        os._exit(7)
+    t0 = time.time()
+    try:
+        comm.allreduceArray(arr, Operands.DOUBLE_OPERAND(), Operators.Double.SUM, 0, n)
+    except Mp4jException as e:
+        return "failed-fast: %s (%.1f s)" % (str(e)[:80], time.time() - t0)
+    return "no error"
