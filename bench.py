@@ -23,6 +23,7 @@ import json
 import os
 import statistics
 import sys
+import tempfile
 import threading
 import time
 
@@ -122,7 +123,7 @@ def main():
     master = None
     if rank == 0:
         port = base_port + 17 if world > 1 else 0
-        master = CommMaster(world, port, quiet=True).start()
+        master = CommMaster(world, port, quiet=True, work_dir=tempfile.gettempdir()).start()
         port = master.port
     else:
         port = base_port + 17

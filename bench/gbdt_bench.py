@@ -9,6 +9,7 @@ import argparse
 import json
 import os
 import sys
+import tempfile
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
@@ -28,7 +29,7 @@ def main():
     lr = int(os.environ.get("LOCAL_RANK", 0))
     addr, port = os.environ.get("MASTER_ADDR", "127.0.0.1"), int(os.environ.get("MASTER_PORT", 29500))
     torch.cuda.set_device(lr)
-    master = CommMaster(world, port + 37 if world > 1 else 0, quiet=True).start() if rank == 0 else None
+    master = CommMaster(world, port + 37 if world > 1 else 0, quiet=True, work_dir=tempfile.gettempdir()).start() if rank == 0 else None
     comm = ProcessCommSlave("gbdt", addr, master.port if master else port + 37, rank_hint=rank, host="127.0.0.1")
     plane = comm.init_gpu(device=lr)
     if world > 1:

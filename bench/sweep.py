@@ -13,6 +13,7 @@ import argparse
 import json
 import os
 import sys
+import tempfile
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
@@ -40,7 +41,7 @@ def main():
     lr = int(os.environ.get("LOCAL_RANK", 0))
     addr, port = os.environ.get("MASTER_ADDR", "127.0.0.1"), int(os.environ.get("MASTER_PORT", 29500))
     torch.cuda.set_device(lr)
-    master = CommMaster(world, port + 23, quiet=True).start() if rank == 0 else None
+    master = CommMaster(world, port + 23, quiet=True, work_dir=tempfile.gettempdir()).start() if rank == 0 else None
     comm = ProcessCommSlave("sweep", addr, port + 23, rank_hint=rank, host="127.0.0.1")
     pool_bytes = max(512 << 20, 2 * a.max_bytes)
     plane = comm.init_gpu(device=lr, heap_bytes=pool_bytes + (512 << 20))

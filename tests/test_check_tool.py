@@ -10,7 +10,11 @@ def test_check_matrix_via_launcher(mode, threads, nproc, tmp_path):
     cmd = [sys.executable, "-m", "ytk_mp4j_b200.parallel.launch", "--nproc", str(nproc), "--threads", str(threads),
            "--log-dir", str(tmp_path / "log"), "--timeout", "240", "--check", "arr_size=2000", "obj_size=30",
            "run_time=1", "mode=%s" % mode, "threads=%d" % threads, "test_rpc=true", "compress=true"]
-    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
+    import os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, PYTHONPATH=root + os.pathsep + os.environ.get("PYTHONPATH", ""))
+    # run from the temp dir: the master drops kill_<port>.sh into its working directory, like the reference
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300, cwd=str(tmp_path), env=env)
     assert r.returncode == 0, r.stderr[-3000:]
     log = (tmp_path / "log" / "master.log").read_text()
     assert "all checks passed" in log and "allreduce takes:" in log

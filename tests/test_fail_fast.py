@@ -10,10 +10,10 @@ from ytk_mp4j_b200.parallel.local_cluster import _worker
 
 
 @pytest.mark.parametrize("transport", ["shm", "tcp"])
-def test_peer_death_is_detected(transport):
+def test_peer_death_is_detected(transport, tmp_path):
     env = {"MP4J_SHM": "1" if transport == "shm" else "0", "MP4J_PEER_TIMEOUT_S": "20"}
     ctx = mp.get_context("spawn")
-    master = CommMaster(2, 0, quiet=True, heartbeat_timeout_s=30).start()
+    master = CommMaster(2, 0, quiet=True, heartbeat_timeout_s=30, work_dir=str(tmp_path)).start()
     q = ctx.Queue()
     procs = [ctx.Process(target=_worker, args=(workers.dying_peer, i, 2, master.port, 0, (), q, env)) for i in range(2)]
     for p in procs:

@@ -6,6 +6,7 @@ the check tool and `mp4j-launch` use to run N ranks (optionally x T threads) loc
 """
 import multiprocessing as mp
 import os
+import tempfile
 import threading
 import traceback
 
@@ -63,7 +64,9 @@ def run_cluster(n, fn, args=(), threads=0, timeout=120, use_hints=True, env=None
     Raises RuntimeError with the first traceback if any slave failed."""
     from ytk_mp4j_b200 import CommMaster
     ctx = mp.get_context("spawn")
-    master = CommMaster(n, 0, quiet=True, **(master_kwargs or {})).start()
+    mk = dict(master_kwargs or {})
+    mk.setdefault("work_dir", tempfile.mkdtemp(prefix="mp4j-"))  # kill_<port>.sh and writeFile outputs
+    master = CommMaster(n, 0, quiet=True, **mk).start()
     q = ctx.Queue()
     procs = [ctx.Process(target=_worker, args=(fn, i if use_hints else None, n, master.port, threads, args, q, env))
              for i in range(n)]
