@@ -211,6 +211,19 @@ int mp4j_host_reduce_into(int dtype, int op, void* dst, const void* src, int64_t
   MP4J_API_END
 }
 
+int mp4j_host_map_reduce(mp4j_comm* c, int mode, int root, const char* keys, size_t keys_len, const void* vals,
+                         size_t n, int dtype, int op, char** out_keys, size_t* out_keys_len, char** out_vals,
+                         size_t* out_n) {
+  MP4J_API_BEGIN
+  std::string ok, ov;
+  c->pc->map_reduce(mode, root, keys, keys_len, vals, n, dtype, op, &ok, &ov);
+  *out_keys = dup_bytes(ok);
+  *out_keys_len = ok.size();
+  *out_vals = dup_bytes(ov);
+  *out_n = ov.size() / dtype_size(dtype);
+  MP4J_API_END
+}
+
 int mp4j_comm_send_bytes(mp4j_comm* c, int dest, const void* data, size_t n) {
   MP4J_API_BEGIN
   c->pc->send_bytes(dest, data, n);

@@ -56,6 +56,11 @@ class ProcessComm {
   // small-message allreduce through the master mailbox (PCS:1776-1799, SRV:373-497)
   void allreduce_rpc(void* arr, int dtype, int op, int64_t n);
 
+  // ---- maps of (String key, primitive value): allreduceMap (mode 0) / reduceMap (mode 1), map_host.cc.
+  // keys: n NUL-separated UTF-8 strings; vals: n elements of dtype. Outputs use the same layout.
+  void map_reduce(int mode, int root, const char* blob, size_t blob_len, const void* vals, size_t n, int dtype,
+                  int op, std::string* out_blob, std::string* out_vals);
+
   // ---- byte-blob transport (length-prefixed) ----
   void send_bytes(int dest, const void* data, size_t n);
   std::string recv_bytes(int src);

@@ -76,6 +76,13 @@ int mp4j_host_reduce(mp4j_comm* c, void* arr, int dtype, int op, int64_t from, i
 int mp4j_host_allreduce(mp4j_comm* c, void* arr, int dtype, int op, int64_t from, int64_t to); /* PCS:1733 */
 int mp4j_host_allreduce_rpc(mp4j_comm* c, void* arr, int dtype, int op, int64_t n);            /* PCS:1776 */
 /* dst[i] = op(dst[i], src[i]) on the host (the operand's local reduce, DOP:441-457) */
+/* allreduceMap (mode 0) / reduceMap (mode 1, result on `root`) of maps with String keys and primitive
+ * values (PCS:2053-2081, 1490-1516), natively: keys = n NUL-separated UTF-8 strings, vals = n elements of
+ * dtype. *out_keys / *out_vals are malloc'd (mp4j_free) in the same layout, *out_n entries. Keys are placed
+ * by String.hashCode() % slaveNum like the reference. */
+int mp4j_host_map_reduce(mp4j_comm* c, int mode, int root, const char* keys, size_t keys_len, const void* vals,
+                         size_t n, int dtype, int op, char** out_keys, size_t* out_keys_len, char** out_vals,
+                         size_t* out_n);
 int mp4j_host_reduce_into(int dtype, int op, void* dst, const void* src, int64_t n);
 
 /* byte-blob transport between slaves (String/Object/map payloads; *out freed with mp4j_free) */

@@ -206,6 +206,39 @@ static void rank_main(int port, int r, int p, int rounds, int64_t n) {
       OK(mp4j_comm_exchange(c, &other));
       CHECK(other >= 0 && other < p && other != r, "exchange partner %d", other);
     }
+    {  // String-keyed map allreduce / reduce (map_host.cc): shared keys + one private key per rank
+      std::string blob;
+      std::vector<double> vals;
+      const int nk = 2000;
+      for (int i = 0; i < nk; ++i) {
+        if (i) blob.push_back('\0');
+        blob += "key-" + std::to_string(i * 7919);
+        vals.push_back(1.0);
+      }
+      blob.push_back('\0');
+      blob += "private-" + std::to_string(r);
+      vals.push_back(5.0);
+      for (int mode = 0; mode < 2; ++mode) {
+        char *ok = nullptr, *ov = nullptr;
+        size_t okl = 0, on = 0;
+        OK(mp4j_host_map_reduce(c, mode, p - 1, blob.data(), blob.size(), vals.data(), vals.size(), MP4J_F64, MP4J_SUM, &ok,
+                                &okl, &ov, &on));
+        const bool has = mode == 0 || r == p - 1;
+        CHECK(on == (has ? (size_t)(nk + p) : 0u), "map_reduce mode=%d entries=%zu", mode, on);
+        if (has && ok && ov) {
+          const double* v = (const double*)ov;
+          size_t shared = 0, priv = 0;
+          for (size_t i = 0; i < on; ++i) {
+            if (v[i] == (double)p) ++shared;
+            else if (v[i] == 5.0) ++priv;
+          }
+          CHECK((p == 5 ? shared + priv == (size_t)(nk + p) : (shared == (size_t)nk && priv == (size_t)p)), "map values shared=%zu priv=%zu",
+                shared, priv);
+        }
+        mp4j_free(ok);
+        mp4j_free(ov);
+      }
+    }
     {  // process x thread allreduce: 3 threads per rank, every thread's array ends with the global sum
       const int T = 3;
       const int64_t m = n / 3 + 7;

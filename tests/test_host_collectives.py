@@ -90,3 +90,12 @@ def test_failing_slave_ends_job_with_code_1():
     assert code == 1
     text = "\n".join(logs)
     assert "slave exception:" in text and "boom" in text
+
+
+@pytest.mark.parametrize("native", ["1", "0"])
+@pytest.mark.parametrize("p", [1, 2, 3, 4])
+def test_string_key_maps_native_and_generic(p, native, monkeypatch):
+    # native: C++ partition / ring / merge on key blobs; generic: the same algorithms in Python (pickle)
+    monkeypatch.setenv("MP4J_NATIVE_MAPS", native)
+    res, code, _ = run_cluster(p, workers.native_maps)
+    assert res == [True] * p and code == 0

@@ -2,6 +2,8 @@
 Value patterns are the reference check harness's (J/check/check*/Process*Check.java,
 Thread*Check.java), extended with what it never exercises: non-zero roots, from > 0, odd sizes,
 every operator."""
+import os
+
 import numpy as np
 
 from ytk_mp4j_b200 import CommUtils, Mp4jException, Operands, Operators
@@ -376,3 +378,37 @@ def dying_peer(comm):
     except Mp4jException as e:
         return "failed-fast: %s (%.1f s)" % (str(e)[:80], time.time() - t0)
     return "no error"
+
+
+def native_maps(comm):
+    """String-keyed maps with primitive values through the C++ map collective (csrc/host/map_host.cc):
+    non-ASCII keys (UTF-16 hashCode placement), empty contributions, non-zero root, several value types."""
+    p, r = comm.getSlaveNum(), comm.getRank()
+    dop, lop = Operands.DOUBLE_OPERAND(), Operands.LONG_OPERAND()
+    keys = ["k%d" % i for i in range(500)] + ["été-%d" % i for i in range(50)] + ["漢字%d" % i for i in range(50)] \
+        + ["\U0001F600%d" % i for i in range(20)] + [""]
+    m = {k: float(i % 7 + 1) for i, k in enumerate(keys)}
+    m["private-%d" % r] = 100.0 + r
+    out = comm.allreduceMap(dict(m), dop, Operators.Double.SUM)
+    assert len(out) == len(keys) + p, (len(out), len(keys) + p)
+    for i, k in enumerate(keys):
+        assert out[k] == p * float(i % 7 + 1), (k, out[k])
+    for q in range(p):
+        assert out["private-%d" % q] == 100.0 + q
+    # only even ranks contribute; MAX over longs; result on the last rank only
+    contrib = {("x%d" % i): (r + 1) * 1000 + i for i in range(300)} if r % 2 == 0 else {}
+    root = p - 1
+    out = comm.reduceMap(contrib, lop, Operators.Long.MAX, root)
+    top = max(q for q in range(p) if q % 2 == 0)
+    if r == root:
+        assert len(out) == 300 and all(out["x%d" % i] == (top + 1) * 1000 + i for i in range(300)), len(out)
+    else:
+        assert out == {}
+    out = comm.allreduceMap({}, dop, Operators.Double.SUM)
+    assert out == {}
+    try:
+        comm.allreduceMap({1: 2.0}, dop, Operators.Double.SUM)
+        assert p == 1 or os.environ.get("MP4J_NATIVE_MAPS") == "0", "int keys must be rejected on the native path"
+    except Mp4jException:
+        pass
+    return True

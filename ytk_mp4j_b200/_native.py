@@ -64,6 +64,8 @@ _proto("mp4j_comm_destroy", None, C.c_void_p)
 _proto("mp4j_comm_rank", C.c_int, C.c_void_p)
 _proto("mp4j_comm_size", C.c_int, C.c_void_p)
 _proto("mp4j_comm_host_transport", C.c_char_p, C.c_void_p)
+_proto("mp4j_host_map_reduce", C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_char_p, C.c_size_t, C.c_void_p, C.c_size_t,
+       C.c_int, C.c_int, c_vpp, C.POINTER(C.c_size_t), c_vpp, C.POINTER(C.c_size_t))
 _proto("mp4j_comm_barrier", C.c_int, C.c_void_p)
 _proto("mp4j_comm_log", C.c_int, C.c_void_p, C.c_int, C.c_char_p)
 _proto("mp4j_comm_close", C.c_int, C.c_void_p, C.c_int)

@@ -516,6 +516,8 @@ class ProcessCommSlave:
         self._check_root(rootRank)
         if self._n == 1:
             return mapData
+        if self._native_map_ok(operand, operator):
+            return self._native_map_reduce(1, rootRank, mapData, operand, operator)
         mine = self.reduceScatterMap(self._partition_map(mapData), operand, operator)
         return self.gatherMap(mine, operand, rootRank)
 
@@ -551,6 +553,8 @@ class ProcessCommSlave:
         merged (PCS:2053-2081). For tensor-backed sparse maps use gpu.allreduce_map."""
         if self._n == 1:
             return mapData
+        if self._native_map_ok(operand, operator):
+            return self._native_map_reduce(0, 0, mapData, operand, operator)
         mine = self.reduceScatterMap(self._partition_map(mapData), operand, operator)
         out = {}
         for m in self.allgatherMap(mine, operand):
@@ -637,6 +641,36 @@ class ProcessCommSlave:
 
     def allreduceListConcat(self, listData, elementSerializer=None, elementType=None):
         return self.allreduceMapListConcat({"key": listData}, elementSerializer, elementType)["key"]
+
+    # ------------------------------------------------------------------ native map path
+    @staticmethod
+    def _native_map_ok(operand, operator):
+        """Maps with primitive values and a predefined operator take the C++ map collective
+        (csrc/host/map_host.cc). The choice depends on (operand, operator) only, so that every rank
+        takes the same path; MP4J_NATIVE_MAPS=0 forces the generic Python ring everywhere."""
+        return (operand.is_primitive and operand.np_dtype is not None and operator is not None
+                and operator.is_native and os.environ.get("MP4J_NATIVE_MAPS", "1") != "0")
+
+    def _native_map_reduce(self, mode, root, mapData, operand, operator):
+        n = len(mapData)
+        try:
+            blob = "\0".join(mapData.keys()).encode("utf-8")
+        except TypeError:
+            raise Mp4jException("map keys must be str (Map<String, V> in the reference)")
+        if n and blob.count(b"\0") != n - 1:
+            raise Mp4jException("map keys must not contain NUL characters")
+        vals = np.fromiter(mapData.values(), dtype=operand.np_dtype, count=n)
+        ok, ov = C.c_void_p(), C.c_void_p()
+        okl, on = C.c_size_t(), C.c_size_t()
+        check(N.lib.mp4j_host_map_reduce(self._h, mode, root, blob, len(blob), vals.ctypes.data, n, operand.code,
+                                         operator.code, C.byref(ok), C.byref(okl), C.byref(ov), C.byref(on)))
+        m = on.value
+        keys_raw = N.take_bytes(ok, okl)
+        vals_raw = N.take_bytes(ov, C.c_size_t(m * np.dtype(operand.np_dtype).itemsize))
+        if m == 0:
+            return {}
+        out_vals = np.frombuffer(vals_raw, dtype=operand.np_dtype, count=m).tolist()
+        return dict(zip(keys_raw.decode("utf-8").split("\0"), out_vals))
 
     # ------------------------------------------------------------------ internals
     def _check_root(self, root):
