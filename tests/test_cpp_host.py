@@ -15,7 +15,9 @@ import build as mp4j_build  # noqa: E402
 def _run(exe, *args, shm="1"):
     env = dict(os.environ, TSAN_OPTIONS="halt_on_error=0 exitcode=66", ASAN_OPTIONS="detect_leaks=1", MP4J_SHM=shm,
                MP4J_SHM_BYTES=str(1 << 20))
-    return subprocess.run([exe] + [str(a) for a in args], capture_output=True, text=True, timeout=300, env=env)
+    import tempfile
+    with tempfile.TemporaryDirectory(prefix="mp4j-") as cwd:  # the master drops kill_<port>.sh into its cwd
+        return subprocess.run([exe] + [str(a) for a in args], capture_output=True, text=True, timeout=300, env=env, cwd=cwd)
 
 
 @pytest.mark.parametrize("p,rounds,n", [(1, 1, 1000), (2, 2, 100003), (3, 2, 1000), (4, 2, 20011), (8, 2, 5000)])
