@@ -10,6 +10,7 @@
 #include <string.h>
 #include <sys/mman.h>
 #include <sys/stat.h>
+#include <sys/statvfs.h>
 #include <sys/syscall.h>
 #include <time.h>
 #include <unistd.h>
@@ -102,10 +103,19 @@ struct ShmPlane::Header {
 
 std::unique_ptr<ShmPlane> ShmPlane::create(MasterClient& master, int rank, int n) {
   if (n < 2 || n > 32) return nullptr;  // masks are 32-bit; identical decision on every rank
-  const bool enabled = env_size("MP4J_SHM", 1) != 0;
+  bool enabled = env_size("MP4J_SHM", 1) != 0;
   size_t window = env_size("MP4J_SHM_BYTES", 64ull << 20);
   window = std::max<size_t>(window, 1 << 16) / 8192 * 8192;  // two page-aligned halves
   const size_t seg_bytes = kHeaderBytes + window;
+  {
+    // The segments are sparse files on a tmpfs: writing beyond what /dev/shm can hold would raise
+    // SIGBUS in the middle of a collective (containers often cap it at 64 MB). Use shared memory only if
+    // all n windows fit with room to spare; otherwise every rank reports "no" and TCP is used.
+    struct statvfs vfs;
+    if (statvfs("/dev/shm", &vfs) != 0 ||
+        (unsigned long long)vfs.f_bavail * vfs.f_frsize < (unsigned long long)n * seg_bytes + (32ull << 20))
+      enabled = false;
+  }
   std::unique_ptr<ShmPlane> p(new ShmPlane());
   p->rank_ = rank;
   p->n_ = n;
