@@ -103,6 +103,15 @@ uint64_t mp4j_tgroup_get_slot(mp4j_tgroup* g, int tid, int which);
  * the process allreduce, each thread copies the result into its array: both thread-level steps use T cores. */
 int mp4j_thread_allreduce(mp4j_tgroup* g, mp4j_comm* c, int tid, void* arr, int dtype, int op, int64_t from,
                           int64_t to);
+/* The other six ThreadCommSlave array collectives on host arrays (TCS:448-1430), called by ALL threads:
+ * kind = mp4j_collective (GATHER, SCATTER, ALL_GATHER, BROADCAST, REDUCE_SCATTER, REDUCE). lo / hi: 2-D
+ * ranges flattened [slaveNum][threadNum] (gather / scatter / allgather); counts likewise (reduce-scatter);
+ * from / to for broadcast, reduce and the start of reduce-scatter. The thread-level combine and fan-out
+ * run on all T threads in parallel; the delegate (root thread on the root process, thread 0 elsewhere)
+ * runs the process collective. */
+int mp4j_thread_collective(mp4j_tgroup* g, mp4j_comm* c, int tid, int kind, void* arr, int dtype, int op,
+                           int64_t from, int64_t to, const int64_t* lo, const int64_t* hi, const int64_t* counts,
+                           int root_rank, int root_tid);
 
 /* ------------------------------------------------------------------ packed LOC helpers (Operators.java:75-88,187-200) */
 double mp4j_composite_double(float val, int32_t loc);

@@ -256,6 +256,32 @@ static void rank_main(int port, int r, int p, int rounds, int64_t n) {
       for (int t = 0; t < T; ++t)
         CHECK(arrs[t][0] == (double)(r * T + t + 1) && arrs[t][1] == want && arrs[t][m - 1] == want, "thread allreduce t=%d got %f want %f",
               t, arrs[t][m - 1], want);
+      // thread-level broadcast from (last rank, last thread) and reduce-scatter with [p][T] counts
+      for (int t = 0; t < T; ++t) arrs[t].assign(m, (r == p - 1 && t == T - 1) ? 42.0 : -1.0);
+      tt.clear();
+      for (int t = 0; t < T; ++t)
+        tt.emplace_back([&, t] {
+          if (mp4j_thread_collective(tg, c, t, MP4J_BROADCAST, arrs[t].data(), MP4J_F64, MP4J_COPY, 2, m, nullptr, nullptr, nullptr,
+                                     p - 1, T - 1) != 0)
+            g_fail.fetch_add(1);
+        });
+      for (auto& th : tt) th.join();
+      for (int t = 0; t < T; ++t) CHECK(arrs[t][2] == 42.0 && arrs[t][m - 1] == 42.0, "thread broadcast t=%d got %f", t, arrs[t][m - 1]);
+      std::vector<int64_t> cnts((size_t)p * T, 5);
+      for (int t = 0; t < T; ++t) arrs[t].assign(m, 1.0);
+      tt.clear();
+      for (int t = 0; t < T; ++t)
+        tt.emplace_back([&, t] {
+          if (mp4j_thread_collective(tg, c, t, MP4J_REDUCE_SCATTER, arrs[t].data(), MP4J_F64, MP4J_SUM, 1, 0, nullptr, nullptr,
+                                     cnts.data(), 0, 0) != 0)
+            g_fail.fetch_add(1);
+        });
+      for (auto& th : tt) th.join();
+      for (int t = 0; t < T; ++t) {
+        const int64_t off = 1 + ((int64_t)r * T + t) * 5;
+        CHECK(arrs[t][off] == (double)(p * T) && arrs[t][off + 4] == (double)(p * T), "thread reduce-scatter t=%d got %f", t,
+              arrs[t][off]);
+      }
       mp4j_tgroup_destroy(tg);
     }
     char msg[64];

@@ -92,6 +92,8 @@ _proto("mp4j_tgroup_destroy", None, C.c_void_p)
 _proto("mp4j_tgroup_barrier", C.c_int, C.c_void_p)
 _proto("mp4j_tgroup_set_slot", C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_uint64)
 _proto("mp4j_tgroup_get_slot", C.c_uint64, C.c_void_p, C.c_int, C.c_int)
+_proto("mp4j_thread_collective", C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int,
+       C.c_int64, C.c_int64, c_i64p, c_i64p, c_i64p, C.c_int, C.c_int)
 _proto("mp4j_thread_allreduce", C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int64,
        C.c_int64)
 # helpers

@@ -26,6 +26,9 @@ from ..exception import Mp4jException, check
 from ..utils.comm_utils import CommUtils
 from .process import ProcessCommSlave, _is_cuda, _is_torch
 
+# mp4j_collective codes of include/mp4j_types.h (native thread-level collectives)
+_GATHER, _SCATTER, _ALL_GATHER, _BROADCAST, _REDUCE_SCATTER, _REDUCE = 0, 1, 2, 3, 4, 5
+
 
 class ThreadCommSlave:
     def __init__(self, loginName, threadNum, masterHost, masterPort, rank_hint=None, host=None):
@@ -133,6 +136,24 @@ class ThreadCommSlave:
             raise e if isinstance(e, Mp4jException) else Mp4jException(repr(e))
         return self._result[par]
 
+    def _native_thread(self, kind, arrData, operand, operator, from_=0, to=0, lo=None, hi=None, counts=None,
+                       rootRank=0, rootThreadId=0):
+        """Host arrays with a native dtype (and a predefined operator where one applies): the C++ thread
+        collective in which all T threads combine and fan out in parallel (mp4j_thread_collective).
+        Returns False if this call must take the generic delegate path instead."""
+        if _is_cuda(arrData):
+            return False
+        a = self.processCommSlave._native_host(arrData, operand, operator)
+        if a is None:
+            return False
+
+        def flat(m):
+            return N.i64_array([x for row in m for x in row]) if m is not None else None
+        check(N.lib.mp4j_thread_collective(self._tg, self.processCommSlave._h, self.getThreadId(), kind, a.ctypes.data,
+                                           operand.code, operator.code if operator is not None else N.COPY, from_, to,
+                                           flat(lo), flat(hi), flat(counts), rootRank, rootThreadId))
+        return True
+
     def _real_root(self, rootRank, rootThreadId):
         if rootThreadId < 0 or rootThreadId >= self._T:
             raise Mp4jException("rootThreadId out of range")
@@ -180,6 +201,9 @@ class ThreadCommSlave:
         CommUtils.isfromsTosLegal(sendfroms, sendtos, self._T)
         rr = self._real_root(rootRank, rootThreadId)
         r = self.getRank()
+        if self._native_thread(_GATHER, arrData, operand, None, lo=sendfroms, hi=sendtos, rootRank=rootRank,
+                               rootThreadId=rootThreadId):
+            return arrData
 
         def run(arrs):
             for t in range(self._T):  # thread merge into the delegate's array (DOP:400-419)
@@ -197,6 +221,8 @@ class ThreadCommSlave:
         CommUtils.isfromsTosLegal(sendfroms, sendtos, self._T)
         r = self.getRank()
         pf, pt = CommUtils.getProcessFroms(sendfroms), CommUtils.getProcessTos(sendtos)
+        if self._native_thread(_ALL_GATHER, arrData, operand, None, lo=sendfroms, hi=sendtos):
+            return arrData
 
         def run(arrs):
             for t in range(1, self._T):
@@ -213,6 +239,10 @@ class ThreadCommSlave:
         if self._T == 1:
             return self.processCommSlave.broadcastArray(arrData, operand, from_, to, rootRank)
         rr = self._real_root(rootRank, rootThreadId)
+        CommUtils.isFromToLegal(from_, to)
+        if self._native_thread(_BROADCAST, arrData, operand, None, from_, to, rootRank=rootRank,
+                               rootThreadId=rootThreadId):
+            return arrData
 
         def run(arrs):
             self.processCommSlave.broadcastArray(arrs[rr], operand, from_, to, rootRank)
@@ -229,6 +259,9 @@ class ThreadCommSlave:
         CommUtils.isfromsTosLegal(recvfroms, recvtos, self._T)
         rr = self._real_root(rootRank, rootThreadId)
         r = self.getRank()
+        if self._native_thread(_SCATTER, arrData, operand, None, lo=recvfroms, hi=recvtos, rootRank=rootRank,
+                               rootThreadId=rootThreadId):
+            return arrData
 
         def run(arrs):
             self.processCommSlave.scatterArray(arrs[rr], operand, CommUtils.getProcessFroms(recvfroms),
@@ -248,6 +281,8 @@ class ThreadCommSlave:
         r = self.getRank()
         pcounts = [sum(c) for c in counts]
         total_to = from_ + sum(pcounts)
+        if self._native_thread(_REDUCE_SCATTER, arrData, operand, operator, from_, total_to, counts=counts):
+            return arrData
 
         def run(arrs):
             self._local_reduce(arrs, operand, operator, from_, total_to, 0)
@@ -264,6 +299,10 @@ class ThreadCommSlave:
         if self._T == 1:
             return self.processCommSlave.reduceArray(arrData, operand, operator, from_, to, rootRank)
         rr = self._real_root(rootRank, rootThreadId)
+        CommUtils.isFromToLegal(from_, to)
+        if self._native_thread(_REDUCE, arrData, operand, operator, from_, to, rootRank=rootRank,
+                               rootThreadId=rootThreadId):
+            return arrData
 
         def run(arrs):
             self._local_reduce(arrs, operand, operator, from_, to, rr)
