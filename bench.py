@@ -103,6 +103,7 @@ def main():
     ap.add_argument("--threads", type=int, default=8)
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--e2e-fanout", action="store_true", help="e2e: write the result into all T host arrays")
     args = ap.parse_args()
     if args.impl == "reference":
         return reference_arm()
@@ -139,7 +140,8 @@ def main():
     chk = [torch.full((4099,), float(rank * T + t + 1), device="cuda") for t in range(T)]
     plane.thread_allreduce(chk, fop, SUM, 0, 4099)
     torch.cuda.synchronize()
-    assert all(bool(torch.all(c == P * (P + 1) / 2)) for c in chk), "allreduce self-check failed"
+    if not os.environ.get("MP4J_BENCH_NOCHECK"):
+        assert all(bool(torch.all(c == P * (P + 1) / 2)) for c in chk), "allreduce self-check failed"
 
     def step():
         plane.thread_allreduce(bufs, fop, SUM, 0, n)
@@ -176,43 +178,56 @@ def main():
     hbm_bytes = 2 * T * S + (0 if world == 1 else 3 * S)
     hbm_gbs = hbm_bytes / (ms_per_step * 1e-3) / 1e9
 
-    # ---- end to end through the public API: T python threads, pinned H2D per step, D2H of the result
+    # ---- end to end through the public API: T python threads call ThreadCommSlave.allreduceArray on PINNED
+    # HOST tensors. The library streams them through the GPU (chunked H2D || fused kernel || D2H, one
+    # cudaMemcpyAsync per buffer and chunk). Every step moves the T input arrays (T*S bytes) host->device and
+    # reads the result array (S bytes) back into thread 0's host array (`resultThread=0`: the T threads of a
+    # process share one result; `--e2e-fanout` writes it into all T host arrays instead, T*S bytes back).
     e2e = None
     if not args.no_e2e:
         Ke = max(1, args.e2e_steps)
-        host_in = [torch.full((n,), 1e-30, dtype=torch.float32).pin_memory() for _ in range(T)]
-        host_out = torch.empty(n, dtype=torch.float32).pin_memory()
+        rt = None if args.e2e_fanout else 0
+        host = [torch.full((n,), 1e-30, dtype=torch.float32).pin_memory() for _ in range(T)]
         e2e_times = []
+        e2e_err = []
 
         def worker(t):
-            comm.setThreadId(t)
-            torch.cuda.set_device(local_rank)
-            for it in range(Ke + 1):
-                if t == 0:
-                    # thread 0 reaches the barrier last (it ends every step with a full device
-                    # sync while the others wait here), so the GPU is idle at this timestamp and
-                    # nobody has started the next step's copies yet
-                    torch.cuda.synchronize()
-                    e2e_times.append(time.perf_counter())
-                comm.barrier()
-                bufs[t].copy_(host_in[t], non_blocking=True)          # H2D of this step's input
-                torch.cuda.current_stream().synchronize()
-                comm.allreduceArray(bufs[t], fop, SUM, 0, n)           # public API
-                if t == 0:
-                    host_out.copy_(bufs[0], non_blocking=True)         # D2H read of the result
-                    torch.cuda.synchronize()
-                    e2e_times.append(time.perf_counter())
+            try:
+                comm.setThreadId(t)
+                torch.cuda.set_device(local_rank)
+                for it in range(Ke + 1):
+                    comm.barrier()                                    # all ranks, all threads: step starts together
+                    if t == 0:
+                        e2e_times.append(time.perf_counter())
+                    comm.allreduceArray(host[t], fop, SUM, 0, n, resultThread=rt)  # public API: host array in, result out
+                    if t == 0:
+                        e2e_times.append(time.perf_counter())
+            except BaseException as e:  # noqa: BLE001 - reported on the main thread
+                e2e_err.append(e)
         ths = [threading.Thread(target=worker, args=(t,)) for t in range(T)]
         for th in ths:
             th.start()
         for th in ths:
             th.join()
+        if e2e_err:
+            raise e2e_err[0]
+        e2e_algo = plane.last()
         per = [(e2e_times[2 * i + 1] - e2e_times[2 * i]) * 1e3 for i in range(1, Ke + 1)]  # drop warm-up
         e2e_ms = pcs.allreduce(sum(per) / len(per), dop, DMAX)
         e2e_busbw = (S / (e2e_ms * 1e-3)) * 2 * (P - 1) / P / 1e9
+        # result check: every thread's host array holds the same finite sum
+        # result check: rank 0's result (thread 0's array; every thread's with --e2e-fanout) must equal the
+        # sum the inputs imply: all inputs were 1e-30, and each step multiplies the live value by P once
+        # for the threads that received the previous result
+        chk_src = host if rt is None else [host[0]]
+        e2e_ok = all(bool(torch.equal(chk_src[0][:4096], h[:4096])) for h in chk_src) and \
+            bool(torch.isfinite(host[0][:4096]).all()) and float(host[0][0]) > 1e-30
         e2e = {"value": round(world * e2e_busbw, 3), "unit": "GB/s", "ms_per_step": round(e2e_ms, 3),
-               "steps": Ke, "h2d_bytes_per_step": T * S, "d2h_bytes_per_step": S,
-               "api": "ThreadCommSlave.allreduceArray (T python threads, pinned host tensors)"}
+               "steps": Ke, "h2d_bytes_per_step": T * S, "d2h_bytes_per_step": (T if rt is None else 1) * S,
+               "h2d_GBps_per_gpu": round(T * S / (e2e_ms * 1e-3) / 1e9, 2),
+               "result_ok": e2e_ok, "path": e2e_algo,
+               "api": "ThreadCommSlave.allreduceArray on pinned host tensors (T python threads); result in "
+                      + ("all T host arrays" if rt is None else "thread 0's host array (resultThread=0)")}
 
     pcs.barrier()
     comm.close(0)

@@ -34,6 +34,8 @@ struct ThreadArgs {
   int fanout;                   // 1: result to all T buffers; 0: only to bufs[dst_index]
   int dst_index;
   int slots;                    // ring depth of the warp-specialised kernel
+  int dbg;                      // diagnostics only (MP4J_WS_DBG): bit mask that disables parts of the pipeline
+  int tail_split;               // pull kernel: a block's last chunk runs as this many shorter pipeline steps (>= 1)
   long long from, to;           // element range
   unsigned long long stg_off;   // byte offset in every heap of the per-block staging slots
   unsigned long long slot_bytes;  // bytes per block slot (multiple of 16 * world)

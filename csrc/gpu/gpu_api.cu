@@ -94,6 +94,12 @@ int mp4j_gpu_last(mp4j_gpu* g, char* buf, size_t n) {
   MP4J_API_END
 }
 
+int mp4j_gpu_set_option(mp4j_gpu* g, const char* name, long long value) {
+  MP4J_API_BEGIN
+  if (!g->g->set_option(name, value)) throw Error(std::string("unknown GPU plane option: ") + name);
+  MP4J_API_END
+}
+
 int mp4j_gpu_alloc(mp4j_gpu* g, size_t bytes, size_t* off) {
   MP4J_API_BEGIN
   *off = g->g->alloc(bytes);
@@ -200,6 +206,13 @@ int mp4j_gpu_thread_allreduce(mp4j_gpu* g, void* const* bufs, int T, int dtype, 
   TraceScope trace_scope(g->g, (cudaStream_t)stream, "mp4j.thread_allreduce");
   g->g->thread_allreduce(bufs, T, dtype, op, from, to, fanout, dst, local_only != 0,
                          (thread_algo & 0xff) | (algo << 16), (cudaStream_t)stream);
+  MP4J_API_END
+}
+
+int mp4j_gpu_thread_allreduce_host(mp4j_gpu* g, void* const* hbufs, int T, int dtype, int op, int64_t from,
+                                   int64_t to, int fanout, int dst, void* stream) {
+  MP4J_API_BEGIN
+  g->g->thread_allreduce_host(hbufs, T, dtype, op, from, to, fanout, dst, (cudaStream_t)stream);
   MP4J_API_END
 }
 

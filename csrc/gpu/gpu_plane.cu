@@ -18,12 +18,13 @@ size_t env_size(const char* name, size_t dflt) {
   return (v && *v) ? (size_t)strtoull(v, nullptr, 10) : dflt;
 }
 size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+}  // namespace
+
 // predefined operators are checked against the dtype table; a custom one against the type it was compiled for
 bool plane_op_ok(int dtype, int op) {
   if (is_custom_op(op)) return custom_op_dtype(op) == dtype;
   return op_valid_for(dtype, op);
 }
-}  // namespace
 
 void GpuOptions::load_env() {
   heap_bytes = env_size("MP4J_HEAP_BYTES", heap_bytes);
@@ -37,6 +38,29 @@ void GpuOptions::load_env() {
   poll_ns = (int)env_size("MP4J_POLL_NS", (size_t)poll_ns);
   if (getenv("MP4J_NVLS")) want_multicast = atoi(getenv("MP4J_NVLS")) != 0;
   if (getenv("MP4J_GPU_TIMEOUT_S")) timeout_s = atof(getenv("MP4J_GPU_TIMEOUT_S"));
+  host_chunk_bytes = env_size("MP4J_HOST_CHUNK_BYTES", host_chunk_bytes);
+  ws_ver = (int)env_size("MP4J_WS_VER", (size_t)ws_ver);
+  ws_tail_split = (int)env_size("MP4J_WS_TAIL_SPLIT", (size_t)ws_tail_split);
+  ws_dbg = (int)env_size("MP4J_WS_DBG", (size_t)ws_dbg);
+}
+
+bool GpuPlane::set_option(const std::string& name, long long v) {
+  if (name == "ws_ver") opt_.ws_ver = (int)v;
+  else if (name == "ws_dbg") opt_.ws_dbg = (int)v;
+  else if (name == "ws_tail_split") opt_.ws_tail_split = std::max(1, (int)v);
+  else if (name == "thread_slots") opt_.thread_slots = std::max(2, std::min((int)v, thread_ws_slots()));
+  else if (name == "thread_slot_bytes") opt_.thread_slot_bytes = align_up((size_t)v, 16 * 8 * 8);
+  else if (name == "nvls_min_world") opt_.nvls_min_world = (int)v;
+  else if (name == "nvls_min_bytes") opt_.nvls_min_bytes = (size_t)v;
+  else if (name == "oneshot_max_bytes") opt_.oneshot_max_bytes = std::min((size_t)v, oneshot_slot_bytes_);
+  else if (name == "max_blocks") opt_.max_blocks = (int)v;
+  else if (name == "poll_ns") opt_.poll_ns = (int)v;
+  else if (name == "host_chunk_bytes") {
+    hpipe_release();
+    opt_.host_chunk_bytes = (size_t)v;
+  }
+  else return false;
+  return true;
 }
 
 GpuPlane* GpuPlane::create_real(ProcessComm* pc, int device, GpuOptions opt) {
@@ -79,7 +103,9 @@ void GpuPlane::finish_init(GpuOptions opt) {
   opt_.thread_slot_bytes = align_up(opt_.thread_slot_bytes, 16 * 8 * 8);
   thread_off_ = align_up(off, 4096);
   opt_.thread_slots = std::max(2, std::min(opt_.thread_slots, thread_ws_slots()));
-  thread_bytes_ = (size_t)std::max(tgrid, sms_ * opt_.thread_slots) * opt_.thread_slot_bytes;
+  // room for the deepest ring of the sweeps (8 slots of >= 64 KiB per SM), so set_option() can retune in place
+  thread_bytes_ = (size_t)std::max(tgrid, sms_ * std::max(opt_.thread_slots, thread_ws_slots())) *
+                  std::max<size_t>(opt_.thread_slot_bytes, 64 << 10);
   off = thread_off_ + thread_bytes_;
   staging_off_ = align_up(off, 4096);
   opt_.staging_bytes = align_up(opt_.staging_bytes, 4096);
@@ -98,6 +124,7 @@ void GpuPlane::host_barrier() {
 GpuPlane::~GpuPlane() {
   cudaDeviceSynchronize();
   map_release();
+  hpipe_release();
   for (float* a : hist_amax_)
     if (a) cudaFree(a);
   for (float* a : lr_scratch_)
@@ -475,15 +502,25 @@ void GpuPlane::thread_allreduce(void* const* bufs, int T, int dtype, int op, int
   a.tab = table();
   for (int i = 0; i < L; ++i)
     for (int t = 0; t < T; ++t) a.bufs[i][t] = bufs[i * T + t];
-  // ---- preferred: warp-specialised kernel (HBM read / NVLink / HBM write overlap inside each SM)
-  bool ws = vec && (algo & 0xff) == 0 && (nbytes % 32) == 0 && thread_local_fast_supported(dtype, op, T);
+  // ---- preferred: warp-specialised kernels (HBM read / NVLink / HBM write overlap inside each SM):
+  // the TMA formulation (any T, 16-byte aligned) or the register formulation (T in {2,4,8}, 32-byte aligned)
+  const int ws_ver = opt_.ws_ver, ws_dbg = opt_.ws_dbg;
+  // thread_algo: 0 = pick, 4 = TMA formulation, 5 = register formulation with pushes, 6 = register formulation
+  // with pulls (3 = chunk-synchronous fallback below)
+  const int talgo = algo & 0xff;
+  bool ws = vec && (talgo == 0 || talgo == 5 || talgo == 6) && (nbytes % 32) == 0 &&
+            thread_local_fast_supported(dtype, op, T);
   for (int i = 0; ws && i < L * T; ++i)
     if ((((uintptr_t)bufs[i] + (size_t)from * es) & 31) != 0) ws = false;
-  if (ws) {
+  const bool tma = vec && (talgo == 0 || talgo == 4) && thread_fused_tma_supported(dtype, op, T) &&
+                   (talgo == 4 || ws_ver == 2 || !ws);
+  if (ws || tma) {
     const size_t wslot = opt_.thread_slot_bytes / 32 * 32;
     a.slot_bytes = wslot;
     a.slots = opt_.thread_slots;
     a.stg_off = thread_off_;
+    a.dbg = ws_dbg;
+    a.tail_split = std::max(1, opt_.ws_tail_split);
     long long wcap = sms_;
     if (emulated()) wcap /= p;
     wcap = std::min<long long>(wcap, (long long)(thread_bytes_ / (wslot * opt_.thread_slots)));
@@ -492,8 +529,16 @@ void GpuPlane::thread_allreduce(void* const* bufs, int T, int dtype, int op, int
     const int wgrid = (int)std::max<long long>(1, std::min<long long>(wcap, (long long)((nbytes + wslot - 1) / wslot)));
     const bool wnvls = has_multicast() && nvls_supported(dtype, op) &&
                        (algo >> 16 == MP4J_ALGO_NVLS || (algo >> 16 == MP4J_ALGO_AUTO && nvls_auto(nbytes)));
-    last_ = CollStat{"thread_allreduce", wnvls ? "fused-ws-nvls" : "fused-ws-p2p", nbytes, wgrid, false};
-    launch_thread_fused_ws(dtype, op, wnvls, a, wgrid, s);
+    if (tma) {
+      last_ = CollStat{"thread_allreduce", wnvls ? "fused-tma-nvls" : "fused-tma-p2p", nbytes, wgrid, false};
+      launch_thread_fused_tma(dtype, op, wnvls, a, wgrid, s);
+    } else if (talgo == 6 || (talgo == 0 && ws_ver == 3)) {
+      last_ = CollStat{"thread_allreduce", wnvls ? "fused-pull-nvls" : "fused-pull-p2p", nbytes, wgrid, false};
+      launch_thread_fused_pull(dtype, op, wnvls, a, wgrid, s);
+    } else {
+      last_ = CollStat{"thread_allreduce", wnvls ? "fused-ws-nvls" : "fused-ws-p2p", nbytes, wgrid, false};
+      launch_thread_fused_ws(dtype, op, wnvls, a, wgrid, s);
+    }
     return;
   }
   const size_t slot = opt_.thread_slot_bytes / (16 * p) * (16 * p);

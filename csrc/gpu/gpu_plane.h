@@ -18,6 +18,7 @@
 namespace mp4j {
 
 class ProcessComm;
+bool plane_op_ok(int dtype, int op);  // operator defined for this dtype on the GPU paths
 
 struct GpuOptions {
   size_t heap_bytes = 1ull << 30;       // MP4J_HEAP_BYTES
@@ -34,6 +35,10 @@ struct GpuOptions {
   int max_blocks = 0;                   // 0 = occupancy-derived (MP4J_MAX_BLOCKS)
   int poll_ns = 0;                      // sleep between device-side flag polls (MP4J_POLL_NS)
   double timeout_s = 60.0;              // device-side flag-wait watchdog (MP4J_GPU_TIMEOUT_S)
+  size_t host_chunk_bytes = 8ull << 20; // per-buffer chunk of the host-array pipeline (MP4J_HOST_CHUNK_BYTES)
+  int ws_tail_split = 4;                // pull kernel: steps the last chunk of a block is cut into (MP4J_WS_TAIL_SPLIT)
+  int ws_ver = 1;                       // fused thread kernel: 1 = register formulation, 2 = TMA (MP4J_WS_VER)
+  int ws_dbg = 0;                       // diagnostics bit mask for the fused thread kernels (MP4J_WS_DBG)
   void load_env();
 };
 
@@ -56,6 +61,8 @@ class GpuPlane {
   bool emulated() const { return heap_.emulated(); }
   bool has_multicast() const { return heap_.mc_base() != nullptr; }
   std::string describe() const;
+  // run-time tuning knob (sweeps): returns false for an unknown name. All ranks must set the same values.
+  bool set_option(const std::string& name, long long value);
   const CollStat& last() const { return last_; }
   CollTrace& trace() { return trace_; }  // per-collective CUDA-event timing + NVTX (MP4J_TRACE=1)
 
@@ -78,6 +85,13 @@ class GpuPlane {
   // local_only: skip the inter-GPU step (intra-process thread reduce, DOP:441-457).
   void thread_allreduce(void* const* bufs, int T, int dtype, int op, int64_t from, int64_t to, int fanout, int dst,
                         bool local_only, int algo, cudaStream_t s);
+  // Host arrays through the GPU plane (the reference's arrays ARE host arrays, PCS:1733 / TCS:1915): the
+  // range is cut into chunks; chunk c+1 is copied in (one cudaMemcpyAsync per buffer on a copy stream)
+  // while the fused kernel reduces chunk c and chunk c-1 is copied out on a third stream. hbufs[local_rank *
+  // T + t] are host pointers (pinned for full speed). fanout=1: the result lands in every thread's host
+  // array, else only in thread `dst`'s. Synchronous: returns when the host arrays hold the result.
+  void thread_allreduce_host(void* const* hbufs, int T, int dtype, int op, int64_t from, int64_t to, int fanout,
+                             int dst, cudaStream_t s);
   // K8: fp32 SUM allreduce whose payload crosses NVLink as bf16 or block-scaled fp8 (lossy, opt-in).
   void allreduce_wire(float* const* arrs, int64_t from, int64_t to, int wire, cudaStream_t s);
   // Raises if a kernel reported a peer-wait timeout since the last check.
@@ -155,6 +169,7 @@ class GpuPlane {
   std::mutex alloc_mu_;
   std::map<size_t, size_t> used_;  // off -> bytes
   CollStat last_;
+  std::string last_algo_store_;  // backing store when last_.algo is composed at run time
   CollTrace trace_;
   size_t lr_shard_off_ = 0, lr_shard_bytes_ = 0;
   size_t lr_recv_off_ = 0, lr_recv_bytes_ = 0;
@@ -165,6 +180,9 @@ class GpuPlane {
   int lr_tiles_[kMaxRanks] = {};
   size_t hist_shard_off_ = 0, hist_shard_bytes_ = 0;
   float* hist_amax_[kMaxRanks] = {};
+  struct HostPipe;
+  HostPipe* hpipe_ = nullptr;
+  void hpipe_release();
   struct MapWork;
   MapWork* map_ = nullptr;
   void map_release();

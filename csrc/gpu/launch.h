@@ -23,6 +23,11 @@ bool thread_local_fast_supported(int dtype, int op, int T);  // algo 2: static-T
 // thread_fused_ws.cu: warp-specialised fused kernel (world > 1, 32-byte aligned, T in {2,4,8},
 // SUM/MAX/MIN on 4/8-byte types). One CTA per SM; needs grid * slots * slot_bytes of staging.
 void launch_thread_fused_ws(int dtype, int op, bool nvls, const ThreadArgs& args, int grid, cudaStream_t stream);
+// thread_fused_tma.cu: the same pipeline with TMA bulk copies for the HBM streams (any T <= 64, 16-byte aligned)
+void launch_thread_fused_tma(int dtype, int op, bool nvls, const ThreadArgs& args, int grid, cudaStream_t stream);
+bool thread_fused_tma_supported(int dtype, int op, int T);
+// thread_fused_pull.cu: pull formulation (no remote stores, no system-scope release); same preconditions as _ws
+void launch_thread_fused_pull(int dtype, int op, bool nvls, const ThreadArgs& args, int grid, cudaStream_t stream);
 int thread_ws_slots();
 int thread_ws_max_blocks();
 

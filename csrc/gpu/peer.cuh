@@ -29,8 +29,14 @@ constexpr size_t kSigWsEpochOff = kSigEpochOff + 4096;
 constexpr size_t kSigWsFaOff = kSigWsEpochOff + 4096;
 constexpr size_t kSigWsFbOff = kSigWsFaOff + kWsMaxBlocks * kMaxRanks * sizeof(uint32_t);
 constexpr size_t kSigWsEnd = kSigWsFbOff + (size_t)kWsMaxBlocks * kWsMaxSlots * kMaxRanks * sizeof(uint32_t);
-constexpr size_t kSigPadBytes = 128 * 1024;           // everything above, zero-initialised once
-static_assert(kSigWsEnd <= kSigPadBytes, "signal pad layout overflows");
+// FC (pull formulation, thread_fused_pull.cu): "rank r has pulled what it needs of chunk k from this slot"
+constexpr size_t kSigWsFcOff = kSigWsEnd;
+constexpr size_t kSigWsFcEnd = kSigWsFcOff + (size_t)kWsMaxBlocks * kWsMaxSlots * kMaxRanks * sizeof(uint32_t);
+constexpr size_t kSigPadBytes = 256 * 1024;           // everything above, zero-initialised once
+// diagnostics (MP4J_WS_DBG bit 128): per-chunk stage timestamps of block 0, kWsTraceChunks x 8 x u64
+constexpr size_t kSigWsTraceOff = kSigWsFcEnd;
+constexpr int kWsTraceChunks = 64;
+static_assert(kSigWsTraceOff + kWsTraceChunks * 8 * 8 <= kSigPadBytes, "signal pad layout overflows");
 
 struct PeerTable {
   int world;
@@ -49,6 +55,9 @@ __device__ __forceinline__ int my_rank(const PeerTable& t) { return t.emulate ? 
 // ---- system-scope flag access
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
   asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void st_relaxed_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
   uint32_t v;

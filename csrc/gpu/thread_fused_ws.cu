@@ -44,11 +44,21 @@ __device__ __forceinline__ void named_bar(int id, int nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
 
+
+// diagnostics: stage timestamps of block 0 (dbg bit 128), read back by tools/ws_trace.py
+#define WS_TRACE(ev, k)                                                                                  \
+  do {                                                                                                   \
+    if ((a.dbg & 128) && blockIdx.x == 0 && (k) < kWsTraceChunks)                                        \
+      ((unsigned long long*)((char*)tab.sig[rank] + kSigWsTraceOff))[(k) * 8 + (ev)] = globaltimer_ns(); \
+  } while (0)
+
 template <typename T, int OP, bool NVLS, int NT, typename SP>
 __global__ void __launch_bounds__(SP::kWsThreads, 1) thread_fused_ws_kernel(const __grid_constant__ ThreadArgs a) {
   constexpr int kThreadsA = SP::kThreadsA, kThreadsB = SP::kThreadsB, kThreadsC = SP::kThreadsC;
   __shared__ volatile unsigned c_done;  // chunks finished by group C (slot recycling)
-  __shared__ unsigned a_cnt;            // (warp, chunk) pairs finished by group A (consumed by the signal warp)
+  // arrivals of the phase-A warps per ring slot. Per SLOT, not one running total: a warp that is a chunk ahead
+  // of a slow one must not complete the slow warp's chunk (a warp cannot lap the ring, so per-slot counts are exact)
+  __shared__ unsigned a_cnt[kWsMaxSlots];
   const PeerTable& tab = a.tab;
   const int rank = my_rank(tab);
   const int world = tab.world;
@@ -65,7 +75,7 @@ __global__ void __launch_bounds__(SP::kWsThreads, 1) thread_fused_ws_kernel(cons
   const unsigned long long ring_off = a.stg_off + (unsigned long long)blockIdx.x * kSlots * a.slot_bytes;
   if (threadIdx.x == 0) {
     c_done = 0;
-    a_cnt = 0;
+    for (int i = 0; i < kWsMaxSlots; ++i) a_cnt[i] = 0;
   }
   __syncthreads();
 
@@ -87,7 +97,7 @@ __global__ void __launch_bounds__(SP::kWsThreads, 1) thread_fused_ws_kernel(cons
         __syncwarp();
       }
       char* slot = tab.heap[rank] + ring_off + (unsigned long long)(k % kSlots) * a.slot_bytes;
-      for (int v = tid; v < nv; v += kThreadsA) {
+      for (int v = tid; v < ((a.dbg & 4) ? 0 : nv); v += kThreadsA) {
         const unsigned long long o = b0 + off + (unsigned long long)v * 32;
         Vec32 x[NT];
 #pragma unroll
@@ -97,12 +107,13 @@ __global__ void __launch_bounds__(SP::kWsThreads, 1) thread_fused_ws_kernel(cons
           x[0].lo = vec_reduce<T, OP>(x[0].lo, x[t].lo);
           x[0].hi = vec_reduce<T, OP>(x[0].hi, x[t].hi);
         }
-        st_keep32(slot + (unsigned long long)v * 32, x[0]);
+        if (!(a.dbg & 32)) st_keep32(slot + (unsigned long long)v * 32, x[0]);
       }
       __syncwarp();
       if (lane == 0) {
         __threadfence_block();  // the warp's slot stores are ordered before the count
-        atomicAdd(&a_cnt, 1u);
+        atomicAdd(&a_cnt[k % kSlots], 1u);
+        if (tid == 0) WS_TRACE(0, k);
       }
     }
   } else if (tid >= kThreadsA + kThreadsB + kThreadsC) {
@@ -111,11 +122,13 @@ __global__ void __launch_bounds__(SP::kWsThreads, 1) thread_fused_ws_kernel(cons
     constexpr unsigned WA = kThreadsA / 32;
     for (long long k = 0; k < mine; ++k) {
       if (lane < world) {
-        while (*(volatile unsigned*)&a_cnt < WA * (unsigned)(k + 1)) {
+        while (*(volatile unsigned*)&a_cnt[k % kSlots] < WA * (unsigned)(k / kSlots + 1)) {
         }
         __threadfence_block();
+        if (lane == 0) WS_TRACE(1, k);
         st_release_sys((uint32_t*)((char*)tab.sig[lane] + kSigWsFaOff) + blockIdx.x * kMaxRanks + rank,
                        base + (uint32_t)k + 1u);
+        if (lane == 0) WS_TRACE(2, k);
       }
     }
   } else if (tid < kThreadsA + kThreadsB) {
@@ -130,17 +143,19 @@ __global__ void __launch_bounds__(SP::kWsThreads, 1) thread_fused_ws_kernel(cons
       const long long c = blockIdx.x + k * gridDim.x;
       const long long off = c * ch;
       const int nv16 = (int)(min(ch, nbytes - off) / 16);
-      if (lane < world)
+      if (lane < world && (!(a.dbg & 2) || lane == rank))
         wait_flag(tab, (uint32_t*)((char*)tab.sig[rank] + kSigWsFaOff) + blockIdx.x * kMaxRanks + lane,
                   base + (uint32_t)k + 1u);
       __syncwarp();
+      if (lane == 0) WS_TRACE(3, k);
       const int sl = (int)(k % kSlots);
       const unsigned long long so = ring_off + (unsigned long long)sl * a.slot_bytes;
       const int lo = (int)((long long)nv16 * rank / world), hi = (int)((long long)nv16 * (rank + 1) / world);
       // An NVLink round trip is ~2-3 us: keep kBatch independent 16-byte requests in flight per
       // thread (the asm volatile accessors are never reordered, so batching is explicit).
       constexpr int kBatch = 8;
-      for (int v0 = lo + lane; v0 < hi; v0 += 32 * kBatch) {
+      const bool loc = (a.dbg & 8) != 0;
+      for (int v0 = lo + lane; v0 < ((a.dbg & 1) ? lo : hi); v0 += 32 * kBatch) {
         Vec16 acc[kBatch];
         if constexpr (NVLS) {
 #pragma unroll
@@ -155,6 +170,7 @@ __global__ void __launch_bounds__(SP::kWsThreads, 1) thread_fused_ws_kernel(cons
           }
         } else {
           for (int q = 0; q < world; ++q) {  // ascending rank order => identical bits on every rank
+            if (loc && q != rank) continue;
             Vec16 x[kBatch];
 #pragma unroll
             for (int j = 0; j < kBatch; ++j) {
@@ -162,9 +178,10 @@ __global__ void __launch_bounds__(SP::kWsThreads, 1) thread_fused_ws_kernel(cons
               if (v < hi) x[j] = ld_coherent(tab.heap[q] + so + (unsigned long long)v * 16);
             }
 #pragma unroll
-            for (int j = 0; j < kBatch; ++j) acc[j] = (q == 0) ? x[j] : vec_reduce<T, OP>(acc[j], x[j]);
+            for (int j = 0; j < kBatch; ++j) acc[j] = (q == 0 || loc) ? x[j] : vec_reduce<T, OP>(acc[j], x[j]);
           }
           for (int q = 0; q < world; ++q) {
+            if (loc && q != rank) continue;
 #pragma unroll
             for (int j = 0; j < kBatch; ++j) {
               const int v = v0 + j * 32;
@@ -174,10 +191,12 @@ __global__ void __launch_bounds__(SP::kWsThreads, 1) thread_fused_ws_kernel(cons
         }
       }
       __syncwarp();  // the warp's stores precede the release below
+      if (lane == 0) WS_TRACE(4, k);
       if (lane < world)
         st_release_sys((uint32_t*)((char*)tab.sig[lane] + kSigWsFbOff) +
                            ((size_t)blockIdx.x * kWsMaxSlots + sl) * kMaxRanks + rank,
                        base + (uint32_t)k + 1u);
+      if (lane == 0) WS_TRACE(5, k);
     }
   } else {
     // ================= group C: fan the finished slot out to the T thread buffers
@@ -186,14 +205,16 @@ __global__ void __launch_bounds__(SP::kWsThreads, 1) thread_fused_ws_kernel(cons
       const long long c = blockIdx.x + k * gridDim.x;
       const long long off = c * ch;
       const int nv = (int)(min(ch, nbytes - off) / 32);
-      if (ct < world)
+      if (ct < world && (!(a.dbg & 2) || ct == rank))
         wait_flag(tab, (uint32_t*)((char*)tab.sig[rank] + kSigWsFbOff) +
                            ((size_t)blockIdx.x * kWsMaxSlots + (int)(k % kSlots)) * kMaxRanks + ct,
                   base + (uint32_t)k + 1u);
       named_bar(3, kThreadsC);
+      if (ct == 0) WS_TRACE(6, k);
       const char* slot = tab.heap[rank] + ring_off + (unsigned long long)(k % kSlots) * a.slot_bytes;
-      for (int v = ct; v < nv; v += kThreadsC) {
-        const Vec32 x = ld_coherent32(slot + (unsigned long long)v * 32);
+      for (int v = ct; v < ((a.dbg & 4) ? 0 : nv); v += kThreadsC) {
+        Vec32 x{};
+        if (!(a.dbg & 16)) x = ld_coherent32(slot + (unsigned long long)v * 32);
         const unsigned long long o = b0 + off + (unsigned long long)v * 32;
         if (a.fanout) {
 #pragma unroll
@@ -204,6 +225,7 @@ __global__ void __launch_bounds__(SP::kWsThreads, 1) thread_fused_ws_kernel(cons
       }
       named_bar(3, kThreadsC);  // slot fully consumed
       if (ct == 0) c_done = (unsigned)(k + 1);
+      if (ct == 0) WS_TRACE(7, k);
     }
   }
   __syncthreads();

@@ -30,6 +30,10 @@ int mp4j_gpu_free(mp4j_gpu* g, size_t off);
 void* mp4j_gpu_ptr(mp4j_gpu* g, int rank, size_t off);
 /* Throws away nothing: returns MP4J_ERR if a kernel reported a peer-wait timeout. */
 int mp4j_gpu_check(mp4j_gpu* g);
+/* Run-time tuning knob for sweeps (the environment variables of INTEGRATION.md without the MP4J_ prefix, lower
+ * case: thread_slots, thread_slot_bytes, ws_ver, nvls_min_world, nvls_min_bytes, oneshot_max_bytes, max_blocks,
+ * poll_ns). Every rank must set the same value before the next collective. No counterpart in the reference. */
+int mp4j_gpu_set_option(mp4j_gpu* g, const char* name, long long value);
 
 int mp4j_gpu_allreduce(mp4j_gpu* g, void* const* arrs, int dtype, int op, int64_t from, int64_t to, int algo,
                        void* stream);                                                   /* PCS:1733 */
@@ -76,6 +80,15 @@ int mp4j_gpu_allreduce_wire(mp4j_gpu* g, void* const* arrs, int64_t from, int64_
 int mp4j_gpu_thread_allreduce(mp4j_gpu* g, void* const* bufs, int T, int dtype, int op, int64_t from,
                               int64_t to, int fanout, int dst, int local_only, int thread_algo, int algo,
                               void* stream);
+
+/* ThreadCommSlave.allreduceArray / ProcessCommSlave.allreduceArray (T = 1) on HOST arrays, streamed through
+ * the GPU plane (TCS:1915, PCS:1733: the reference's arrays are host arrays): hbufs[local_rank * T + t] are host
+ * pointers, pinned for full speed. The range is cut into chunks (MP4J_HOST_CHUNK_BYTES per buffer, default 8 MiB);
+ * the copy-in of chunk c+1, the fused kernel of chunk c and the copy-out of chunk c-1 overlap on three streams.
+ * fanout = 1 leaves the result in every thread's array, 0 only in thread `dst`'s. Returns when the host arrays
+ * hold the result (work enqueued on `stream` before the call is waited for first). */
+int mp4j_gpu_thread_allreduce_host(mp4j_gpu* g, void* const* hbufs, int T, int dtype, int op, int64_t from,
+                                   int64_t to, int fanout, int dst, void* stream);
 
 /* Sparse (map container) collectives on (int64 key, value) device arrays: allreduceMap (mode 0,
  * PCS:2053), reduceScatterMap (mode 1, PCS:1299: every rank receives the keys it owns) and

@@ -132,7 +132,7 @@ def test_thread_local_variants_agree(planes, thread_algo, name):
 
 
 @pytest.mark.parametrize("world,T", [(2, 8), (4, 4), (8, 2)])
-@pytest.mark.parametrize("thread_algo,name", [(0, "fused-ws"), (3, "fused-p2p")])
+@pytest.mark.parametrize("thread_algo,name", [(5, "fused-ws"), (6, "fused-pull"), (4, "fused-tma"), (3, "fused-p2p")])
 def test_thread_fused_variants_agree(planes, world, T, thread_algo, name):
     """Warp-specialised kernel vs chunk-synchronous fallback: identical bits, several chunks per block."""
     plane = planes(world)
@@ -150,3 +150,41 @@ def test_thread_fused_variants_agree(planes, world, T, thread_algo, name):
             for t in range(T):
                 assert torch.equal(dev[r][t].cpu(), want), (rep, r, t)
         host = [[want.clone() for _ in range(T)] for _ in range(world)]
+
+
+@pytest.mark.parametrize("world,T", [(2, 1), (2, 3), (4, 5), (8, 8), (2, 64)])
+@pytest.mark.parametrize("n,f", [(4096, 0), (100004, 0), ((3 << 20) + 8, 4), (1 << 20, 1 << 19)])
+def test_thread_fused_tma_any_T(planes, world, T, n, f):
+    """TMA formulation: run-time T, 16-byte alignment, partial last tiles / chunks, from > 0."""
+    plane = planes(world)
+    if T == 64:
+        n = min(n, 1 << 18)
+        f = min(f, n // 2)
+    g = torch.Generator().manual_seed(n + world * 17 + T)
+    host = [[torch.randn(n, generator=g, dtype=torch.float32) for _ in range(T)] for _ in range(world)]
+    dev = [[h.cuda() for h in row] for row in host]
+    plane.thread_allreduce(dev, N.SUM, f, n, thread_algo=4)
+    torch.cuda.synchronize()
+    plane.check()
+    assert "fused-tma" in plane.last(), plane.last()
+    want = expected([[h[f:] for h in row] for row in host])
+    for r in range(world):
+        for t in range(T):
+            got = dev[r][t].cpu()
+            assert torch.equal(got[f:], want), (r, t)
+            assert torch.equal(got[:f], host[r][t][:f])
+
+
+def test_thread_fused_tma_no_fanout_f64_max(planes):
+    plane = planes(2)
+    T, n = 3, 70000
+    g = torch.Generator().manual_seed(3)
+    host = [[torch.randn(n, generator=g, dtype=torch.float64) for _ in range(T)] for _ in range(2)]
+    dev = [[h.cuda() for h in row] for row in host]
+    plane.thread_allreduce(dev, N.MAX, 0, n, fanout=False, dst=2, thread_algo=4)
+    torch.cuda.synchronize()
+    plane.check()
+    want = expected(host, N.MAX)
+    for r in range(2):
+        assert torch.equal(dev[r][2].cpu(), want)
+        assert torch.equal(dev[r][0].cpu(), host[r][0]) and torch.equal(dev[r][1].cpu(), host[r][1])

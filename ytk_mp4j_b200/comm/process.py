@@ -41,6 +41,11 @@ def _is_cuda(x):
     return _is_torch(x) and x.is_cuda
 
 
+def _is_pinned_host(x):
+    """A pinned CPU tensor: the caller's way of asking for the GPU plane's host-array pipeline."""
+    return _is_torch(x) and not x.is_cuda and x.dim() == 1 and x.is_contiguous() and x.is_pinned()
+
+
 def java_string_hash(key):
     """java.lang.String.hashCode for str keys; ints hash to themselves (Integer.hashCode)."""
     if isinstance(key, str):
@@ -186,6 +191,12 @@ class ProcessCommSlave:
         if operand.np_dtype is not None and a.dtype != np.dtype(operand.np_dtype):
             raise Mp4jException("array dtype %s does not match operand %s" % (a.dtype, operand.name))
         return a
+
+    def _gpu_host_ok(self, arr, operand, operator):
+        """Pinned host tensor + initialised GPU plane + an (operand, operator) pair the fused kernels
+        know: the array is streamed through the GPU instead of the host plane."""
+        return (self._gpu is not None and _is_pinned_host(arr) and operand.is_primitive and operator is not None
+                and operator.is_native and operand.code in (N.F64, N.F32, N.I64, N.I32))
 
     def _native_host(self, arr, operand, operator):
         if not operand.is_primitive:
@@ -532,6 +543,9 @@ class ProcessCommSlave:
             return arrData
         if _is_cuda(arrData):
             self.gpu.allreduce(arrData, operand, operator, from_, to)
+            return arrData
+        if self._gpu_host_ok(arrData, operand, operator):
+            self._gpu.thread_allreduce_host([arrData], operand, operator, from_, to)
             return arrData
         a = self._native_host(arrData, operand, operator)
         if a is not None:

@@ -311,14 +311,31 @@ class ThreadCommSlave:
         self._delegate(arrData, run, rr)
         return arrData
 
-    def allreduceArray(self, arrData, operand, operator, from_=0, to=None):
+    def allreduceArray(self, arrData, operand, operator, from_=0, to=None, resultThread=None):
         """All slaveNum x threadNum arrays are reduced; every thread's array holds the result
-        (TCS:1915-1963). CUDA tensors take the fused thread-reduce + inter-GPU + fan-out kernel."""
+        (TCS:1915-1963). CUDA tensors take the fused thread-reduce + inter-GPU + fan-out kernel; pinned
+        host tensors are streamed through the GPU plane when it is initialised.
+
+        resultThread (an addition; None = the reference's behaviour): when the T threads of a process
+        share the result anyway, name the one thread whose array must hold it on every rank; the other
+        threads' arrays are then unspecified (input or result). On the host-array pipeline this cuts the
+        device->host traffic from T copies of the result to one."""
         if to is None:
             to = len(arrData)
+        if resultThread is not None and not 0 <= resultThread < self._T:
+            raise Mp4jException("resultThread out of range")
         if self._T == 1:
             return self.processCommSlave.allreduceArray(arrData, operand, operator, from_, to)
         CommUtils.isFromToLegal(from_, to)
+        if self.processCommSlave._gpu_host_ok(arrData, operand, operator):
+            # pinned host tensors with the GPU plane up: thread 0 streams all T arrays through the GPU
+            # (H2D || fused kernel || D2H pipeline in the library); every thread's array gets the result
+            def run_host(arrs):
+                self.gpu.thread_allreduce_host(arrs, operand, operator, from_, to, fanout=resultThread is None,
+                                               dst=resultThread or 0)
+                return None
+            self._delegate(arrData, run_host, 0)
+            return arrData
         if not _is_cuda(arrData):
             # host arrays + predefined operator: native path in which ALL T threads take part (each
             # reduces its 1/T slice, each copies its own result) instead of one delegate doing everything

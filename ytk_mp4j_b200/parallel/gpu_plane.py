@@ -40,6 +40,9 @@ _P("mp4j_gpu_reduce", C.c_int, C.c_void_p, N.c_vpp, C.c_int, C.c_int, C.c_int64,
 _P("mp4j_gpu_thread_allreduce", C.c_int, C.c_void_p, N.c_vpp, C.c_int, C.c_int, C.c_int, C.c_int64, C.c_int64,
    C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p)
 
+_P("mp4j_gpu_thread_allreduce_host", C.c_int, C.c_void_p, N.c_vpp, C.c_int, C.c_int, C.c_int, C.c_int64, C.c_int64,
+   C.c_int, C.c_int, C.c_void_p)
+
 _P("mp4j_gpu_map_collective", C.c_int, C.c_void_p, C.c_int, N.c_vpp, N.c_vpp, N.c_i64p, C.c_int64, C.c_int64, C.c_int,
    C.c_int, C.c_int, N.c_vpp, N.c_vpp, N.c_vpp, C.c_void_p)
 
@@ -55,6 +58,7 @@ _P("mp4j_gpu_gbdt_hist_reduce_scatter", C.c_int, C.c_void_p, N.c_vpp, N.c_i64p, 
 _P("mp4j_gpu_allreduce_wire", C.c_int, C.c_void_p, N.c_vpp, C.c_int64, C.c_int64, C.c_int, C.c_void_p)
 _P("mp4j_gpu_custom_op", C.c_int, C.c_void_p, C.c_int, C.c_char_p, C.POINTER(C.c_int))
 _P("mp4j_gpu_trace", C.c_int, C.c_void_p, C.c_int)
+_P("mp4j_gpu_set_option", C.c_int, C.c_void_p, C.c_char_p, C.c_longlong)
 _P("mp4j_gpu_stats", C.c_int, C.c_void_p, C.c_char_p, C.c_size_t, C.c_int)
 _P("mp4j_rtc_compile", C.c_int, C.c_int, C.c_char_p, C.c_int, C.POINTER(C.c_longlong))
 
@@ -122,6 +126,11 @@ def _check_tensor(t):
         raise Mp4jException("GPU collectives need 1-D contiguous CUDA tensors")
 
 
+def _check_host_tensor(t):
+    if t.is_cuda or t.dim() != 1 or not t.is_contiguous():
+        raise Mp4jException("the host-array pipeline needs 1-D contiguous CPU tensors (pinned for full speed)")
+
+
 def _native_op(operator):
     if operator is None:
         return N.COPY
@@ -184,6 +193,10 @@ class _PlaneBase:
         check(N.lib.mp4j_gpu_stats(self._g, buf, len(buf), 1 if reset else 0))
         return json.loads(buf.value.decode())
 
+    def set_option(self, name, value):
+        """Run-time tuning knob (sweeps). Every rank must set the same value before the next collective."""
+        check(N.lib.mp4j_gpu_set_option(self._g, name.encode(), int(value)))
+
     def check(self):
         """Raises if a kernel hit the device-side peer-wait watchdog since the last call."""
         check(N.lib.mp4j_gpu_check(self._g))
@@ -199,6 +212,12 @@ class _PlaneBase:
             t = torch.as_tensor(_RawCuda(ptr, n, N.I16, self), device="cuda:%d" % self.device)
             return t.view(torch.bfloat16)
         return torch.as_tensor(_RawCuda(ptr, n, code, self), device="cuda:%d" % self.device)
+
+    def ws_trace(self, rank=None):
+        """Diagnostics: stage timestamps (ns) written by block 0 of the fused thread kernels when
+        option ws_dbg has bit 128 set; [64 chunks, 8 stages] int64, zero where nothing was recorded."""
+        r = N.lib.mp4j_gpu_rank(self._g) if rank is None else rank
+        return self._wrap(r, 114688 + 65536, 64 * 8, N.I64).view(64, 8)
 
     # raw collectives on lists of tensors (one per local rank)
     def _allreduce(self, ts, code, op, f, t, algo, stream):
@@ -233,6 +252,10 @@ class _PlaneBase:
         check(N.lib.mp4j_gpu_thread_allreduce(self._g, _ptr_array(ts), T, code, op, f, t, 1 if fanout else 0, dst,
                                               1 if local_only else 0, thread_algo, algo, _stream_ptr(stream)))
 
+
+    def _thread_allreduce_host(self, ts, T, code, op, f, t, fanout, dst, stream):
+        check(N.lib.mp4j_gpu_thread_allreduce_host(self._g, _ptr_array(ts), T, code, op, f, t, 1 if fanout else 0, dst,
+                                                   _stream_ptr(stream)))
 
     def _lr_xtr_reduce_scatter(self, xts, rts, stream=None):
         """xts[i]: [F, K] bf16, rts[i]: [C, K] bf16 (one pair per local rank). Returns per local rank the
@@ -438,6 +461,15 @@ class GpuPlane(_PlaneBase):
         self._thread_allreduce(ts, len(ts), _code_of(ts[0], operand), self._op(operator, operand.code), f, to, True, 0, local,
                                self.thread_algo if local else 0, algo, stream)
 
+    def thread_allreduce_host(self, ts, operand, operator, f, to, fanout=True, dst=0, stream=None):
+        """allreduceArray on HOST tensors (one per thread of this process; one tensor = the process-level
+        call): chunked H2D || fused kernel || D2H pipeline inside the library. Pinned tensors run at the
+        PCIe rate. The result lands in every tensor (fanout) or only in ts[dst]. Synchronous."""
+        for t in ts:
+            _check_host_tensor(t)
+        self._thread_allreduce_host(ts, len(ts), _code_of(ts[0], operand), self._op(operator, operand.code), f, to,
+                                    fanout, dst, stream)
+
     def thread_reduce(self, ts, operand, operator, f, to, dst, stream=None):
         """Intra-process reduce of the T buffers into ts[dst] (thread path of DOP:441-457)."""
         for t in ts:
@@ -518,3 +550,11 @@ class EmuPlane(_PlaneBase):
         flat = [x for row in ts_by_rank for x in row]
         self._thread_allreduce(flat, T, _code_of(flat[0]), op, f, t, fanout, dst, local_only, thread_algo, algo,
                                stream)
+
+    def thread_allreduce_host(self, ts_by_rank, op, f, t, fanout=True, dst=0, stream=None):
+        """ts_by_rank: [rank][thread] HOST tensors (see GpuPlane.thread_allreduce_host)."""
+        T = len(ts_by_rank[0])
+        flat = [x for row in ts_by_rank for x in row]
+        for x in flat:
+            _check_host_tensor(x)
+        self._thread_allreduce_host(flat, T, _code_of(flat[0]), op, f, t, fanout, dst, stream)
