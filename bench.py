@@ -42,55 +42,87 @@ def reference_arm():
     return 0
 
 
-class ClockSampler(threading.Thread):
-    """Samples SM clock + throttle reasons of one GPU while the timed region runs."""
+class ClockSampler:
+    """SM clocks + throttle reasons of the job's GPUs DURING the timed region, by the profiling recipe's own
+    tool: one `nvidia-smi --query-gpu=... -lms 5` child process (rank 0 only, all N GPUs), started before
+    the warm-up, killed after the timed steps; only samples whose timestamp lies inside the timed region
+    count. In-process NVML polling is not used: from a thread per rank, or even synchronously between
+    launches, it stalled the launch loop of whichever rank was asking, and every other rank's kernel then
+    waited for that rank inside its timed step (8 GPUs: 0.82 -> 0.89-1.04 ms per step)."""
 
-    def __init__(self, index, period=0.004):
-        super().__init__(daemon=True)
-        self.index, self.period = index, period
-        self.samples, self.reasons, self.max_mhz = [], set(), None
-        self._halt = threading.Event()
-        self._nvml = None
-        try:
-            import pynvml
-            pynvml.nvmlInit()
-            self._nvml = pynvml
-            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
-            phys = int(vis.split(",")[index]) if vis and vis.split(",")[index].isdigit() else index
-            self._h = pynvml.nvmlDeviceGetHandleByIndex(phys)
-            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self._h, pynvml.NVML_CLOCK_SM)
-        except Exception:
-            self._nvml = None
+    FIELDS = ("timestamp,index,clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
 
-    def run(self):
-        if self._nvml is None:
+    def __init__(self, n_gpus, enabled=True):
+        self.proc, self.path = None, None
+        if not enabled or os.environ.get("MP4J_BENCH_NOSAMPLER"):
             return
-        nv = self._nvml
-        names = {
-            getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8): "hw_slowdown",
-            getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
-            getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
-            getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4): "sw_power_cap",
-        }
-        while not self._halt.is_set():
-            try:
-                self.samples.append(nv.nvmlDeviceGetClockInfo(self._h, nv.NVML_CLOCK_SM))
-                try:
-                    mask = nv.nvmlDeviceGetCurrentClocksEventReasons(self._h)
-                except Exception:
-                    mask = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self._h)
-                for bit, name in names.items():
-                    if mask & bit:
-                        self.reasons.add(name)
-            except Exception:
-                pass
-            self._halt.wait(self.period)
+        import subprocess
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        ids = vis.split(",")[:n_gpus] if vis else [str(i) for i in range(n_gpus)]
+        fd, self.path = tempfile.mkstemp(prefix="mp4j_clocks_", suffix=".csv")
+        os.close(fd)
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "--query-gpu=" + self.FIELDS, "--format=csv,noheader,nounits",
+                                          "-lms", "5", "-i", ",".join(ids)], stdout=open(self.path, "w"),
+                                         stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
 
-    def finish(self):
-        self._halt.set()
-        self.join(timeout=2)
-        return {"sm_mhz": statistics.median(self.samples) if self.samples else None,
-                "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
+    def wait_started(self, timeout_s=5.0):
+        """Blocks until the child has written its first sample (its start-up takes a few hundred ms)."""
+        if self.proc is None:
+            return
+        t0 = time.time()
+        while time.time() - t0 < timeout_s:
+            try:
+                if os.path.getsize(self.path) > 0:
+                    return
+            except OSError:
+                pass
+            time.sleep(0.01)
+
+    def finish(self, t_begin, t_end):
+        """t_begin / t_end: time.time() at the start / end of the timed region."""
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0, "tool": "nvidia-smi -lms 5 (rank 0, all GPUs)"}
+        if self.proc is None:
+            out["tool"] = "none"
+            return out
+        import datetime
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=3)
+        except Exception:
+            self.proc.kill()
+        inside, around, reasons, maxs = [], [], set(), []
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        for line in open(self.path):
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 8:
+                continue
+            try:
+                ts = datetime.datetime.strptime(f[0], "%Y/%m/%d %H:%M:%S.%f").timestamp()
+                mhz, mx = float(f[2]), float(f[3])
+            except ValueError:
+                continue
+            maxs.append(mx)
+            if t_begin - 0.003 <= ts <= t_end + 0.003:
+                inside.append(mhz)
+                for nm, v in zip(names, f[4:8]):
+                    if v.lower().startswith("active"):
+                        reasons.add(nm)
+            elif t_begin - 0.05 <= ts <= t_end + 0.05:
+                around.append(mhz)
+        try:
+            os.unlink(self.path)
+        except OSError:
+            pass
+        use = inside if inside else around
+        out.update({"sm_mhz": statistics.median(use) if use else None, "sm_max_mhz": max(maxs) if maxs else None,
+                    "reasons": sorted(reasons), "samples": len(inside),
+                    "window": "timed region" if inside else "within 50 ms of the timed region (under the same load)"})
+        return out
 
 
 def main():
@@ -146,15 +178,17 @@ def main():
     def step():
         plane.thread_allreduce(bufs, fop, SUM, 0, n)
 
+    sampler = ClockSampler(world, enabled=(rank == 0))
+    sampler.wait_started()
+    pcs.barrier()
     for _ in range(W):
         step()
     torch.cuda.synchronize()
     pcs.barrier()
-    sampler = ClockSampler(local_rank)
-    sampler.start()
     starts = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
     ends = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
     torch.cuda.synchronize()
+    t_begin = time.time()
     t0 = time.perf_counter()
     for i in range(K):
         starts[i].record()
@@ -162,8 +196,9 @@ def main():
         ends[i].record()
     torch.cuda.synchronize()
     wall_ms = (time.perf_counter() - t0) * 1e3
+    t_end = time.time()
     pcs.barrier()
-    clocks = sampler.finish()
+    clocks = sampler.finish(t_begin, t_end)
     plane.check()
     dev_ms = sum(s.elapsed_time(e) for s, e in zip(starts, ends))
     algo_desc = plane.last()

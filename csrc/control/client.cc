@@ -1,5 +1,7 @@
 // MasterClient: synchronous request/response proxy to the Master (parity: the IServer proxy
 // obtained at PCS:151 and used throughout ProcessCommSlave).
+#include <stdio.h>
+#include <stdlib.h>
 #include <unistd.h>
 
 #include "control.h"
@@ -76,7 +78,18 @@ int MasterClient::exchange(int rank) {
   return rd.i32();
 }
 
+void MasterClient::open_local_log(int rank) {
+  LogSettings ls = load_log_settings("slave");
+  const char* dir = getenv("MP4J_SLAVE_LOG_DIR");
+  if (dir && *dir) ls.log_dir = dir;
+  if (!ls.log_dir.empty()) local_log_.open(ls, "slave_" + std::to_string(rank));
+}
+
 void MasterClient::log(LogLevel lvl, const std::string& msg) {
+  if (local_log_.active()) {
+    local_log_.write(lvl, msg);
+    if (local_log_.echo(lvl)) fprintf(stderr, "%s\n", msg.c_str());
+  }
   net::Writer w;
   w.u8(lvl);
   w.str(msg);

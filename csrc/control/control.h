@@ -11,6 +11,7 @@
 //   RPC allreduce mailbox (as rank-ordered gather) SRV:373-514
 // New duty: the same gather mailbox brokers GPU memory handles at communicator set-up.
 #pragma once
+#include "../core/logconf.h"
 #include <stdint.h>
 
 #include <atomic>
@@ -124,7 +125,8 @@ class Master {
   // logs
   std::mutex log_mu_;
   std::deque<std::string> log_lines_;
-  FILE* log_file_ = nullptr;
+  LogSettings log_settings_;
+  LogSink log_sink_;  // <log_dir>/master.log (+ master_error.log), thresholds and rolling from the properties file
 };
 
 // Slave-side proxy. One mutex-guarded request connection + a dedicated heartbeat connection
@@ -140,6 +142,9 @@ class MasterClient {
   void barrier();
   int exchange(int rank);
   void log(LogLevel lvl, const std::string& msg);
+  // slave-side log files (slave_<rank>.log, slave_<rank>_error.log): settings "slave.*" of the properties
+  // file, directory overridable with $MP4J_SLAVE_LOG_DIR. Called once the rank is known.
+  void open_local_log(int rank);
   void close(int rank, int code);
   void kill_me(int rank, const std::string& cmd);
   void write_file(const std::string& content, const std::string& fname);
@@ -163,6 +168,7 @@ class MasterClient {
   std::mutex hb_mu_;
   std::condition_variable hb_cv_;
   bool hb_stop_ = false;
+  LogSink local_log_;
 };
 
 }  // namespace mp4j

@@ -30,15 +30,13 @@ Master::Master(int nslaves, int port, MasterOptions opt) : n_(nslaves), port_(po
   last_beat_.resize(n_);
   close_codes_.assign(n_, INT_MIN);
   ga_parts_.assign(n_, std::string());
-  if (!opt_.log_dir.empty()) {
-    mkdir(opt_.log_dir.c_str(), 0755);
-    log_file_ = fopen((opt_.log_dir + "/master.log").c_str(), "a");
-  }
+  log_settings_ = load_log_settings("master");
+  if (!opt_.log_dir.empty()) log_settings_.log_dir = opt_.log_dir;  // explicit argument wins over the file
+  log_sink_.open(log_settings_, "master");
 }
 
 Master::~Master() {
   shutdown();
-  if (log_file_) fclose(log_file_);
 }
 
 void Master::start() {
@@ -58,12 +56,9 @@ void Master::log_line(LogLevel lvl, const std::string& msg) {
   std::string line = std::string("[") + level_name(lvl) + "] " + msg;
   std::lock_guard<std::mutex> lk(log_mu_);
   log_lines_.push_back(line);
-  if (log_lines_.size() > 100000) log_lines_.pop_front();
-  if (!opt_.quiet && lvl != LOG_DEBUG) fprintf(stderr, "[mp4j-master] %s\n", line.c_str());
-  if (log_file_) {
-    fprintf(log_file_, "%s\n", line.c_str());
-    fflush(log_file_);
-  }
+  if (log_lines_.size() > std::max<size_t>(log_settings_.memory_lines, 1)) log_lines_.pop_front();
+  if (!opt_.quiet && log_sink_.echo(lvl)) fprintf(stderr, "[mp4j-master] %s\n", line.c_str());
+  log_sink_.write(lvl, msg);
 }
 
 std::vector<std::string> Master::logs() {

@@ -131,7 +131,7 @@ __global__ void __launch_bounds__(kCodecThreads, 1) codec_allreduce_kernel(const
       }
       CD::encode(v, my_in + (size_t)b * CD::kBytesPerBlock, (float*)(my_in + SL::kCodes) + b, lane);
     }
-    block_barrier_peers(tab, rank, ep);
+    if (!block_barrier_peers(tab, rank, ep)) break;
     // ---- reduce sub-slice `rank` (whole quantisation blocks) and push the re-encoded sum
     const int b_lo = (int)((long long)nblk * rank / world), b_hi = (int)((long long)nblk * (rank + 1) / world);
     for (int b = b_lo + warp; b < b_hi; b += nwarps) {
@@ -146,7 +146,7 @@ __global__ void __launch_bounds__(kCodecThreads, 1) codec_allreduce_kernel(const
         CD::encode(acc, out_q + (size_t)b * CD::kBytesPerBlock, (float*)(out_q + SL::kCodes) + b, lane);
       }
     }
-    block_barrier_peers(tab, rank, ep);
+    if (!block_barrier_peers(tab, rank, ep)) break;
     // ---- decode the reduced chunk into the user's array
     const char* my_out = tab.heap[rank] + slot_off + SL::kArea;
     for (int b = warp; b < nblk; b += nwarps) {
@@ -178,6 +178,7 @@ void launch_codec(const CodecArgs& a, int grid, cudaStream_t s) {
 }  // namespace
 
 void GpuPlane::allreduce_wire(float* const* arrs, int64_t from, int64_t to, int wire, cudaStream_t s) {
+  entry_check();
   check_from_to(from, to);
   const int p = world();
   if (p == 1 || from == to) return;

@@ -23,7 +23,7 @@ struct GrsArgs {
   int entry_barrier;
   int exit_barrier;
   int vec_ok;                  // local src/dst pointers are 16-byte congruent with the heap addresses
-  int pad_;
+  int dead_rank_p1;            // test hook (option dead_rank): rank + 1 that returns at once, 0 = none
   GrsItem item[kMaxRanks];     // indexed by rank in emulation, [0] otherwise
 };
 
@@ -37,6 +37,8 @@ struct ThreadArgs {
   int dbg;                      // diagnostics only (MP4J_WS_DBG): bit mask that disables parts of the pipeline
   int tail_split;               // pull kernel: a block's last chunk runs as this many shorter pipeline steps (>= 1)
   long long from, to;           // element range
+  int push;                     // pull kernel: 1 = phase B pushes its result to every rank (hybrid), 0 = phase C pulls
+  int fa_gpu;                   // register formulation: 1 = phase A publishes with a device-scope fence + relaxed flag
   unsigned long long stg_off;   // byte offset in every heap of the per-block staging slots
   unsigned long long slot_bytes;  // bytes per block slot (multiple of 16 * world)
   void* bufs[kMaxRanks][MP4J_MAX_THREADS];  // [rank][thread] in emulation, [0][thread] otherwise

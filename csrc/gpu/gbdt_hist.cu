@@ -145,6 +145,7 @@ __global__ void __launch_bounds__(kHistThreads) gbdt_hist_rs_kernel(const __grid
 void GpuPlane::gbdt_hist_reduce_scatter(const uint8_t* const* bins, const long long* pitch, const float* const* grad,
                                         const float* const* hess, const long long* rows, int F, float** shard_out,
                                         int* feats_per_rank_out, cudaStream_t s) {
+  entry_check();
   const int p = world();
   const int L = local_ranks();
   if (F <= 0) throw Error("gbdt_hist_reduce_scatter: bad shape");

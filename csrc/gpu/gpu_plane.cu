@@ -30,6 +30,7 @@ void GpuOptions::load_env() {
   heap_bytes = env_size("MP4J_HEAP_BYTES", heap_bytes);
   staging_bytes = env_size("MP4J_STAGING_BYTES", staging_bytes);
   thread_slot_bytes = env_size("MP4J_THREAD_SLOT_BYTES", thread_slot_bytes);
+  if (getenv("MP4J_THREAD_SLOT_BYTES")) thread_slot_auto = false;
   thread_slots = (int)env_size("MP4J_THREAD_SLOTS", (size_t)thread_slots);
   oneshot_max_bytes = env_size("MP4J_ONE_SHOT_MAX_BYTES", oneshot_max_bytes);
   nvls_min_bytes = env_size("MP4J_NVLS_MIN_BYTES", nvls_min_bytes);
@@ -41,6 +42,7 @@ void GpuOptions::load_env() {
   host_chunk_bytes = env_size("MP4J_HOST_CHUNK_BYTES", host_chunk_bytes);
   ws_ver = (int)env_size("MP4J_WS_VER", (size_t)ws_ver);
   ws_tail_split = (int)env_size("MP4J_WS_TAIL_SPLIT", (size_t)ws_tail_split);
+  ws_fa_gpu = (int)env_size("MP4J_WS_FA_GPU", (size_t)ws_fa_gpu);
   ws_dbg = (int)env_size("MP4J_WS_DBG", (size_t)ws_dbg);
 }
 
@@ -48,13 +50,19 @@ bool GpuPlane::set_option(const std::string& name, long long v) {
   if (name == "ws_ver") opt_.ws_ver = (int)v;
   else if (name == "ws_dbg") opt_.ws_dbg = (int)v;
   else if (name == "ws_tail_split") opt_.ws_tail_split = std::max(1, (int)v);
+  else if (name == "ws_fa_gpu") opt_.ws_fa_gpu = (int)v;
   else if (name == "thread_slots") opt_.thread_slots = std::max(2, std::min((int)v, thread_ws_slots()));
-  else if (name == "thread_slot_bytes") opt_.thread_slot_bytes = align_up((size_t)v, 16 * 8 * 8);
+  else if (name == "thread_slot_bytes") {
+    opt_.thread_slot_bytes = align_up((size_t)v, 16 * 8 * 8);
+    opt_.thread_slot_auto = false;
+  }
   else if (name == "nvls_min_world") opt_.nvls_min_world = (int)v;
   else if (name == "nvls_min_bytes") opt_.nvls_min_bytes = (size_t)v;
   else if (name == "oneshot_max_bytes") opt_.oneshot_max_bytes = std::min((size_t)v, oneshot_slot_bytes_);
   else if (name == "max_blocks") opt_.max_blocks = (int)v;
   else if (name == "poll_ns") opt_.poll_ns = (int)v;
+  else if (name == "timeout_ms") opt_.timeout_s = (double)v / 1e3;
+  else if (name == "dead_rank") dead_rank_p1_ = (int)v + 1;  // test hook: -1 = none
   else if (name == "host_chunk_bytes") {
     hpipe_release();
     opt_.host_chunk_bytes = (size_t)v;
@@ -178,10 +186,16 @@ void GpuPlane::free(size_t off) {
 
 void GpuPlane::check_error() {
   if (err_host_ && *err_host_) {
+    poisoned_ = true;
     *err_host_ = 0;
-    throw Error("GPU collective: a peer did not arrive within the device-side timeout (dead or diverged rank?)");
+    throw Error("GPU collective: a peer did not arrive within the device-side timeout (dead or diverged rank?); "
+                "the kernel stored nothing after the failed wait and this GPU plane is now unusable");
   }
+  if (poisoned_)
+    throw Error("GPU plane is unusable: an earlier collective hit the peer-wait timeout (close the communicator)");
 }
+
+void GpuPlane::entry_check() { check_error(); }
 
 int GpuPlane::pick_grid(long long max_units, int max_blocks_per_sm) const {
   long long cap = (long long)sms_ * max_blocks_per_sm;
@@ -236,6 +250,7 @@ void GpuPlane::run_grs(const char* name, void* const* arrs, int dtype, int op, c
   a.entry_barrier = 1;
   a.exit_barrier = 1;
   a.vec_ok = 1;
+  a.dead_rank_p1 = dead_rank_p1_;
   const bool nvls_ok = has_multicast() && nvls_supported(dtype, op) &&
                        (algo == MP4J_ALGO_NVLS || (algo == MP4J_ALGO_AUTO && nvls_auto(span_bytes)));
   last_.name = name;
@@ -297,6 +312,7 @@ void GpuPlane::run_grs(const char* name, void* const* arrs, int dtype, int op, c
 }
 
 void GpuPlane::allreduce(void* const* arrs, int dtype, int op, int64_t from, int64_t to, int algo, cudaStream_t s) {
+  entry_check();
   check_from_to(from, to);
   const int p = world();
   if (p == 1 || from == to) return;
@@ -349,6 +365,7 @@ void GpuPlane::allreduce(void* const* arrs, int dtype, int op, int64_t from, int
 
 void GpuPlane::reduce_scatter(void* const* arrs, int dtype, int op, int64_t from, const int64_t* counts, int algo,
                               cudaStream_t s) {
+  entry_check();
   const int p = world();
   check_from_counts(from, counts, p);
   if (p == 1) return;
@@ -364,6 +381,7 @@ void GpuPlane::reduce_scatter(void* const* arrs, int dtype, int op, int64_t from
 
 void GpuPlane::allgather(void* const* arrs, int dtype, const int64_t* froms, const int64_t* tos, int algo,
                          cudaStream_t s) {
+  entry_check();
   const int p = world();
   check_froms_tos(froms, tos, p);
   if (p == 1) return;
@@ -376,6 +394,7 @@ void GpuPlane::allgather(void* const* arrs, int dtype, const int64_t* froms, con
 }
 
 void GpuPlane::broadcast(void* const* arrs, int dtype, int64_t from, int64_t to, int root, int algo, cudaStream_t s) {
+  entry_check();
   const int p = world();
   check_from_to(from, to);
   if (root < 0 || root >= p) throw Error("root rank out of range");
@@ -394,6 +413,7 @@ void GpuPlane::broadcast(void* const* arrs, int dtype, int64_t from, int64_t to,
 
 void GpuPlane::gather(void* const* arrs, int dtype, const int64_t* froms, const int64_t* tos, int root,
                       cudaStream_t s) {
+  entry_check();
   const int p = world();
   check_froms_tos(froms, tos, p);
   if (root < 0 || root >= p) throw Error("root rank out of range");
@@ -408,6 +428,7 @@ void GpuPlane::gather(void* const* arrs, int dtype, const int64_t* froms, const 
 
 void GpuPlane::scatter(void* const* arrs, int dtype, const int64_t* froms, const int64_t* tos, int root,
                        cudaStream_t s) {
+  entry_check();
   const int p = world();
   check_froms_tos(froms, tos, p);
   if (root < 0 || root >= p) throw Error("root rank out of range");
@@ -422,6 +443,7 @@ void GpuPlane::scatter(void* const* arrs, int dtype, const int64_t* froms, const
 
 void GpuPlane::reduce(void* const* arrs, int dtype, int op, int64_t from, int64_t to, int root, int algo,
                       cudaStream_t s) {
+  entry_check();
   const int p = world();
   check_from_to(from, to);
   if (root < 0 || root >= p) throw Error("root rank out of range");
@@ -438,6 +460,7 @@ void GpuPlane::reduce(void* const* arrs, int dtype, int op, int64_t from, int64_
 
 void GpuPlane::thread_allreduce(void* const* bufs, int T, int dtype, int op, int64_t from, int64_t to, int fanout,
                                 int dst, bool local_only, int algo, cudaStream_t s) {
+  entry_check();
   check_from_to(from, to);
   if (T < 1 || T > MP4J_MAX_THREADS) throw Error("thread count out of range");
   if (dst < 0 || dst >= T) throw Error("dst thread out of range");
@@ -505,22 +528,24 @@ void GpuPlane::thread_allreduce(void* const* bufs, int T, int dtype, int op, int
   // ---- preferred: warp-specialised kernels (HBM read / NVLink / HBM write overlap inside each SM):
   // the TMA formulation (any T, 16-byte aligned) or the register formulation (T in {2,4,8}, 32-byte aligned)
   const int ws_ver = opt_.ws_ver, ws_dbg = opt_.ws_dbg;
-  // thread_algo: 0 = pick, 4 = TMA formulation, 5 = register formulation with pushes, 6 = register formulation
-  // with pulls (3 = chunk-synchronous fallback below)
+  // thread_algo: 0 = pick, 4 = TMA formulation, 5 = first register formulation (system-scope release per
+  // phase), 6 = pull formulation, 7 = hybrid (pull-style phase A/B, pushed result) (3 = chunk-synchronous
+  // fallback below). ws_ver: 1 -> 5, 2 -> 4, 3 -> 6, 4 -> 7, 0 -> 6 at two ranks and 7 beyond.
   const int talgo = algo & 0xff;
-  bool ws = vec && (talgo == 0 || talgo == 5 || talgo == 6) && (nbytes % 32) == 0 &&
+  bool ws = vec && (talgo == 0 || talgo == 5 || talgo == 6 || talgo == 7) && (nbytes % 32) == 0 &&
             thread_local_fast_supported(dtype, op, T);
   for (int i = 0; ws && i < L * T; ++i)
     if ((((uintptr_t)bufs[i] + (size_t)from * es) & 31) != 0) ws = false;
   const bool tma = vec && (talgo == 0 || talgo == 4) && thread_fused_tma_supported(dtype, op, T) &&
                    (talgo == 4 || ws_ver == 2 || !ws);
   if (ws || tma) {
-    const size_t wslot = opt_.thread_slot_bytes / 32 * 32;
+    const size_t wslot = (opt_.thread_slot_auto && p == 2 ? (size_t)(48 << 10) : opt_.thread_slot_bytes) / 32 * 32;
     a.slot_bytes = wslot;
     a.slots = opt_.thread_slots;
     a.stg_off = thread_off_;
     a.dbg = ws_dbg;
     a.tail_split = std::max(1, opt_.ws_tail_split);
+    a.fa_gpu = opt_.ws_fa_gpu;
     long long wcap = sms_;
     if (emulated()) wcap /= p;
     wcap = std::min<long long>(wcap, (long long)(thread_bytes_ / (wslot * opt_.thread_slots)));
@@ -532,8 +557,12 @@ void GpuPlane::thread_allreduce(void* const* bufs, int T, int dtype, int op, int
     if (tma) {
       last_ = CollStat{"thread_allreduce", wnvls ? "fused-tma-nvls" : "fused-tma-p2p", nbytes, wgrid, false};
       launch_thread_fused_tma(dtype, op, wnvls, a, wgrid, s);
-    } else if (talgo == 6 || (talgo == 0 && ws_ver == 3)) {
-      last_ = CollStat{"thread_allreduce", wnvls ? "fused-pull-nvls" : "fused-pull-p2p", nbytes, wgrid, false};
+    } else if (talgo == 6 || talgo == 7 || (talgo == 0 && (ws_ver == 3 || ws_ver == 4 || ws_ver == 0))) {
+      a.push = (talgo == 7 || (talgo == 0 && (ws_ver == 4 || (ws_ver == 0 && p > 2)))) ? 1 : 0;
+      last_ = CollStat{"thread_allreduce",
+                       a.push ? (wnvls ? "fused-hybrid-nvls" : "fused-hybrid-p2p")
+                              : (wnvls ? "fused-pull-nvls" : "fused-pull-p2p"),
+                       nbytes, wgrid, false};
       launch_thread_fused_pull(dtype, op, wnvls, a, wgrid, s);
     } else {
       last_ = CollStat{"thread_allreduce", wnvls ? "fused-ws-nvls" : "fused-ws-p2p", nbytes, wgrid, false};

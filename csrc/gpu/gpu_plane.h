@@ -25,8 +25,10 @@ struct GpuOptions {
   size_t staging_bytes = 128ull << 20;  // general staging window for non-symmetric tensors
   // fused thread kernel: per-block slot (MP4J_THREAD_SLOT_BYTES) and ring depth (MP4J_THREAD_SLOTS).
   // Measured (profiles/README.md §1): 64 KiB x 4 is the best trade between pipeline fill/drain and
-  // L2 footprint (small) and per-chunk cross-GPU flag latency (large) at 2 and 8 GPUs.
+  // L2 footprint (small) and per-chunk cross-GPU flag latency (large) at 4 and 8 GPUs; at 2 GPUs (P2P, the
+  // shortest chain) 48 KiB x 4 is 3 % faster. thread_slot_auto = nobody set the size explicitly.
   size_t thread_slot_bytes = 64 << 10;
+  bool thread_slot_auto = true;
   int thread_slots = 4;
   size_t oneshot_max_bytes = 256 << 10; // <= : one-shot allreduce (MP4J_ONE_SHOT_MAX_BYTES)
   size_t nvls_min_bytes = 512 << 10;    // >= : NVLS when available (MP4J_NVLS_MIN_BYTES)
@@ -37,6 +39,7 @@ struct GpuOptions {
   double timeout_s = 60.0;              // device-side flag-wait watchdog (MP4J_GPU_TIMEOUT_S)
   size_t host_chunk_bytes = 8ull << 20; // per-buffer chunk of the host-array pipeline (MP4J_HOST_CHUNK_BYTES)
   int ws_tail_split = 4;                // pull kernel: steps the last chunk of a block is cut into (MP4J_WS_TAIL_SPLIT)
+  int ws_fa_gpu = 1;                    // register formulation: device-scope publish of phase A (MP4J_WS_FA_GPU)
   int ws_ver = 1;                       // fused thread kernel: 1 = register formulation, 2 = TMA (MP4J_WS_VER)
   int ws_dbg = 0;                       // diagnostics bit mask for the fused thread kernels (MP4J_WS_DBG)
   void load_env();
@@ -94,7 +97,8 @@ class GpuPlane {
                              int dst, cudaStream_t s);
   // K8: fp32 SUM allreduce whose payload crosses NVLink as bf16 or block-scaled fp8 (lossy, opt-in).
   void allreduce_wire(float* const* arrs, int64_t from, int64_t to, int wire, cudaStream_t s);
-  // Raises if a kernel reported a peer-wait timeout since the last check.
+  // Raises if a kernel reported a peer-wait timeout since the last check. After a timeout the plane is
+  // unusable (the peers' epochs are out of step): every later collective raises at once.
   void check_error();
 
   // ---- sparse (map container) collectives: allreduceMap / reduceScatterMap / allgatherMap on
@@ -124,7 +128,8 @@ class GpuPlane {
 
   // Local reduce-by-key (the thread-level map merge of DOP:458-477 on device arrays, also usable
   // as pre-aggregation): out = unique keys of (keys, vals) with equal keys reduced by `op`.
-  // *out_count (device u64) receives the number of unique keys (clamped to out_cap). The hash
+  // *out_count (device u64) receives the full number of unique keys (it may exceed out_cap; at most out_cap
+  // pairs are stored). Pairs with the reserved key INT64_MIN are ignored. The hash
   // table is plane-owned scratch (cudaMalloc, cached and grown on demand).
   void map_reduce_local(int local_rank, const long long* keys, const void* vals, long long n, int dtype, int op,
                         long long* out_keys, void* out_vals, long long out_cap, unsigned long long* out_count,
@@ -169,6 +174,9 @@ class GpuPlane {
   std::mutex alloc_mu_;
   std::map<size_t, size_t> used_;  // off -> bytes
   CollStat last_;
+  bool poisoned_ = false;  // a kernel hit the peer-wait watchdog
+  int dead_rank_p1_ = 0;   // test hook, see GrsArgs::dead_rank_p1
+  void entry_check();      // start of every collective: surfaces a timeout of an earlier (asynchronous) one
   std::string last_algo_store_;  // backing store when last_.algo is composed at run time
   CollTrace trace_;
   size_t lr_shard_off_ = 0, lr_shard_bytes_ = 0;

@@ -56,6 +56,7 @@ __global__ void __launch_bounds__(kThreads) grs_kernel(const __grid_constant__ G
 
   BlockEpoch ep;
   ep.load(tab, rank);
+  if (a.dead_rank_p1 != 0 && rank == a.dead_rank_p1 - 1) return;  // test hook: this rank never shows up
 
   // [lo, hi) = scalar head | 16-byte vector body | scalar tail, decided by the HEAP address only so
   // that every rank splits identically; a local pointer of different alignment is read/written
@@ -92,7 +93,10 @@ __global__ void __launch_bounds__(kThreads) grs_kernel(const __grid_constant__ G
     }
   }
 
-  if (a.entry_barrier) block_barrier_peers(tab, rank, ep);
+  if (a.entry_barrier && !block_barrier_peers(tab, rank, ep)) {
+    ep.store();
+    return;  // a peer is missing: store nothing; the host raises on the error word
+  }
 
   const unsigned smask = it.src_mask & full, dmask = it.dst_mask & full;
   const bool multi_src = (smask & (smask - 1)) != 0;
@@ -219,7 +223,7 @@ __global__ void __launch_bounds__(kThreads) grs_kernel(const __grid_constant__ G
     }
   }
 
-  if (a.exit_barrier) block_barrier_peers(tab, rank, ep);
+  if (a.exit_barrier) (void)block_barrier_peers(tab, rank, ep);
   ep.store();
 }
 

@@ -424,6 +424,7 @@ void make_map(CUtensorMap* m, const void* base, long long rows, long long K, int
 // Host entry: G shards are plane-owned symmetric buffers; returns their address for every local rank.
 void GpuPlane::lr_xtr_reduce_scatter(const void* const* xt, const void* const* rt, int F, int C, long long K,
                                      float** shard_out, int* feats_per_rank_out, cudaStream_t s) {
+  entry_check();
   const int p = world();
   const int L = local_ranks();
   if (F <= 0 || K <= 0) throw Error("lr_xtr_reduce_scatter: bad shape");

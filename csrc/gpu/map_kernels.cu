@@ -174,6 +174,10 @@ __global__ void __launch_bounds__(kMapThreads) map_clear_kernel(MapTable t) {
 // inserts `cnt` pairs; table must have room (size >= 2 * pairs)
 template <typename V, int OP>
 __device__ __forceinline__ void table_insert(const MapTable& t, long long key, V val) {
+  // INT64_MIN marks a free slot: a pair with that key cannot be stored (it would be folded into whatever
+  // free slot it probed first and leak into the next key placed there). Such pairs are ignored - documented
+  // in mp4j_gpu.h; the String-key bridge never produces the value.
+  if (key == kMapEmpty) return;
   unsigned long long h = splitmix64((unsigned long long)key ^ 0x5851f42d4c957f2dull) & t.mask;
   for (;;) {
     const long long prev = (long long)atomicCAS((unsigned long long*)&t.keys[h], (unsigned long long)kMapEmpty,
@@ -287,7 +291,7 @@ __global__ void __launch_bounds__(kMapThreads) map_allgather_push_kernel(const _
       ((V*)(tab.heap[q] + a.ovals_off))[off + i] = v;
     }
   }
-  block_barrier_peers(tab, rank, ep);  // all pushes landed everywhere before anyone reads its output
+  if (!block_barrier_peers(tab, rank, ep)) return;  // all pushes landed everywhere before anyone reads its output
   ep.store();
 }
 

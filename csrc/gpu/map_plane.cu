@@ -104,6 +104,7 @@ void GpuPlane::map_collective(int mode, const long long* const* keys, const void
                               long long max_n, long long out_cap, int dtype, int op, int partition,
                               long long** out_keys, void** out_vals, unsigned long long** info_host,
                               cudaStream_t s) {
+  entry_check();
   const int p = world();
   const int L = local_ranks();
   if (mode < 0 || mode > 2) throw Error("map_collective: bad mode");

@@ -93,9 +93,13 @@ __device__ __forceinline__ bool wait_flag(const PeerTable& t, const uint32_t* fl
       (void)ld_acquire_sys(flag);  // acquire once, on the already-arrived flag (cheaper than a full fence)
       return true;
     }
-    if ((spins & 1023u) == 0 && globaltimer_ns() - t0 > t.timeout_ns) {
-      atomicExch((unsigned*)t.err, 1u);
-      return false;
+    if ((spins & 1023u) == 0) {
+      // somebody else already gave up: the launch is lost, leave quickly instead of timing out again
+      if (*(volatile uint32_t*)t.err != 0u) return false;
+      if (globaltimer_ns() - t0 > t.timeout_ns) {
+        atomicExch((unsigned*)t.err, 1u);
+        return false;
+      }
     }
   }
 }
@@ -116,15 +120,18 @@ struct BlockEpoch {
 // Cross-GPU barrier between the same-index blocks of all ranks. Data written by any thread of the
 // block before the call is visible to the peers' block after their call returns (bar.sync orders
 // the CTA's writes before the releasing thread; st.release.sys is cumulative).
-__device__ __forceinline__ void block_barrier_peers(const PeerTable& t, int rank, BlockEpoch& ep) {
+// Returns false if a peer did not arrive within the watchdog time: the caller must then leave without
+// storing anything (the host finds the error word and declares the plane unusable).
+__device__ __forceinline__ bool block_barrier_peers(const PeerTable& t, int rank, BlockEpoch& ep) {
   ep.value += 1;
   __syncthreads();
+  bool ok = true;
   if (threadIdx.x < (unsigned)t.world) {
     const int q = threadIdx.x;
     st_release_sys(t.sig[q] + blockIdx.x * kMaxRanks + rank, ep.value);
-    wait_flag(t, t.sig[rank] + blockIdx.x * kMaxRanks + q, ep.value);
+    ok = wait_flag(t, t.sig[rank] + blockIdx.x * kMaxRanks + q, ep.value);
   }
-  __syncthreads();
+  return __syncthreads_and(ok ? 1 : 0) != 0;
 }
 
 // ---- 16-byte vector moves (streaming: touched once, keep them out of L1)

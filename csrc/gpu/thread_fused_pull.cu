@@ -37,7 +37,7 @@ namespace {
 template <int WA, int WB, int WC>
 struct SplitP {
   static constexpr int kThreadsA = WA * 32, kThreadsB = WB * 32, kThreadsC = WC * 32;
-  static constexpr int kThreads = kThreadsA + kThreadsB + kThreadsC + 32;  // + the signal warp
+  static constexpr int kThreads = kThreadsA + kThreadsB + kThreadsC + 64;  // + the two signal warps (FA, FB)
 };
 
 __device__ __forceinline__ void named_bar(int id, int nthreads) {
@@ -94,7 +94,7 @@ struct Steps {
 };
 
 // phase B without the switch: W ranks, all loads of a batch in flight together, rank-ordered reduce
-template <typename T, int OP, int W, int nthr>
+template <typename T, int OP, int W, int nthr, bool PUSH>
 __device__ __forceinline__ void b_p2p(const PeerTable& tab, unsigned long long so, int rank, int lo, int hi, int btid) {
   constexpr int kB = W == 2 ? 6 : 8 / W;  // vectors per thread per round: 8-12 loads in flight (16 spill)
   for (int v0 = lo + btid; v0 < hi; v0 += nthr * kB) {
@@ -113,19 +113,31 @@ __device__ __forceinline__ void b_p2p(const PeerTable& tab, unsigned long long s
         Vec16 acc = x[j][0];
 #pragma unroll
         for (int q = 1; q < W; ++q) acc = vec_reduce<T, OP>(acc, x[j][q]);  // ascending rank order
-        st_slot16(tab.heap[rank] + so + (unsigned long long)v * 16, acc);
+        if constexpr (PUSH) {
+#pragma unroll
+          for (int q = 0; q < W; ++q) st_slot16(tab.heap[q] + so + (unsigned long long)v * 16, acc);
+        } else {
+          st_slot16(tab.heap[rank] + so + (unsigned long long)v * 16, acc);
+        }
       }
     }
   }
 }
 
-template <typename T, int OP, bool NVLS, int NT, typename SP>
+// PUSH = false: the pull formulation described at the top. PUSH = true ("hybrid", the choice beyond 2 ranks):
+// phase B pushes its reduced sub-slice into every rank's slot (multimem.st: one store, the switch replicates -
+// pulling the same bytes would double every GPU's NVLink egress at 8 ranks and made phase C, 7/8 remote
+// loads, the bottleneck: 0.85 vs 0.82 ms), so phase C reads only local memory and no FC flags exist. The
+// remote stores need ONE system-scope release per chunk; it is issued by a warp of its own (signal warp B), so
+// its 15-20 us under load are latency of that chunk only, never a stall of the group that moves data.
+template <typename T, int OP, bool NVLS, int NT, typename SP, bool PUSH>
 __global__ void __launch_bounds__(SP::kThreads, 1) thread_fused_pull_kernel(const __grid_constant__ ThreadArgs a) {
   constexpr int kThreadsA = SP::kThreadsA, kThreadsB = SP::kThreadsB, kThreadsC = SP::kThreadsC;
   __shared__ volatile unsigned c_done;  // chunks whose slot group C has fully read
   // arrivals of the phase-A warps per ring slot. Per SLOT, not one running total: a warp that is a chunk ahead
   // of a slow one must not complete the slow warp's chunk (a warp cannot lap the ring, so per-slot counts are exact)
   __shared__ unsigned a_cnt[kWsMaxSlots];
+  __shared__ unsigned b_cnt[kWsMaxSlots];  // same for the phase-B warps (PUSH: consumed by signal warp B)
   const PeerTable& tab = a.tab;
   const int rank = my_rank(tab);
   const int world = tab.world;
@@ -151,7 +163,7 @@ __global__ void __launch_bounds__(SP::kThreads, 1) thread_fused_pull_kernel(cons
   };
   if (threadIdx.x == 0) {
     c_done = 0;
-    for (int i = 0; i < kWsMaxSlots; ++i) a_cnt[i] = 0;
+    for (int i = 0; i < kWsMaxSlots; ++i) a_cnt[i] = b_cnt[i] = 0;
   }
   __syncthreads();
 
@@ -168,7 +180,10 @@ __global__ void __launch_bounds__(SP::kThreads, 1) thread_fused_pull_kernel(cons
         if (lane == 0)
           while (c_done < (unsigned)(k - kSlots + 1)) {
           }
-        if (lane < world && !(a.dbg & 2)) wait_flag(tab, fc(rank, (int)(k % kSlots), lane), base + (uint32_t)(k - kSlots) + 1u);
+        if constexpr (!PUSH) {
+          if (lane < world && !(a.dbg & 2))
+            wait_flag(tab, fc(rank, (int)(k % kSlots), lane), base + (uint32_t)(k - kSlots) + 1u);
+        }
         __syncwarp();
       }
       char* slot = tab.heap[rank] + ring_off + (unsigned long long)(k % kSlots) * a.slot_bytes;
@@ -193,8 +208,26 @@ __global__ void __launch_bounds__(SP::kThreads, 1) thread_fused_pull_kernel(cons
         if (tid == 0) WS_TRACE(0, k);
       }
     }
+  } else if (tid >= kThreadsA + kThreadsB + kThreadsC + 32) {
+    // ================= signal warp B (PUSH only): FB(k) once every B warp has issued its stores of chunk k.
+    // The release is at system scope because the stores it orders went to other GPUs.
+    if constexpr (PUSH) {
+      const int lane = tid & 31;
+      constexpr unsigned WB = kThreadsB / 32;
+      for (long long k = 0; k < mine; ++k) {
+        const int sl = (int)(k % kSlots);
+        if (lane == 0) {
+          while (*(volatile unsigned*)&b_cnt[sl] < WB * (unsigned)(k / kSlots + 1)) {
+          }
+          WS_TRACE(4, k);
+        }
+        __syncwarp();
+        if (lane < world) st_release_sys(fb(lane, sl, rank), base + (uint32_t)k + 1u);
+        if (lane == 0) WS_TRACE(5, k);
+      }
+    }
   } else if (tid >= kThreadsA + kThreadsB + kThreadsC) {
-    // ================= signal warp: FA(k) to every rank once all A warps finished chunk k.
+    // ================= signal warp A: FA(k) to every rank once all A warps finished chunk k.
     // The slot lives in THIS GPU's memory and the peers read it through this GPU's L2, so a
     // device-scope fence is what orders the data before the flag; the flag itself is a plain store.
     const int lane = tid & 31;
@@ -238,31 +271,47 @@ __global__ void __launch_bounds__(SP::kThreads, 1) thread_fused_pull_kernel(cons
 #pragma unroll
             for (int j = 0; j < kB; ++j) {
               const int v = v0 + j * kThreadsB;
-              if (v < hi) st_slot16(tab.heap[rank] + so + (unsigned long long)v * 16, acc[j]);
+              if (v < hi) {
+                if constexpr (PUSH) multimem_st(tab.mc_heap + so + (unsigned long long)v * 16, acc[j]);
+                else st_slot16(tab.heap[rank] + so + (unsigned long long)v * 16, acc[j]);
+              }
             }
           }
         } else {
           switch (world) {
-            case 2: b_p2p<T, OP, 2, kThreadsB>(tab, so, rank, lo, hi, btid); break;
-            case 4: b_p2p<T, OP, 4, kThreadsB>(tab, so, rank, lo, hi, btid); break;
-            case 8: b_p2p<T, OP, 8, kThreadsB>(tab, so, rank, lo, hi, btid); break;
+            case 2: b_p2p<T, OP, 2, kThreadsB, PUSH>(tab, so, rank, lo, hi, btid); break;
+            case 4: b_p2p<T, OP, 4, kThreadsB, PUSH>(tab, so, rank, lo, hi, btid); break;
+            case 8: b_p2p<T, OP, 8, kThreadsB, PUSH>(tab, so, rank, lo, hi, btid); break;
             default:
               for (int v = lo + btid; v < hi; v += kThreadsB) {
                 Vec16 acc = ld_coherent(tab.heap[0] + so + (unsigned long long)v * 16);
                 for (int q = 1; q < world; ++q)
                   acc = vec_reduce<T, OP>(acc, ld_coherent(tab.heap[q] + so + (unsigned long long)v * 16));
-                st_slot16(tab.heap[rank] + so + (unsigned long long)v * 16, acc);
+                if constexpr (PUSH) {
+                  for (int q = 0; q < world; ++q) st_slot16(tab.heap[q] + so + (unsigned long long)v * 16, acc);
+                } else {
+                  st_slot16(tab.heap[rank] + so + (unsigned long long)v * 16, acc);
+                }
               }
           }
         }
       }
-      __threadfence();          // each thread's result stores are in L2 before the barrier
-      named_bar(2, kThreadsB);  // ... and the barrier orders them before the flag of warp 0
-      if (bw == 0) {
-        if (lane == 0) WS_TRACE(4, k);
-        __threadfence();
-        if (lane < world) st_relaxed_sys(fb(lane, sl, rank), base + (uint32_t)k + 1u);
-        if (lane == 0) WS_TRACE(5, k);
+      if constexpr (PUSH) {
+        // hand the chunk to signal warp B and go on with the next one
+        __syncwarp();
+        if (lane == 0) {
+          __threadfence_block();  // the warp's stores are ordered before the count
+          atomicAdd(&b_cnt[sl], 1u);
+        }
+      } else {
+        __threadfence();          // each thread's result stores are in L2 before the barrier
+        named_bar(2, kThreadsB);  // ... and the barrier orders them before the flag of warp 0
+        if (bw == 0) {
+          if (lane == 0) WS_TRACE(4, k);
+          __threadfence();
+          if (lane < world) st_relaxed_sys(fb(lane, sl, rank), base + (uint32_t)k + 1u);
+          if (lane == 0) WS_TRACE(5, k);
+        }
       }
     }
   } else {
@@ -286,7 +335,7 @@ __global__ void __launch_bounds__(SP::kThreads, 1) thread_fused_pull_kernel(cons
           if (v < nv) {
             int q = (int)((long long)v * world / nv);
             while (v >= (int)((long long)nv * (q + 1) / world)) ++q;  // owner of 32-byte vector v
-            if (a.dbg & 8) q = rank;
+            if (PUSH || (a.dbg & 8)) q = rank;
             x[j] = ld_coherent32(tab.heap[q] + so + (unsigned long long)v * 32);
           }
         }
@@ -305,7 +354,9 @@ __global__ void __launch_bounds__(SP::kThreads, 1) thread_fused_pull_kernel(cons
         }
       }
       named_bar(3, kThreadsC);  // every load of the chunk has returned (its value was stored above)
-      if (ct < world) st_relaxed_sys(fc(ct, sl, rank), base + (uint32_t)k + 1u);
+      if constexpr (!PUSH) {
+        if (ct < world) st_relaxed_sys(fc(ct, sl, rank), base + (uint32_t)k + 1u);
+      }
       if (ct == 0) {
         c_done = (unsigned)(k + 1);
         WS_TRACE(7, k);
@@ -314,17 +365,17 @@ __global__ void __launch_bounds__(SP::kThreads, 1) thread_fused_pull_kernel(cons
   }
   __syncthreads();
   // nobody may reuse the ring (next launch) while a peer still pulls from it
-  if (tid < world && !(a.dbg & 2)) {
+  if (!PUSH && tid < world && !(a.dbg & 2)) {
     const long long k0 = mine > kSlots ? mine - kSlots : 0;
     for (long long k = k0; k < mine; ++k) wait_flag(tab, fc(rank, (int)(k % kSlots), tid), base + (uint32_t)k + 1u);
   }
   if (threadIdx.x == 0) *(volatile uint32_t*)ws_epoch = base + (uint32_t)mine;
 }
 
-template <typename T, int OP, bool NVLS, int NT>
-void launch_pull_nt(const ThreadArgs& args, int grid, cudaStream_t stream) {
-  typedef SplitP<6, 4, 5> SP;
-  auto kfn = thread_fused_pull_kernel<T, OP, NVLS, NT, SP>;
+template <typename T, int OP, bool NVLS, int NT, bool PUSH>
+void launch_pull_mode(const ThreadArgs& args, int grid, cudaStream_t stream) {
+  typedef SplitP<6, 4, 4> SP;
+  auto kfn = thread_fused_pull_kernel<T, OP, NVLS, NT, SP, PUSH>;
   if (args.tab.emulate) {
     void* params[] = {(void*)&args};
     MP4J_CUDA(cudaLaunchCooperativeKernel((const void*)kfn, dim3(grid, args.tab.world), dim3(SP::kThreads), params, 0,
@@ -333,6 +384,12 @@ void launch_pull_nt(const ThreadArgs& args, int grid, cudaStream_t stream) {
     kfn<<<grid, SP::kThreads, 0, stream>>>(args);
     MP4J_CUDA(cudaGetLastError());
   }
+}
+
+template <typename T, int OP, bool NVLS, int NT>
+void launch_pull_nt(const ThreadArgs& args, int grid, cudaStream_t stream) {
+  if (args.push) return launch_pull_mode<T, OP, NVLS, NT, true>(args, grid, stream);
+  launch_pull_mode<T, OP, NVLS, NT, false>(args, grid, stream);
 }
 
 template <typename T, int OP, bool NVLS>

@@ -109,6 +109,10 @@ __global__ void __launch_bounds__(SP::kWsThreads, 1) thread_fused_ws_kernel(cons
         }
         if (!(a.dbg & 32)) st_keep32(slot + (unsigned long long)v * 32, x[0]);
       }
+      // fa_gpu: every storing thread fences its own slot stores to device scope. The slot is in THIS GPU's
+      // memory and the peers read it through this GPU's L2, so that is what the flag must be ordered after;
+      // the signal warp then needs no system-scope release (25-30 us per chunk at 8 GPUs under load).
+      if (a.fa_gpu) __threadfence();
       __syncwarp();
       if (lane == 0) {
         __threadfence_block();  // the warp's slot stores are ordered before the count
@@ -126,8 +130,14 @@ __global__ void __launch_bounds__(SP::kWsThreads, 1) thread_fused_ws_kernel(cons
         }
         __threadfence_block();
         if (lane == 0) WS_TRACE(1, k);
-        st_release_sys((uint32_t*)((char*)tab.sig[lane] + kSigWsFaOff) + blockIdx.x * kMaxRanks + rank,
-                       base + (uint32_t)k + 1u);
+        if (a.fa_gpu) {
+          __threadfence();
+          st_relaxed_sys((uint32_t*)((char*)tab.sig[lane] + kSigWsFaOff) + blockIdx.x * kMaxRanks + rank,
+                         base + (uint32_t)k + 1u);
+        } else {
+          st_release_sys((uint32_t*)((char*)tab.sig[lane] + kSigWsFaOff) + blockIdx.x * kMaxRanks + rank,
+                         base + (uint32_t)k + 1u);
+        }
         if (lane == 0) WS_TRACE(2, k);
       }
     }
@@ -153,7 +163,7 @@ __global__ void __launch_bounds__(SP::kWsThreads, 1) thread_fused_ws_kernel(cons
       const int lo = (int)((long long)nv16 * rank / world), hi = (int)((long long)nv16 * (rank + 1) / world);
       // An NVLink round trip is ~2-3 us: keep kBatch independent 16-byte requests in flight per
       // thread (the asm volatile accessors are never reordered, so batching is explicit).
-      constexpr int kBatch = 8;
+      constexpr int kBatch = NVLS ? 16 : 8;  // NVLS holds only accumulators: 16 requests per lane = one round trip at 8 ranks
       const bool loc = (a.dbg & 8) != 0;
       for (int v0 = lo + lane; v0 < ((a.dbg & 1) ? lo : hi); v0 += 32 * kBatch) {
         Vec16 acc[kBatch];

@@ -119,7 +119,7 @@ __global__ void __launch_bounds__(kTThreads, 2) thread_allreduce_kernel(const __
       V acc = reduce_threads<U>(bufs, nT, b0 + (unsigned long long)(c0 + u) * UB);
       U::st(my_slot + u * UB, acc);
     }
-    block_barrier_peers(tab, rank, ep);
+    if (!block_barrier_peers(tab, rank, ep)) break;  // peer missing: store nothing more
     // ---- phase B: inter-GPU reduce of sub-slice `rank`, pushed to every peer
     const long long lo = len * rank / world, hi = len * (rank + 1) / world;
     for (long long u = lo + threadIdx.x; u < hi; u += blockDim.x) {
@@ -141,7 +141,7 @@ __global__ void __launch_bounds__(kTThreads, 2) thread_allreduce_kernel(const __
           if (q < world) U::st(tab.heap[q] + o, acc);
       }
     }
-    block_barrier_peers(tab, rank, ep);
+    if (!block_barrier_peers(tab, rank, ep)) break;
     // ---- phase C: fan the finished chunk out to the T thread buffers
     for (long long u = threadIdx.x; u < len; u += blockDim.x) {
       V x = U::ld_co(my_slot + u * UB);

@@ -24,6 +24,7 @@ ProcessComm::ProcessComm(const std::string& login, const std::string& master_hos
                                      : my_host;
   std::string me = host + kAddrDelim + std::to_string(listen_port_);
   rank_ = master_->rendezvous(me, rank_hint, &addrs_);
+  master_->open_local_log(rank_);
   n_ = (int)addrs_.size();
   for (auto& a : addrs_) {
     size_t k = a.rfind(kAddrDelim);

@@ -3,6 +3,7 @@
 // Exit code: 0 iff every slave closed with code 0; 1 otherwise; 2/3/201 for watchdog timeouts.
 #include <stdio.h>
 #include <stdlib.h>
+#include <unistd.h>
 
 #include "../control/control.h"
 
@@ -13,8 +14,12 @@ int main(int argc, char** argv) {
   }
   int code = 1;
   try {
+    // like the reference's master, which finds config/log4j_master.properties next to its start script
+    if (!getenv("MP4J_LOG_CONFIG") && access("config/logging.properties", R_OK) == 0)
+      setenv("MP4J_LOG_CONFIG", "config/logging.properties", 0);
     mp4j::MasterOptions opt;
-    opt.log_dir = argc > 3 ? argv[3] : "log";
+    if (argc > 3) opt.log_dir = argv[3];
+    else if (!getenv("MP4J_LOG_CONFIG")) opt.log_dir = "log";
     if (getenv("MP4J_CONNECT_TIMEOUT_S")) opt.connect_timeout_s = atoi(getenv("MP4J_CONNECT_TIMEOUT_S"));
     if (getenv("MP4J_HEARTBEAT_TIMEOUT_S")) opt.heartbeat_timeout_s = atoi(getenv("MP4J_HEARTBEAT_TIMEOUT_S"));
     mp4j::Master master(atoi(argv[1]), atoi(argv[2]), opt);

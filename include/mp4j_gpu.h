@@ -125,8 +125,11 @@ int mp4j_gpu_gbdt_hist_reduce_scatter(mp4j_gpu* g, const uint8_t* const* bins, c
 /* Local reduce-by-key on one GPU: the thread-level map merge (DOP:458-477) on device arrays.
  * out_keys/out_vals (capacity out_cap pairs) receive the unique keys with equal keys reduced by
  * `op` (SUM/MAX/MIN; float/double/int/long values), *out_count (device uint64) their number.
- * The hash table is scratch owned by the plane (allocated with cudaMalloc, cached, grown on
- * demand). Result order is unspecified. */
+ * *out_count is the FULL number of unique keys: if it exceeds out_cap only out_cap pairs were
+ * stored (never more), so compare the two to detect truncation and never read beyond
+ * min(*out_count, out_cap). Key INT64_MIN (0x8000000000000000) is reserved as the table's "free
+ * slot" marker: pairs carrying it are ignored. The hash table is scratch owned by the plane
+ * (allocated with cudaMalloc, cached, grown on demand). Result order is unspecified. */
 int mp4j_gpu_map_reduce_local(mp4j_gpu* g, int local_rank, const int64_t* keys, const void* vals, int64_t n,
                               int dtype, int op, int64_t* out_keys, void* out_vals, int64_t out_cap,
                               uint64_t* out_count, void* stream);
@@ -139,8 +142,10 @@ int mp4j_gpu_map_reduce_local(mp4j_gpu* g, int local_rank, const int64_t* keys, 
  * mp4j_gpu plane whose cached scratch they could borrow.
  *
  * Same contract as mp4j_gpu_map_reduce_local (unique keys of (keys, vals) with equal keys reduced
- * by SUM/MAX/MIN; float/double/int/long values; result order unspecified; *out_count = number of
- * unique keys, clamped to out_cap), on the CURRENT device, with these differences:
+ * by SUM/MAX/MIN; float/double/int/long values; result order unspecified; *out_count = the full
+ * number of unique keys, which may exceed out_cap - at most out_cap pairs are stored, read no more
+ * than min(*out_count, out_cap); pairs whose key is INT64_MIN, the reserved free-slot marker, are
+ * ignored), on the CURRENT device, with these differences:
  *   - the hash table is a fixed 8 MiB array built into the library (held by every GPU that loads
  *     it until the process exits), so n may not exceed 262,144 pairs; larger n returns MP4J_ERR
  *     with a message naming the limit;

@@ -2,6 +2,7 @@
 // Not built on this image (no JDK / jni.h): see java/build.sh. The same C ABI is exercised from
 // Python (ctypes) by the test-suite, so the surface below is covered even where Java is absent.
 #include <jni.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "../../include/mp4j.h"
@@ -24,13 +25,41 @@ struct Longs {
   ~Longs() { e->ReleaseLongArrayElements(a, p, JNI_ABORT); }
   const int64_t* get() const { return (const int64_t*)p; }
 };
-// pins a primitive Java array for the duration of a host collective (in place, no copy)
+// A native copy of a primitive Java array for the duration of a host collective. The collective blocks on
+// sockets, futexes and master RPCs, and JNI forbids blocking inside a Get/ReleasePrimitiveArrayCritical
+// region (any other Java thread that triggers a GC would stall behind it - with T threads of a
+// ThreadCommSlave that can deadlock the job). So the critical pin is taken only around the two memcpys:
+// copy in, run the collective on the native buffer, copy the result back.
+static size_t elem_size(int dt) {
+  switch (dt) {
+    case MP4J_F64: case MP4J_I64: return 8;
+    case MP4J_F32: case MP4J_I32: return 4;
+    case MP4J_I16: case MP4J_BF16: case MP4J_F16: return 2;
+    default: return 1;
+  }
+}
 struct Pinned {
   JNIEnv* e;
   jarray a;
   void* p;
-  Pinned(JNIEnv* env, jobject arr) : e(env), a((jarray)arr), p(env->GetPrimitiveArrayCritical((jarray)arr, nullptr)) {}
-  ~Pinned() { e->ReleasePrimitiveArrayCritical(a, p, 0); }
+  size_t bytes;
+  Pinned(JNIEnv* env, jobject arr, int dt) : e(env), a((jarray)arr), p(nullptr), bytes(0) {
+    bytes = (size_t)env->GetArrayLength(a) * elem_size(dt);
+    p = malloc(bytes ? bytes : 1);
+    void* j = env->GetPrimitiveArrayCritical(a, nullptr);
+    if (j) {
+      memcpy(p, j, bytes);
+      env->ReleasePrimitiveArrayCritical(a, j, JNI_ABORT);  // nothing written to the Java array yet
+    }
+  }
+  ~Pinned() {
+    void* j = e->GetPrimitiveArrayCritical(a, nullptr);
+    if (j) {
+      memcpy(j, p, bytes);
+      e->ReleasePrimitiveArrayCritical(a, j, 0);
+    }
+    free(p);
+  }
 };
 jbyteArray to_bytes(JNIEnv* env, char* data, size_t n) {
   jbyteArray out = env->NewByteArray((jsize)n);
@@ -81,38 +110,38 @@ FN(jint, commWriteFile)(JNIEnv* env, jclass, jlong h, jstring content, jstring n
 
 FN(jint, hostReduceScatter)(JNIEnv* env, jclass, jlong h, jobject arr, jint dt, jint op, jlong from, jlongArray counts) {
   Longs c(env, counts);
-  Pinned p(env, arr);
+  Pinned p(env, arr, dt);
   return mp4j_host_reduce_scatter((mp4j_comm*)h, p.p, dt, op, from, c.get());
 }
 FN(jint, hostAllgather)(JNIEnv* env, jclass, jlong h, jobject arr, jint dt, jlongArray froms, jlongArray tos) {
   Longs f(env, froms), t(env, tos);
-  Pinned p(env, arr);
+  Pinned p(env, arr, dt);
   return mp4j_host_allgather((mp4j_comm*)h, p.p, dt, f.get(), t.get());
 }
 FN(jint, hostGather)(JNIEnv* env, jclass, jlong h, jobject arr, jint dt, jlongArray froms, jlongArray tos, jint root) {
   Longs f(env, froms), t(env, tos);
-  Pinned p(env, arr);
+  Pinned p(env, arr, dt);
   return mp4j_host_gather((mp4j_comm*)h, p.p, dt, f.get(), t.get(), root);
 }
 FN(jint, hostScatter)(JNIEnv* env, jclass, jlong h, jobject arr, jint dt, jlongArray froms, jlongArray tos, jint root) {
   Longs f(env, froms), t(env, tos);
-  Pinned p(env, arr);
+  Pinned p(env, arr, dt);
   return mp4j_host_scatter((mp4j_comm*)h, p.p, dt, f.get(), t.get(), root);
 }
 FN(jint, hostBroadcast)(JNIEnv* env, jclass, jlong h, jobject arr, jint dt, jlong from, jlong to, jint root) {
-  Pinned p(env, arr);
+  Pinned p(env, arr, dt);
   return mp4j_host_broadcast((mp4j_comm*)h, p.p, dt, from, to, root);
 }
 FN(jint, hostReduce)(JNIEnv* env, jclass, jlong h, jobject arr, jint dt, jint op, jlong from, jlong to, jint root) {
-  Pinned p(env, arr);
+  Pinned p(env, arr, dt);
   return mp4j_host_reduce((mp4j_comm*)h, p.p, dt, op, from, to, root);
 }
 FN(jint, hostAllreduce)(JNIEnv* env, jclass, jlong h, jobject arr, jint dt, jint op, jlong from, jlong to) {
-  Pinned p(env, arr);
+  Pinned p(env, arr, dt);
   return mp4j_host_allreduce((mp4j_comm*)h, p.p, dt, op, from, to);
 }
 FN(jint, hostAllreduceRpc)(JNIEnv* env, jclass, jlong h, jobject arr, jint dt, jint op, jlong n) {
-  Pinned p(env, arr);
+  Pinned p(env, arr, dt);
   return mp4j_host_allreduce_rpc((mp4j_comm*)h, p.p, dt, op, n);
 }
 

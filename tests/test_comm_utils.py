@@ -74,3 +74,23 @@ def test_reference_halving_scatter_plan_delivers_every_slice():
                     pending.remove(s)
             assert all(r in have.get(r, ()) for r in range(p)), (p, root)
             assert all(recv_num(plan, r) <= 1 for r in range(p) if r != root), (p, root)
+
+
+def test_ranges_beyond_the_array_are_rejected():
+    """A `to` / `tos` / `from + counts` beyond the array length must raise instead of letting native code
+    read past the buffer (the reference throws ArrayIndexOutOfBoundsException)."""
+    import pytest
+    from ytk_mp4j_b200.exception import Mp4jException
+    CommUtils.isFromToLegal(0, 10, 10)
+    with pytest.raises(Mp4jException):
+        CommUtils.isFromToLegal(0, 11, 10)
+    CommUtils.isfromsTosLegal([0, 4], [4, 10], size=10)
+    with pytest.raises(Mp4jException):
+        CommUtils.isfromsTosLegal([0, 4], [4, 12], size=10)
+    with pytest.raises(Mp4jException):
+        CommUtils.isfromsTosLegal([[0, 2], [4, 6]], [[2, 4], [6, 11]], 2, size=10)
+    CommUtils.isFromCountsLegal(2, [4, 4], 10)
+    with pytest.raises(Mp4jException):
+        CommUtils.isFromCountsLegal(3, [4, 4], 10)
+    with pytest.raises(Mp4jException):
+        CommUtils.isFromCountsLegal(0, [[4, 4], [2, 1]], 10)

@@ -132,7 +132,7 @@ def test_thread_local_variants_agree(planes, thread_algo, name):
 
 
 @pytest.mark.parametrize("world,T", [(2, 8), (4, 4), (8, 2)])
-@pytest.mark.parametrize("thread_algo,name", [(5, "fused-ws"), (6, "fused-pull"), (4, "fused-tma"), (3, "fused-p2p")])
+@pytest.mark.parametrize("thread_algo,name", [(5, "fused-ws"), (6, "fused-pull"), (7, "fused-hybrid"), (4, "fused-tma"), (3, "fused-p2p")])
 def test_thread_fused_variants_agree(planes, world, T, thread_algo, name):
     """Warp-specialised kernel vs chunk-synchronous fallback: identical bits, several chunks per block."""
     plane = planes(world)

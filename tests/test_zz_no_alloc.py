@@ -89,3 +89,29 @@ def test_noalloc_rejects_oversize_and_bad_arguments():
     assert k.numel() == MAX_PAIRS and bool(torch.all(v == 1))
     k, v = _noalloc(fn, keys[:0], vals[:0], N.F32, N.SUM)
     assert k.numel() == 0
+
+
+def test_noalloc_count_beyond_capacity_and_reserved_key():
+    """Two corners of the contract in mp4j_gpu.h: *out_count is the full number of unique keys even when it
+    exceeds out_cap (only out_cap pairs are stored, nothing beyond the caller's buffer is touched), and pairs
+    whose key is INT64_MIN - the table's free-slot marker - are ignored without disturbing other keys."""
+    torch.cuda.set_device(0)
+    fn = _proto()
+    s = torch.cuda.current_stream().cuda_stream
+    # 1000 unique keys into a 100-pair output buffer with a guard zone behind it
+    keys = torch.arange(1000, dtype=torch.int64, device="cuda")
+    vals = torch.ones(1000, dtype=torch.float32, device="cuda")
+    ok = torch.full((200,), -7, dtype=torch.int64, device="cuda")
+    ov = torch.full((200,), -7.0, dtype=torch.float32, device="cuda")
+    cnt = torch.zeros(1, dtype=torch.int64, device="cuda")
+    assert fn(keys.data_ptr(), vals.data_ptr(), 1000, N.F32, N.SUM, ok.data_ptr(), ov.data_ptr(), 100, cnt.data_ptr(), s) == 0
+    torch.cuda.synchronize()
+    assert int(cnt.item()) == 1000
+    assert bool(torch.all(ok[100:] == -7)) and bool(torch.all(ov[100:] == -7.0))
+    assert bool(torch.all((ok[:100] >= 0) & (ok[:100] < 1000))) and bool(torch.all(ov[:100] == 1.0))
+    # the reserved key is dropped; every other key keeps exactly its own sum
+    int64_min = -(1 << 63)
+    keys = torch.tensor([5, int64_min, 7, int64_min, 5, 9], dtype=torch.int64, device="cuda")
+    vals = torch.tensor([1.0, 100.0, 2.0, 100.0, 3.0, 4.0], dtype=torch.float32, device="cuda")
+    k, v = _sorted_pairs(*_noalloc(fn, keys, vals, N.F32, N.SUM))
+    assert k.tolist() == [5, 7, 9] and v.tolist() == [4.0, 2.0, 4.0]

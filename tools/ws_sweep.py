@@ -51,6 +51,7 @@ def main():
         f = [int(x) for x in cfg.split(":")]
         ver, dbg, kib, slots, nvls = f[:5]
         plane.set_option("ws_tail_split", f[5] if len(f) > 5 else 4)
+        plane.set_option("ws_fa_gpu", f[6] if len(f) > 6 else 1)
         plane.set_option("ws_ver", ver)
         plane.set_option("ws_dbg", dbg)
         plane.set_option("thread_slot_bytes", kib << 10)

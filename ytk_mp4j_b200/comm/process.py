@@ -321,7 +321,7 @@ class ProcessCommSlave:
     # ------------------------------------------------------------------ gather
     def gatherArray(self, arrData, operand, sendfroms, sendtos, rootRank):
         """Rank i's [from_i, to_i) lands at the same offsets in root's array (PCS:535)."""
-        CommUtils.isfromsTosLegal(sendfroms, sendtos)
+        CommUtils.isfromsTosLegal(sendfroms, sendtos, size=len(arrData))
         self._check_root(rootRank)
         if self._n == 1:
             return arrData
@@ -357,7 +357,7 @@ class ProcessCommSlave:
 
     # ------------------------------------------------------------------ allgather
     def allgatherArray(self, arrData, operand, froms, tos):
-        CommUtils.isfromsTosLegal(froms, tos)
+        CommUtils.isfromsTosLegal(froms, tos, size=len(arrData))
         if self._n == 1:
             return arrData
         if _is_cuda(arrData):
@@ -385,7 +385,7 @@ class ProcessCommSlave:
     # ------------------------------------------------------------------ broadcast
     def broadcastArray(self, arrData, operand, from_, to, rootRank):
         """= scatter of p balanced chunks + allgather (PCS:750-770)."""
-        CommUtils.isFromToLegal(from_, to)
+        CommUtils.isFromToLegal(from_, to, len(arrData))
         self._check_root(rootRank)
         if self._n == 1:
             return arrData
@@ -426,7 +426,7 @@ class ProcessCommSlave:
 
     # ------------------------------------------------------------------ scatter
     def scatterArray(self, arrData, operand, recvfroms, recvtos, rootRank):
-        CommUtils.isfromsTosLegal(recvfroms, recvtos)
+        CommUtils.isfromsTosLegal(recvfroms, recvtos, size=len(arrData))
         self._check_root(rootRank)
         if self._n == 1:
             return arrData
@@ -468,7 +468,7 @@ class ProcessCommSlave:
         """Rank r ends with the fully reduced [from+sum(counts[:r]), +counts[r]) (PCS:1174).
         Outside the owned slice the array keeps its input values on the GPU/generic paths
         (the reference leaves partial sums there, PCS:1162-1172; both are 'unspecified')."""
-        CommUtils.isFromCountsLegal(from_, counts)
+        CommUtils.isFromCountsLegal(from_, counts, len(arrData))
         if len(counts) != self._n:
             raise Mp4jException("counts must have one entry per slave")
         if self._n == 1:
@@ -500,7 +500,7 @@ class ProcessCommSlave:
     # ------------------------------------------------------------------ reduce
     def reduceArray(self, arrData, operand, operator, from_, to, rootRank):
         """= reduce-scatter + gather (PCS:1390-1416)."""
-        CommUtils.isFromToLegal(from_, to)
+        CommUtils.isFromToLegal(from_, to, len(arrData))
         self._check_root(rootRank)
         if self._n == 1:
             return arrData
@@ -538,7 +538,7 @@ class ProcessCommSlave:
         kernel chosen by size (one-shot / two-shot / NVLS)."""
         if to is None:
             to = len(arrData)
-        CommUtils.isFromToLegal(from_, to)
+        CommUtils.isFromToLegal(from_, to, len(arrData))
         if self._n == 1:
             return arrData
         if _is_cuda(arrData):

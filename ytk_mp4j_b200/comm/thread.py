@@ -198,7 +198,7 @@ class ThreadCommSlave:
         if self._T == 1:
             return self.processCommSlave.gatherArray(arrData, operand, CommUtils.getProcessFroms(sendfroms),
                                                      CommUtils.getProcessTos(sendtos), rootRank)
-        CommUtils.isfromsTosLegal(sendfroms, sendtos, self._T)
+        CommUtils.isfromsTosLegal(sendfroms, sendtos, self._T, size=len(arrData))
         rr = self._real_root(rootRank, rootThreadId)
         r = self.getRank()
         if self._native_thread(_GATHER, arrData, operand, None, lo=sendfroms, hi=sendtos, rootRank=rootRank,
@@ -218,7 +218,7 @@ class ThreadCommSlave:
         if self._T == 1:
             return self.processCommSlave.allgatherArray(arrData, operand, CommUtils.getProcessFroms(sendfroms),
                                                         CommUtils.getProcessTos(sendtos))
-        CommUtils.isfromsTosLegal(sendfroms, sendtos, self._T)
+        CommUtils.isfromsTosLegal(sendfroms, sendtos, self._T, size=len(arrData))
         r = self.getRank()
         pf, pt = CommUtils.getProcessFroms(sendfroms), CommUtils.getProcessTos(sendtos)
         if self._native_thread(_ALL_GATHER, arrData, operand, None, lo=sendfroms, hi=sendtos):
@@ -239,7 +239,7 @@ class ThreadCommSlave:
         if self._T == 1:
             return self.processCommSlave.broadcastArray(arrData, operand, from_, to, rootRank)
         rr = self._real_root(rootRank, rootThreadId)
-        CommUtils.isFromToLegal(from_, to)
+        CommUtils.isFromToLegal(from_, to, len(arrData))
         if self._native_thread(_BROADCAST, arrData, operand, None, from_, to, rootRank=rootRank,
                                rootThreadId=rootThreadId):
             return arrData
@@ -256,7 +256,7 @@ class ThreadCommSlave:
         if self._T == 1:
             return self.processCommSlave.scatterArray(arrData, operand, CommUtils.getProcessFroms(recvfroms),
                                                       CommUtils.getProcessTos(recvtos), rootRank)
-        CommUtils.isfromsTosLegal(recvfroms, recvtos, self._T)
+        CommUtils.isfromsTosLegal(recvfroms, recvtos, self._T, size=len(arrData))
         rr = self._real_root(rootRank, rootThreadId)
         r = self.getRank()
         if self._native_thread(_SCATTER, arrData, operand, None, lo=recvfroms, hi=recvtos, rootRank=rootRank,
@@ -277,7 +277,7 @@ class ThreadCommSlave:
         if self._T == 1:
             return self.processCommSlave.reduceScatterArray(arrData, operand, operator, from_,
                                                             [c[0] for c in counts])
-        CommUtils.isFromCountsLegal(from_, counts)
+        CommUtils.isFromCountsLegal(from_, counts, len(arrData))
         r = self.getRank()
         pcounts = [sum(c) for c in counts]
         total_to = from_ + sum(pcounts)
@@ -299,7 +299,7 @@ class ThreadCommSlave:
         if self._T == 1:
             return self.processCommSlave.reduceArray(arrData, operand, operator, from_, to, rootRank)
         rr = self._real_root(rootRank, rootThreadId)
-        CommUtils.isFromToLegal(from_, to)
+        CommUtils.isFromToLegal(from_, to, len(arrData))
         if self._native_thread(_REDUCE, arrData, operand, operator, from_, to, rootRank=rootRank,
                                rootThreadId=rootThreadId):
             return arrData
@@ -326,7 +326,7 @@ class ThreadCommSlave:
             raise Mp4jException("resultThread out of range")
         if self._T == 1:
             return self.processCommSlave.allreduceArray(arrData, operand, operator, from_, to)
-        CommUtils.isFromToLegal(from_, to)
+        CommUtils.isFromToLegal(from_, to, len(arrData))
         if self.processCommSlave._gpu_host_ok(arrData, operand, operator):
             # pinned host tensors with the GPU plane up: thread 0 streams all T arrays through the GPU
             # (H2D || fused kernel || D2H pipeline in the library); every thread's array gets the result

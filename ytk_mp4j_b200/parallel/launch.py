@@ -32,6 +32,8 @@ def main(argv=None):
     ap.add_argument("--host", default="127.0.0.1")
     ap.add_argument("--threads", type=int, default=1)
     ap.add_argument("--log-dir", default="log")
+    ap.add_argument("--log-config", default=None, help="logging.properties (default: ./config/logging.properties "
+                    "when present); levels, files and rolling of master and slave logs")
     ap.add_argument("--timeout", type=float, default=None)
     ap.add_argument("--check", action="store_true", help="run the CommCheckTool matrix instead of a script")
     ap.add_argument("--print-ssh", nargs="*", metavar="HOST", help="only print per-host ssh command lines")
@@ -43,6 +45,10 @@ def main(argv=None):
 
     if a.kill_previous and a.port and os.path.exists("kill_%d.sh" % a.port):
         subprocess.call(["sh", "kill_%d.sh" % a.port], stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    # logging configuration: read by the native core of the master (this process) and of every slave
+    cfg = a.log_config or ("config/logging.properties" if os.path.exists("config/logging.properties") else None)
+    if cfg and "MP4J_LOG_CONFIG" not in os.environ:
+        os.environ["MP4J_LOG_CONFIG"] = os.path.abspath(cfg)
     master = CommMaster(a.nproc, a.port, log_dir=a.log_dir, quiet=False).start()
     port = master.port
     if a.check:
@@ -74,6 +80,8 @@ def main(argv=None):
             envs = {"MP4J_MASTER_HOST": a.host, "MP4J_MASTER_PORT": port, "MP4J_RANK": i, "MP4J_WORLD": a.nproc,
                     "LOCAL_RANK": local, "MP4J_HOST": h, "MP4J_THREADS": a.threads,
                     "PYTHONPATH": root + os.pathsep + os.environ.get("PYTHONPATH", "")}
+            if os.environ.get("MP4J_LOG_CONFIG"):
+                envs["MP4J_LOG_CONFIG"] = os.environ["MP4J_LOG_CONFIG"]
             remote = "cd %s && env %s %s" % (shlex.quote(os.getcwd()),
                                             " ".join("%s=%s" % (k, shlex.quote(str(v))) for k, v in envs.items()),
                                             " ".join(shlex.quote(c) for c in cmd))

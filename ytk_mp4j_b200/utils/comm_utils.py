@@ -8,10 +8,12 @@ from ..exception import Mp4jException
 
 class CommUtils:
     @staticmethod
-    def isfromsTosLegal(froms, tos, threadNum=None):
+    def isfromsTosLegal(froms, tos, threadNum=None, size=None):
+        """size: length of the array the ranges index; a range that ends beyond it is rejected here (the
+        reference fails with ArrayIndexOutOfBoundsException; native code would read past the buffer)."""
         if threadNum is not None:  # 2-D form: [slaveNum][threadNum]
             for f, t in zip(froms, tos):
-                CommUtils.isfromsTosLegal(f, t)
+                CommUtils.isfromsTosLegal(f, t, size=size)
                 if len(f) != threadNum:
                     raise Mp4jException("froms arrays must be array[slaveNum][threadNum]")
                 if len(t) != threadNum:
@@ -29,27 +31,37 @@ class CommUtils:
                 raise Mp4jException("froms[i] must be <= tos[i]!")
             if i >= 1 and froms[i] < tos[i - 1]:
                 raise Mp4jException("froms[i] must be >= to[i - 1]")
+            if size is not None and tos[i] > size:
+                raise Mp4jException("tos[i] = %d is beyond the array length %d" % (tos[i], size))
 
     @staticmethod
-    def isFromCountsLegal(from_, counts):
+    def isFromCountsLegal(from_, counts, size=None):
         if from_ < 0:
             raise Mp4jException("from must be >= 0!")
+        total = 0
         for c in counts:
             if isinstance(c, (list, tuple)):
                 for cc in c:
                     if cc < 0:
                         raise Mp4jException("counts[i][j] must be >= 0!")
+                    total += cc
             elif c < 0:
                 raise Mp4jException("counts[i] must be >= 0!")
+            else:
+                total += c
+        if size is not None and from_ + total > size:
+            raise Mp4jException("from + sum(counts) = %d is beyond the array length %d" % (from_ + total, size))
 
     @staticmethod
-    def isFromToLegal(from_, to):
+    def isFromToLegal(from_, to, size=None):
         if from_ < 0:
             raise Mp4jException("from must be >= 0!")
         if to < 0:
             raise Mp4jException("to must be >= 0!")
         if from_ > to:
             raise Mp4jException("from must be <= to!")
+        if size is not None and to > size:
+            raise Mp4jException("to = %d is beyond the array length %d" % (to, size))
 
     @staticmethod
     def getFromsFromCount(from_, counts, slaveNum):
