@@ -209,6 +209,20 @@ int mp4j_gpu_thread_allreduce(mp4j_gpu* g, void* const* bufs, int T, int dtype, 
   MP4J_API_END
 }
 
+int mp4j_gpu_thread_segments(mp4j_gpu* g, void* const* bufs, int T, int dtype, int op, const int64_t* segs, int nseg,
+                             const char* name, void* stream) {
+  MP4J_API_BEGIN
+  // the name is kept by the plane for last(): map it onto static strings
+  static const char* const kNames[] = {"thread_gather", "thread_allgather", "thread_broadcast", "thread_scatter",
+                                       "thread_reduce_scatter", "thread_reduce"};
+  const char* nm = "thread_segments";
+  for (const char* k : kNames)
+    if (name && strcmp(name, k) == 0) nm = k;
+  TraceScope trace_scope(g->g, (cudaStream_t)stream, "mp4j.thread_segments");
+  g->g->thread_segments(bufs, T, dtype, op, segs, nseg, nm, (cudaStream_t)stream);
+  MP4J_API_END
+}
+
 int mp4j_gpu_thread_allreduce_host(mp4j_gpu* g, void* const* hbufs, int T, int dtype, int op, int64_t from,
                                    int64_t to, int fanout, int dst, void* stream) {
   MP4J_API_BEGIN

@@ -88,6 +88,11 @@ class GpuPlane {
   // local_only: skip the inter-GPU step (intra-process thread reduce, DOP:441-457).
   void thread_allreduce(void* const* bufs, int T, int dtype, int op, int64_t from, int64_t to, int fanout, int dst,
                         bool local_only, int algo, cudaStream_t s);
+  // The other six ThreadCommSlave array collectives as ONE launch (thread_seg.cu): a table of segments, each
+  // {lo, hi, src_rank, src_thread, dst_rank, dst_thread} (int64; src (-1,-1) = reduce over every thread of
+  // every rank with `op`, else copy from that thread; dst -1 = every rank / every thread). bufs[local_rank * T + t].
+  void thread_segments(void* const* bufs, int T, int dtype, int op, const int64_t* segs, int nseg, const char* name,
+                       cudaStream_t s);
   // Host arrays through the GPU plane (the reference's arrays ARE host arrays, PCS:1733 / TCS:1915): the
   // range is cut into chunks; chunk c+1 is copied in (one cudaMemcpyAsync per buffer on a copy stream)
   // while the fused kernel reduces chunk c and chunk c-1 is copied out on a third stream. hbufs[local_rank *

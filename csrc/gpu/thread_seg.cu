@@ -1,0 +1,381 @@
+// ThreadCommSlave gather / allgather / broadcast / scatter / reduce-scatter / reduce on CUDA tensors:
+// ONE launch per collective (TCS:448, 621, 802, 1010, 1174, 1396).
+//
+// The reference runs every one of them as "thread merge -> process collective -> thread copy" (three
+// passes over the data plus lg T Exchanger rounds). Here a collective is a table of SEGMENTS of the
+// common index space; each segment says where its value comes from and where it goes:
+//
+//   source       REDUCE : op over all T thread buffers of all ranks (thread-id order, then rank order)
+//                COPY   : thread ts of rank qs
+//   destination  thread td (or every thread) of rank qd (or of every rank)
+//
+//   reduceScatterArray  one REDUCE segment per (rank q, thread t) -> (q, t)      counts[q][t]
+//   reduceArray         one REDUCE segment                        -> (root rank, root thread)
+//   allgatherArray      one COPY segment per (q, t) from (q, t)   -> everybody
+//   gatherArray         one COPY segment per (q, t) from (q, t)   -> (root rank, root thread)
+//   scatterArray        one COPY segment per (q, t) from the root -> (q, t)
+//   broadcastArray      one COPY segment from the root            -> everybody
+//
+// The kernel cuts the segments into windows of one staging slot (64 KiB); block b walks windows b, b + G,
+// ... on every rank:
+//   stage 1 (source ranks)       fold / copy the local thread buffers of the window; write the local
+//                                destinations directly when the value is already final (COPY, or one
+//                                rank), else put it into this block's slot (double buffered)
+//   cross-GPU barrier            device-scope fence + relaxed flags: all cross-GPU traffic of this kernel
+//                                is LOADS from the peers' slots, nothing remote is ever stored
+//   stage 2 (destination ranks)  load the window from the source ranks' slots over NVLink (rank order for
+//                                REDUCE), write the local destination thread buffers
+// Only what a destination needs crosses NVLink, once. Unaligned segment ends (counts are arbitrary) are
+// handled element-wise; the 16-byte aligned interior of every window moves as 16-byte vectors.
+#include <algorithm>
+
+#include "../core/partition.h"
+#include "cuda_check.h"
+#include "custom_op.h"
+#include "dense.cuh"
+#include "gpu_plane.h"
+#include "launch.h"
+
+namespace mp4j {
+
+namespace {
+
+constexpr int kSegThreads = 256;
+constexpr int kMaxSegs = 128;
+constexpr int kAll = -1;
+
+struct SegItem {
+  long long lo, hi;  // element range
+  int src_rank, src_thread;  // kAll / kAll = REDUCE over everybody; else COPY from that thread
+  int dst_rank, dst_thread;  // kAll = every rank / every thread
+  long long first_window;    // index of the segment's first window in the launch's window list
+};
+
+struct SegArgs {
+  PeerTable tab;
+  int T;
+  int nseg;
+  int vec_ok;                    // all thread buffers share one alignment modulo 16
+  int base_mis;                  // that alignment (bytes)
+  unsigned long long stg_off;    // heap offset of the slots: [block][2][slot_bytes]
+  unsigned long long slot_bytes;
+  long long nwindows;
+  void* bufs[kMaxRanks][MP4J_MAX_THREADS];  // [rank][thread] in emulation, [0][thread] otherwise
+  SegItem seg[kMaxSegs];
+};
+
+// barrier between the same-index blocks of all ranks for kernels that only LOAD remote data: what the peers
+// will read is in this GPU's memory, so a device-scope fence by every writer orders it before the flag
+__device__ __forceinline__ bool block_barrier_pull(const PeerTable& t, int rank, BlockEpoch& ep) {
+  ep.value += 1;
+  __threadfence();
+  __syncthreads();
+  bool ok = true;
+  if (threadIdx.x < (unsigned)t.world) {
+    const int q = threadIdx.x;
+    st_relaxed_sys(t.sig[q] + blockIdx.x * kMaxRanks + rank, ep.value);
+    ok = wait_flag(t, t.sig[rank] + blockIdx.x * kMaxRanks + q, ep.value);
+  }
+  return __syncthreads_and(ok ? 1 : 0) != 0;
+}
+
+template <typename T, int OP>
+__device__ __forceinline__ T red1(T a, T b) {
+  if constexpr (OP == MP4J_COPY) return a;
+  else return Reduce<T, OP>::apply(a, b);
+}
+template <typename T, int OP>
+__device__ __forceinline__ Vec16 red16(const Vec16& a, const Vec16& b) {
+  if constexpr (OP == MP4J_COPY) return a;
+  else return vec_reduce<T, OP>(a, b);
+}
+
+template <typename T, int OP>
+__global__ void __launch_bounds__(kSegThreads, 2) thread_seg_kernel(const __grid_constant__ SegArgs a) {
+  constexpr long long ES = sizeof(T);
+  const PeerTable& tab = a.tab;
+  const int rank = my_rank(tab);
+  const int world = tab.world;
+  const int erow = tab.emulate ? rank : 0;
+  const int nT = a.T;
+  const long long CH = (long long)a.slot_bytes;
+  const long long c = a.base_mis;
+  BlockEpoch ep;
+  ep.load(tab, rank);
+  bool alive = true;
+  long long k = 0;
+  for (long long w = blockIdx.x; w < a.nwindows && alive; w += gridDim.x, ++k) {
+    // ---- which segment, which window of it
+    int lo_s = 0, hi_s = a.nseg - 1;
+    while (lo_s < hi_s) {
+      const int mid = (lo_s + hi_s + 1) >> 1;
+      if (a.seg[mid].first_window <= w) lo_s = mid;
+      else hi_s = mid - 1;
+    }
+    const SegItem& sg = a.seg[lo_s];
+    const bool reduce = sg.src_rank == kAll;
+    const bool is_src = reduce || sg.src_rank == rank;
+    const bool is_dst = sg.dst_rank == kAll || sg.dst_rank == rank;
+    // virtual byte offsets y = element offset * ES + c: y % 16 == address % 16 in every thread buffer
+    const long long ylo = sg.lo * ES + c, yhi = sg.hi * ES + c;
+    const long long win = ylo / CH + (w - sg.first_window);
+    const long long ya = max(ylo, win * CH), yb = min(yhi, (win + 1) * CH);
+    long long yva = (ya + 15) & ~15ll, yvb = yb & ~15ll;  // 16-byte aligned interior
+    if (!a.vec_ok || yva >= yvb) yva = yvb = ya;          // all scalar: [ya, yb) = head, no body, no tail
+    const long long nvec = (yvb - yva) / 16;
+    const long long nhead = (yva - ya) / ES, ntail = (yb - max(yvb, ya)) / ES;  // (yva == yvb == ya: tail = all)
+    const unsigned long long slot_off =
+        a.stg_off + ((unsigned long long)blockIdx.x * 2 + (unsigned long long)(k & 1)) * a.slot_bytes;
+    char* my_slot = tab.heap[rank] + slot_off - win * CH;  // my_slot + y = slot byte of virtual offset y
+    // Is the value final after the local step? COPY: yes. REDUCE: only with one rank.
+    const bool local_final = !reduce || world == 1;
+    // Does anybody else need this rank's contribution through the slot?
+    const bool to_slot = world > 1 && is_src && (reduce || sg.dst_rank == kAll || sg.dst_rank != rank);
+    const int td0 = sg.dst_thread == kAll ? 0 : sg.dst_thread, td1 = sg.dst_thread == kAll ? nT : sg.dst_thread + 1;
+
+    // ================= stage 1: local fold / copy
+    if (is_src) {
+      const bool write_local = local_final && is_dst;
+      auto buf = [&](int t, long long y) { return (char*)a.bufs[erow][t] + (y - c); };
+      // vector body. REDUCE: the loads of up to 8 thread buffers are in flight together (the accessors are
+      // asm volatile, so a load placed after a dependent reduce would wait for it), thread-id order.
+      // COPY: 4 independent vectors per thread.
+      if (reduce) {
+        for (long long v = threadIdx.x; v < nvec; v += kSegThreads) {
+          const long long y = yva + v * 16;
+          Vec16 acc;
+          for (int t0 = 0; t0 < nT; t0 += 8) {
+            Vec16 x[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+              if (t0 + j < nT) x[j] = ld_stream(buf(t0 + j, y));
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+              if (t0 + j < nT) acc = (t0 + j == 0) ? x[j] : red16<T, OP>(acc, x[j]);
+          }
+          if (to_slot) st_stream(my_slot + y, acc);
+          if (write_local)
+            for (int t = td0; t < td1; ++t) st_stream(buf(t, y), acc);
+        }
+      } else {
+        for (long long v0 = threadIdx.x; v0 < nvec; v0 += (long long)kSegThreads * 4) {
+          Vec16 acc[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const long long v = v0 + (long long)j * kSegThreads;
+            if (v < nvec) acc[j] = ld_stream(buf(sg.src_thread, yva + v * 16));
+          }
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const long long v = v0 + (long long)j * kSegThreads;
+            if (v < nvec) {
+              const long long y = yva + v * 16;
+              if (to_slot) st_stream(my_slot + y, acc[j]);
+              if (write_local)
+                for (int t = td0; t < td1; ++t)
+                  if (t != sg.src_thread) st_stream(buf(t, y), acc[j]);
+            }
+          }
+        }
+      }
+      // scalar head and tail
+      for (long long i = threadIdx.x; i < nhead + ntail; i += kSegThreads) {
+        const long long y = i < nhead ? ya + i * ES : max(yvb, ya) + (i - nhead) * ES;
+        T acc;
+        if (reduce) {
+          acc = *(const T*)buf(0, y);
+          for (int t = 1; t < nT; ++t) acc = red1<T, OP>(acc, *(const T*)buf(t, y));
+        } else {
+          acc = *(const T*)buf(sg.src_thread, y);
+        }
+        if (to_slot) *(T*)(my_slot + y) = acc;
+        if (write_local)
+          for (int t = td0; t < td1; ++t)
+            if (reduce || t != sg.src_thread) *(T*)buf(t, y) = acc;
+      }
+    }
+    if (world == 1) continue;
+
+    // ================= all ranks meet: the slots of this window are complete everywhere
+    if (!block_barrier_pull(tab, rank, ep)) {
+      alive = false;
+      break;
+    }
+
+    // ================= stage 2: pull from the source ranks' slots, write the local destinations
+    if (is_dst && (reduce || sg.src_rank != rank)) {
+      auto buf = [&](int t, long long y) { return (char*)a.bufs[erow][t] + (y - c); };
+      auto slot_of = [&](int q, long long y) { return tab.heap[q] + slot_off - win * CH + y; };
+      const int q0 = reduce ? 0 : sg.src_rank, q1 = reduce ? world : sg.src_rank + 1;
+      if (reduce) {
+        // all source ranks' loads of a vector are in flight together (one NVLink round trip), rank order
+        for (long long v = threadIdx.x; v < nvec; v += kSegThreads) {
+          const long long y = yva + v * 16;
+          Vec16 x[kMaxRanks];
+#pragma unroll
+          for (int q = 0; q < kMaxRanks; ++q)
+            if (q < world) x[q] = ld_coherent(slot_of(q, y));
+          Vec16 acc = x[0];
+#pragma unroll
+          for (int q = 1; q < kMaxRanks; ++q)
+            if (q < world) acc = red16<T, OP>(acc, x[q]);
+          for (int t = td0; t < td1; ++t) st_stream(buf(t, y), acc);
+        }
+      } else {
+        for (long long v0 = threadIdx.x; v0 < nvec; v0 += (long long)kSegThreads * 8) {
+          Vec16 acc[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const long long v = v0 + (long long)j * kSegThreads;
+            if (v < nvec) acc[j] = ld_coherent(slot_of(q0, yva + v * 16));
+          }
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const long long v = v0 + (long long)j * kSegThreads;
+            if (v < nvec)
+              for (int t = td0; t < td1; ++t) st_stream(buf(t, yva + v * 16), acc[j]);
+          }
+        }
+      }
+      for (long long i = threadIdx.x; i < nhead + ntail; i += kSegThreads) {
+        const long long y = i < nhead ? ya + i * ES : max(yvb, ya) + (i - nhead) * ES;
+        T acc = *(const volatile T*)slot_of(q0, y);
+        for (int q = q0 + 1; q < q1; ++q) acc = red1<T, OP>(acc, *(const volatile T*)slot_of(q, y));
+        for (int t = td0; t < td1; ++t) *(T*)buf(t, y) = acc;
+      }
+    }
+  }
+  // nobody leaves (and lets a later launch reuse the slots) while a peer may still read them
+  if (world > 1 && alive && k > 0) (void)block_barrier_pull(tab, rank, ep);
+  ep.store();
+}
+
+template <typename T, int OP>
+void launch_seg(const SegArgs& args, int grid, cudaStream_t stream) {
+  auto kfn = thread_seg_kernel<T, OP>;
+  if (args.tab.emulate && args.tab.world > 1) {
+    void* params[] = {(void*)&args};
+    MP4J_CUDA(cudaLaunchCooperativeKernel((const void*)kfn, dim3(grid, args.tab.world), dim3(kSegThreads), params, 0,
+                                          stream));
+  } else {
+    kfn<<<grid, kSegThreads, 0, stream>>>(args);
+    MP4J_CUDA(cudaGetLastError());
+  }
+}
+
+template <typename T, bool INTEGRAL, bool LOC>
+void seg_by_op(int op, const SegArgs& a, int grid, cudaStream_t s) {
+  switch (op) {
+    case MP4J_SUM: return launch_seg<T, MP4J_SUM>(a, grid, s);
+    case MP4J_MAX: return launch_seg<T, MP4J_MAX>(a, grid, s);
+    case MP4J_MIN: return launch_seg<T, MP4J_MIN>(a, grid, s);
+    case MP4J_PROD: return launch_seg<T, MP4J_PROD>(a, grid, s);
+  }
+  if constexpr (INTEGRAL) {
+    switch (op) {
+      case MP4J_BAND: return launch_seg<T, MP4J_BAND>(a, grid, s);
+      case MP4J_BOR: return launch_seg<T, MP4J_BOR>(a, grid, s);
+      case MP4J_BXOR: return launch_seg<T, MP4J_BXOR>(a, grid, s);
+    }
+  }
+  if constexpr (LOC) {
+    switch (op) {
+      case MP4J_MAXLOC: return launch_seg<T, MP4J_MAXLOC>(a, grid, s);
+      case MP4J_MINLOC: return launch_seg<T, MP4J_MINLOC>(a, grid, s);
+    }
+  }
+  throw Error("operator " + std::to_string(op) + " is not defined for this dtype on the GPU path");
+}
+
+int seg_blocks_per_sm() {
+  static int cached = -1;
+  if (cached < 0) {
+    int nb = 0;
+    MP4J_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, thread_seg_kernel<float, MP4J_SUM>, kSegThreads, 0));
+    cached = std::max(1, std::min(nb, 4));
+  }
+  return cached;
+}
+
+}  // namespace
+
+// segs: nseg x {lo, hi, src_rank, src_thread, dst_rank, dst_thread} (int64 each; -1 = all).
+void GpuPlane::thread_segments(void* const* bufs, int T, int dtype, int op, const int64_t* segs, int nseg,
+                               const char* name, cudaStream_t s) {
+  entry_check();
+  if (T < 1 || T > MP4J_MAX_THREADS) throw Error("thread count out of range");
+  if (nseg < 0 || nseg > kMaxSegs) throw Error("too many segments for one launch (max " + std::to_string(kMaxSegs) + ")");
+  const size_t es = dtype_size(dtype);
+  if (es == 0) throw Error("unknown dtype");
+  const int p = world();
+  const int L = local_ranks();
+  bool any_reduce = false;
+  SegArgs a{};
+  a.tab = table();
+  a.T = T;
+  for (int i = 0; i < L; ++i)
+    for (int t = 0; t < T; ++t) a.bufs[i][t] = bufs[(size_t)i * T + t];
+  const long long scale = 1;
+  a.vec_ok = 1;
+  a.base_mis = (int)((uintptr_t)bufs[0] & 15);
+  for (int i = 0; i < L * T; ++i)
+    if ((int)((uintptr_t)bufs[i] & 15) != a.base_mis) a.vec_ok = 0;
+  if (!a.vec_ok) a.base_mis = 0;
+  const size_t CH = std::max<size_t>(opt_.thread_slot_bytes, 64 << 10) / 16 * 16;
+  a.slot_bytes = CH;
+  a.stg_off = thread_off_;
+  long long nwin = 0;
+  int n = 0;
+  for (int i = 0; i < nseg; ++i) {
+    const int64_t* g = segs + (size_t)i * 6;
+    if (g[0] < 0 || g[1] < g[0]) throw Error("segment range is not legal");
+    if (g[1] == g[0]) continue;
+    SegItem& it = a.seg[n++];
+    it.lo = g[0] * scale;
+    it.hi = g[1] * scale;
+    it.src_rank = (int)g[2];
+    it.src_thread = (int)g[3];
+    it.dst_rank = (int)g[4];
+    it.dst_thread = (int)g[5];
+    if ((it.src_rank == kAll) != (it.src_thread == kAll)) throw Error("segment source must be (all, all) or one thread");
+    if (it.src_rank >= p || it.dst_rank >= p || it.src_thread >= T || it.dst_thread >= T) throw Error("segment endpoint out of range");
+    if (it.src_rank == kAll) any_reduce = true;
+    it.first_window = nwin;
+    const long long ylo = it.lo * (long long)es + a.base_mis, yhi = it.hi * (long long)es + a.base_mis;
+    nwin += (yhi - 1) / (long long)CH - ylo / (long long)CH + 1;
+  }
+  a.nseg = n;
+  a.nwindows = nwin;
+  if (n == 0) return;
+  if (any_reduce && (!plane_op_ok(dtype, op) || op == MP4J_COPY || is_custom_op(op)))
+    throw Error("operator is not defined for this dtype on the fused thread collectives");
+  long long cap = (long long)sms_ * seg_blocks_per_sm();
+  if (emulated()) cap = std::max(1, sms_ / p);
+  cap = std::min<long long>(cap, (long long)(thread_bytes_ / (2 * CH)));
+  cap = std::min<long long>(cap, kMaxBlocks);
+  if (opt_.max_blocks > 0) cap = std::min<long long>(cap, opt_.max_blocks);
+  const int grid = (int)std::max<long long>(1, std::min(cap, nwin));
+  last_ = CollStat{name, "fused-segments", 0, grid, false};
+  for (int i = 0; i < n; ++i) last_.bytes += (size_t)(a.seg[i].hi - a.seg[i].lo) * es;
+  const int kop = any_reduce ? op : MP4J_COPY;
+  if (kop == MP4J_COPY) {
+    // COPY segments never combine values: move them as raw elements of the same width
+    switch (es) {
+      case 8: return launch_seg<int64_t, MP4J_COPY>(a, grid, s);
+      case 4: return launch_seg<int32_t, MP4J_COPY>(a, grid, s);
+      case 2: return launch_seg<int16_t, MP4J_COPY>(a, grid, s);
+      default: return launch_seg<int8_t, MP4J_COPY>(a, grid, s);
+    }
+  }
+  switch (dtype) {
+    case MP4J_F64: return seg_by_op<double, false, true>(kop, a, grid, s);
+    case MP4J_F32: return seg_by_op<float, false, false>(kop, a, grid, s);
+    case MP4J_I64: return seg_by_op<int64_t, true, true>(kop, a, grid, s);
+    case MP4J_I32: return seg_by_op<int32_t, true, false>(kop, a, grid, s);
+    case MP4J_I16: return seg_by_op<int16_t, true, false>(kop, a, grid, s);
+    case MP4J_I8: return seg_by_op<int8_t, true, false>(kop, a, grid, s);
+  }
+  throw Error("dtype " + std::to_string(dtype) + " is not supported by the fused thread collectives");
+}
+
+}  // namespace mp4j

@@ -81,6 +81,16 @@ int mp4j_gpu_thread_allreduce(mp4j_gpu* g, void* const* bufs, int T, int dtype, 
                               int64_t to, int fanout, int dst, int local_only, int thread_algo, int algo,
                               void* stream);
 
+/* ThreadCommSlave gatherArray / allgatherArray / broadcastArray / scatterArray / reduceScatterArray /
+ * reduceArray on device buffers as ONE launch (TCS:448, 621, 802, 1010, 1174, 1396): bufs[local_rank * T + t],
+ * segs = nseg x {lo, hi, src_rank, src_thread, dst_rank, dst_thread} (int64 each). A segment whose source is
+ * (-1, -1) is the reduction, with `op`, of that element range over every thread of every rank (thread-id order,
+ * then rank order); otherwise it is copied from that one thread. Destination -1 = every rank / every thread.
+ * Segments must not overlap. At most 128 non-empty segments per call. name: "thread_gather" ... "thread_reduce"
+ * (for mp4j_gpu_last / tracing). */
+int mp4j_gpu_thread_segments(mp4j_gpu* g, void* const* bufs, int T, int dtype, int op, const int64_t* segs, int nseg,
+                             const char* name, void* stream);
+
 /* ThreadCommSlave.allreduceArray / ProcessCommSlave.allreduceArray (T = 1) on HOST arrays, streamed through
  * the GPU plane (TCS:1915, PCS:1733: the reference's arrays are host arrays): hbufs[local_rank * T + t] are host
  * pointers, pinned for full speed. The range is cut into chunks (MP4J_HOST_CHUNK_BYTES per buffer, default 8 MiB);

@@ -12,7 +12,7 @@ pytestmark = pytest.mark.gpu
 
 def test_missing_peer_raises_and_poisons_the_plane():
     from ytk_mp4j_b200.parallel.gpu_plane import EmuPlane
-    plane = EmuPlane(2, 0, heap_bytes=64 << 20, staging_bytes=4 << 20)
+    plane = EmuPlane(2, 0, heap_bytes=192 << 20, staging_bytes=4 << 20)
     try:
         n = 1 << 20
         ts = [torch.full((n,), float(r + 1), device="cuda") for r in range(2)]

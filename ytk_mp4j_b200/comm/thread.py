@@ -154,6 +154,22 @@ class ThreadCommSlave:
                                            flat(lo), flat(hi), flat(counts), rootRank, rootThreadId))
         return True
 
+    def _gpu_segments(self, name, arrData, operand, operator, segs, root_thread=0):
+        """CUDA tensors: the whole collective (thread step + inter-GPU step + thread step) as ONE launch of the
+        segment kernel (csrc/gpu/thread_seg.cu). Returns False if this call cannot take it (too many segments,
+        custom operator, 16-bit floats): the caller then composes it from separate steps."""
+        if not _is_cuda(arrData):
+            return False
+        segs = [s for s in segs if s[1] > s[0]]
+        if not self.gpu.thread_segments_ok([arrData], operand, operator, len(segs)):
+            return False
+
+        def run(arrs):
+            self.gpu.thread_segments(name, arrs, operand, operator, segs)
+            return None
+        self._delegate(arrData, run, root_thread)
+        return True
+
     def _real_root(self, rootRank, rootThreadId):
         if rootThreadId < 0 or rootThreadId >= self._T:
             raise Mp4jException("rootThreadId out of range")
@@ -201,6 +217,10 @@ class ThreadCommSlave:
         CommUtils.isfromsTosLegal(sendfroms, sendtos, self._T, size=len(arrData))
         rr = self._real_root(rootRank, rootThreadId)
         r = self.getRank()
+        if self._gpu_segments("thread_gather", arrData, operand, None,
+                              [(sendfroms[q][t], sendtos[q][t], q, t, rootRank, rootThreadId)
+                               for q in range(self.getSlaveNum()) for t in range(self._T)], rr):
+            return arrData
         if self._native_thread(_GATHER, arrData, operand, None, lo=sendfroms, hi=sendtos, rootRank=rootRank,
                                rootThreadId=rootThreadId):
             return arrData
@@ -221,6 +241,10 @@ class ThreadCommSlave:
         CommUtils.isfromsTosLegal(sendfroms, sendtos, self._T, size=len(arrData))
         r = self.getRank()
         pf, pt = CommUtils.getProcessFroms(sendfroms), CommUtils.getProcessTos(sendtos)
+        if self._gpu_segments("thread_allgather", arrData, operand, None,
+                              [(sendfroms[q][t], sendtos[q][t], q, t, -1, -1)
+                               for q in range(self.getSlaveNum()) for t in range(self._T)]):
+            return arrData
         if self._native_thread(_ALL_GATHER, arrData, operand, None, lo=sendfroms, hi=sendtos):
             return arrData
 
@@ -240,6 +264,9 @@ class ThreadCommSlave:
             return self.processCommSlave.broadcastArray(arrData, operand, from_, to, rootRank)
         rr = self._real_root(rootRank, rootThreadId)
         CommUtils.isFromToLegal(from_, to, len(arrData))
+        if self._gpu_segments("thread_broadcast", arrData, operand, None,
+                              [(from_, to, rootRank, rootThreadId, -1, -1)], rr):
+            return arrData
         if self._native_thread(_BROADCAST, arrData, operand, None, from_, to, rootRank=rootRank,
                                rootThreadId=rootThreadId):
             return arrData
@@ -259,6 +286,10 @@ class ThreadCommSlave:
         CommUtils.isfromsTosLegal(recvfroms, recvtos, self._T, size=len(arrData))
         rr = self._real_root(rootRank, rootThreadId)
         r = self.getRank()
+        if self._gpu_segments("thread_scatter", arrData, operand, None,
+                              [(recvfroms[q][t], recvtos[q][t], rootRank, rootThreadId, q, t)
+                               for q in range(self.getSlaveNum()) for t in range(self._T)], rr):
+            return arrData
         if self._native_thread(_SCATTER, arrData, operand, None, lo=recvfroms, hi=recvtos, rootRank=rootRank,
                                rootThreadId=rootThreadId):
             return arrData
@@ -281,6 +312,14 @@ class ThreadCommSlave:
         r = self.getRank()
         pcounts = [sum(c) for c in counts]
         total_to = from_ + sum(pcounts)
+        if _is_cuda(arrData):
+            segs, off = [], from_
+            for q in range(self.getSlaveNum()):
+                for t in range(self._T):
+                    segs.append((off, off + counts[q][t], -1, -1, q, t))
+                    off += counts[q][t]
+            if self._gpu_segments("thread_reduce_scatter", arrData, operand, operator, segs):
+                return arrData
         if self._native_thread(_REDUCE_SCATTER, arrData, operand, operator, from_, total_to, counts=counts):
             return arrData
 
@@ -300,6 +339,9 @@ class ThreadCommSlave:
             return self.processCommSlave.reduceArray(arrData, operand, operator, from_, to, rootRank)
         rr = self._real_root(rootRank, rootThreadId)
         CommUtils.isFromToLegal(from_, to, len(arrData))
+        if self._gpu_segments("thread_reduce", arrData, operand, operator,
+                              [(from_, to, -1, -1, rootRank, rootThreadId)], rr):
+            return arrData
         if self._native_thread(_REDUCE, arrData, operand, operator, from_, to, rootRank=rootRank,
                                rootThreadId=rootThreadId):
             return arrData

@@ -40,6 +40,8 @@ _P("mp4j_gpu_reduce", C.c_int, C.c_void_p, N.c_vpp, C.c_int, C.c_int, C.c_int64,
 _P("mp4j_gpu_thread_allreduce", C.c_int, C.c_void_p, N.c_vpp, C.c_int, C.c_int, C.c_int, C.c_int64, C.c_int64,
    C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p)
 
+_P("mp4j_gpu_thread_segments", C.c_int, C.c_void_p, N.c_vpp, C.c_int, C.c_int, C.c_int, N.c_i64p, C.c_int, C.c_char_p,
+   C.c_void_p)
 _P("mp4j_gpu_thread_allreduce_host", C.c_int, C.c_void_p, N.c_vpp, C.c_int, C.c_int, C.c_int, C.c_int64, C.c_int64,
    C.c_int, C.c_int, C.c_void_p)
 
@@ -252,6 +254,15 @@ class _PlaneBase:
         check(N.lib.mp4j_gpu_thread_allreduce(self._g, _ptr_array(ts), T, code, op, f, t, 1 if fanout else 0, dst,
                                               1 if local_only else 0, thread_algo, algo, _stream_ptr(stream)))
 
+
+    MAX_SEGMENTS = 128
+    SEG_REDUCE_DTYPES = (N.F64, N.F32, N.I64, N.I32, N.I16, N.I8)
+
+    def _thread_segments(self, ts, T, code, op, segs, name, stream):
+        """segs: list of (lo, hi, src_rank, src_thread, dst_rank, dst_thread); -1 = all (see mp4j_gpu.h)."""
+        flat = [int(x) for s in segs for x in s]
+        check(N.lib.mp4j_gpu_thread_segments(self._g, _ptr_array(ts), T, code, op, N.i64_array(flat), len(segs),
+                                             name.encode(), _stream_ptr(stream)))
 
     def _thread_allreduce_host(self, ts, T, code, op, f, t, fanout, dst, stream):
         check(N.lib.mp4j_gpu_thread_allreduce_host(self._g, _ptr_array(ts), T, code, op, f, t, 1 if fanout else 0, dst,
@@ -470,6 +481,23 @@ class GpuPlane(_PlaneBase):
         self._thread_allreduce_host(ts, len(ts), _code_of(ts[0], operand), self._op(operator, operand.code), f, to,
                                     fanout, dst, stream)
 
+    def thread_segments_ok(self, ts, operand, operator, nseg):
+        """Can the one-launch segment kernel run this collective? (else the caller composes it from the
+        thread reduce, the dense collective and copies)"""
+        if nseg > self.MAX_SEGMENTS or not all(t.is_cuda and t.dim() == 1 and t.is_contiguous() for t in ts):
+            return False
+        if operator is None:
+            return ts[0].dtype in DTYPE_CODES
+        return operator.is_native and DTYPE_CODES.get(ts[0].dtype) in self.SEG_REDUCE_DTYPES
+
+    def thread_segments(self, name, ts, operand, operator, segs, stream=None):
+        """gather / allgather / broadcast / scatter / reduce-scatter / reduce of the T thread tensors of this
+        process (and of every other rank's) in ONE launch; segs as in mp4j_gpu_thread_segments."""
+        for t in ts:
+            _check_tensor(t)
+        op = N.COPY if operator is None else self._op(operator, operand.code)
+        self._thread_segments(ts, len(ts), _code_of(ts[0], operand), op, segs, name, stream)
+
     def thread_reduce(self, ts, operand, operator, f, to, dst, stream=None):
         """Intra-process reduce of the T buffers into ts[dst] (thread path of DOP:441-457)."""
         for t in ts:
@@ -550,6 +578,12 @@ class EmuPlane(_PlaneBase):
         flat = [x for row in ts_by_rank for x in row]
         self._thread_allreduce(flat, T, _code_of(flat[0]), op, f, t, fanout, dst, local_only, thread_algo, algo,
                                stream)
+
+    def thread_segments(self, name, ts_by_rank, op, segs, stream=None):
+        """ts_by_rank: [rank][thread] tensors; op: native operator code or N.COPY."""
+        T = len(ts_by_rank[0])
+        flat = [x for row in ts_by_rank for x in row]
+        self._thread_segments(flat, T, _code_of(flat[0]), op, segs, name, stream)
 
     def thread_allreduce_host(self, ts_by_rank, op, f, t, fanout=True, dst=0, stream=None):
         """ts_by_rank: [rank][thread] HOST tensors (see GpuPlane.thread_allreduce_host)."""
