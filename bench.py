@@ -136,6 +136,9 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--e2e-fanout", action="store_true", help="e2e: write the result into all T host arrays")
+    ap.add_argument("--no-extras", action="store_true",
+                    help="N >= 2: skip the correctness matrix and the dense float/double sweep vs NCCL")
+    ap.add_argument("--sweep-max-bytes", type=int, default=1 << 30)
     args = ap.parse_args()
     if args.impl == "reference":
         return reference_arm()
@@ -162,7 +165,9 @@ def main():
         port = base_port + 17
     comm = ThreadCommSlave("bench", T, addr, port, rank_hint=rank, host="127.0.0.1")
     pcs = comm.processCommSlave
-    plane = comm.init_gpu(device=local_rank)
+    extras = world > 1 and not args.no_extras
+    # the dense sweep needs a symmetric pool of the largest message next to the plane's own regions
+    plane = comm.init_gpu(device=local_rank, heap_bytes=(args.sweep_max_bytes + (1 << 30)) if extras else None)
     fop, SUM = Operands.FLOAT_OPERAND(), Operators.Float.SUM
     P = world * T
     S = n * 4
@@ -264,6 +269,22 @@ def main():
                "api": "ThreadCommSlave.allreduceArray on pinned host tensors (T python threads); result in "
                       + ("all T host arrays" if rt is None else "thread 0's host array (resultThread=0)")}
 
+    # ---- N >= 2: the rest of the product on the real multi-GPU path, under the driver's eyes
+    correctness = sweep = None
+    if extras:
+        sys.path.insert(0, os.path.join(ROOT, "bench"))
+        import driver_extras
+        del bufs
+        torch.cuda.empty_cache()
+        correctness = driver_extras.correctness_matrix(pcs, plane, rank, world)
+        sweep = driver_extras.dense_sweep(pcs, plane, rank, world, max_bytes=args.sweep_max_bytes)
+        try:
+            import torch.distributed as dist
+            if dist.is_initialized():
+                dist.destroy_process_group()
+        except Exception:  # noqa: BLE001
+            pass
+
     pcs.barrier()
     comm.close(0)
     if master is not None:
@@ -299,6 +320,8 @@ def main():
             "clocks": clocks,
             "gpu_launches": K,
             "e2e": e2e,
+            "correctness_matrix": correctness,
+            "dense_sweep": sweep,
         }
         try:
             peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))

@@ -34,6 +34,10 @@ void GpuOptions::load_env() {
   thread_slots = (int)env_size("MP4J_THREAD_SLOTS", (size_t)thread_slots);
   oneshot_max_bytes = env_size("MP4J_ONE_SHOT_MAX_BYTES", oneshot_max_bytes);
   nvls_min_bytes = env_size("MP4J_NVLS_MIN_BYTES", nvls_min_bytes);
+  rs_nvls_min_bytes = env_size("MP4J_RS_NVLS_MIN_BYTES", rs_nvls_min_bytes);
+  ag_nvls_min_bytes = env_size("MP4J_AG_NVLS_MIN_BYTES", ag_nvls_min_bytes);
+  rs_nvls_max_bytes = env_size("MP4J_RS_NVLS_MAX_BYTES", rs_nvls_max_bytes);
+  ag_nvls_max_bytes = env_size("MP4J_AG_NVLS_MAX_BYTES", ag_nvls_max_bytes);
   max_blocks = (int)env_size("MP4J_MAX_BLOCKS", (size_t)max_blocks);
   nvls_min_world = (int)env_size("MP4J_NVLS_MIN_WORLD", (size_t)nvls_min_world);
   poll_ns = (int)env_size("MP4J_POLL_NS", (size_t)poll_ns);
@@ -58,6 +62,10 @@ bool GpuPlane::set_option(const std::string& name, long long v) {
   }
   else if (name == "nvls_min_world") opt_.nvls_min_world = (int)v;
   else if (name == "nvls_min_bytes") opt_.nvls_min_bytes = (size_t)v;
+  else if (name == "rs_nvls_min_bytes") opt_.rs_nvls_min_bytes = (size_t)v;
+  else if (name == "ag_nvls_min_bytes") opt_.ag_nvls_min_bytes = (size_t)v;
+  else if (name == "rs_nvls_max_bytes") opt_.rs_nvls_max_bytes = (size_t)v;
+  else if (name == "ag_nvls_max_bytes") opt_.ag_nvls_max_bytes = (size_t)v;
   else if (name == "oneshot_max_bytes") opt_.oneshot_max_bytes = std::min((size_t)v, oneshot_slot_bytes_);
   else if (name == "max_blocks") opt_.max_blocks = (int)v;
   else if (name == "poll_ns") opt_.poll_ns = (int)v;
@@ -244,6 +252,8 @@ void GpuPlane::run_grs(const char* name, void* const* arrs, int dtype, int op, c
   }
   if (max_n == 0) return;
   const size_t span_bytes = (size_t)(span_hi - span_lo) * es;
+  const int family = (!strcmp(name, "reduce_scatter") || !strcmp(name, "reduce")) ? 1
+                     : (!strcmp(name, "allgather") || !strcmp(name, "broadcast")) ? 2 : 0;
 
   GrsArgs a{};
   a.tab = table();
@@ -252,7 +262,7 @@ void GpuPlane::run_grs(const char* name, void* const* arrs, int dtype, int op, c
   a.vec_ok = 1;
   a.dead_rank_p1 = dead_rank_p1_;
   const bool nvls_ok = has_multicast() && nvls_supported(dtype, op) &&
-                       (algo == MP4J_ALGO_NVLS || (algo == MP4J_ALGO_AUTO && nvls_auto(span_bytes)));
+                       (algo == MP4J_ALGO_NVLS || (algo == MP4J_ALGO_AUTO && nvls_auto(span_bytes, family)));
   last_.name = name;
   last_.bytes = span_bytes;
 

@@ -32,6 +32,12 @@ struct GpuOptions {
   int thread_slots = 4;
   size_t oneshot_max_bytes = 256 << 10; // <= : one-shot allreduce (MP4J_ONE_SHOT_MAX_BYTES)
   size_t nvls_min_bytes = 512 << 10;    // >= : NVLS when available (MP4J_NVLS_MIN_BYTES)
+  // the same threshold for the reduce-scatter family (reduce-scatter, reduce) and the allgather family (allgather,
+  // broadcast); 0 = follow nvls_min_bytes. Their crossovers differ from allreduce's (tuning/*.json).
+  size_t rs_nvls_min_bytes = 0;         // MP4J_RS_NVLS_MIN_BYTES
+  size_t ag_nvls_min_bytes = 0;         // MP4J_AG_NVLS_MIN_BYTES
+  size_t rs_nvls_max_bytes = 0;         // >= : two-shot again (0 = no upper end; MP4J_RS_NVLS_MAX_BYTES)
+  size_t ag_nvls_max_bytes = 0;         // MP4J_AG_NVLS_MAX_BYTES
   int nvls_min_world = 2;               // AUTO uses NVLS only when world > this (MP4J_NVLS_MIN_WORLD)
   bool want_multicast = true;           // MP4J_NVLS=0 disables
   int max_blocks = 0;                   // 0 = occupancy-derived (MP4J_MAX_BLOCKS)
@@ -158,7 +164,14 @@ class GpuPlane {
   int pick_grid(long long max_units, int max_blocks_per_sm) const;
   // AUTO's NVLS rule, from measurement (profiles/): in-switch reduction only pays once it removes
   // traffic, i.e. beyond 2 ranks, and for messages large enough to amortise the multicast path.
-  bool nvls_auto(size_t bytes) const { return world() > opt_.nvls_min_world && bytes >= opt_.nvls_min_bytes; }
+  bool nvls_auto(size_t bytes, int family = 0) const {  // family: 0 allreduce, 1 reduce-scatter, 2 allgather
+    size_t th = opt_.nvls_min_bytes;
+    if (family == 1 && opt_.rs_nvls_min_bytes) th = opt_.rs_nvls_min_bytes;
+    if (family == 2 && opt_.ag_nvls_min_bytes) th = opt_.ag_nvls_min_bytes;
+    const size_t mx = family == 1 ? opt_.rs_nvls_max_bytes : (family == 2 ? opt_.ag_nvls_max_bytes : 0);
+    if (mx && bytes >= mx) return false;
+    return world() > opt_.nvls_min_world && bytes >= th;
+  }
   bool offsets_symmetric(void* const* arrs, size_t* off) const;
 
   SymmHeap heap_;

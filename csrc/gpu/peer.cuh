@@ -36,7 +36,9 @@ constexpr size_t kSigPadBytes = 256 * 1024;           // everything above, zero-
 // diagnostics (MP4J_WS_DBG bit 128): per-chunk stage timestamps of block 0, kWsTraceChunks x 8 x u64
 constexpr size_t kSigWsTraceOff = kSigWsFcEnd;
 constexpr int kWsTraceChunks = 64;
-static_assert(kSigWsTraceOff + kWsTraceChunks * 8 * 8 <= kSigPadBytes, "signal pad layout overflows");
+// thread_seg.cu: "reader r has pulled this block's k-th window" [block][reader rank]
+constexpr size_t kSigSegFcOff = kSigWsTraceOff + kWsTraceChunks * 8 * 8;
+static_assert(kSigSegFcOff + kSigFlagsBytes <= kSigPadBytes, "signal pad layout overflows");
 
 struct PeerTable {
   int world;

@@ -57,27 +57,14 @@ struct SegArgs {
   int nseg;
   int vec_ok;                    // all thread buffers share one alignment modulo 16
   int base_mis;                  // that alignment (bytes)
-  unsigned long long stg_off;    // heap offset of the slots: [block][2][slot_bytes]
+  unsigned long long stg_off;    // heap offset of the slots: [block][kSegSlots][slot_bytes]
   unsigned long long slot_bytes;
   long long nwindows;
   void* bufs[kMaxRanks][MP4J_MAX_THREADS];  // [rank][thread] in emulation, [0][thread] otherwise
   SegItem seg[kMaxSegs];
 };
 
-// barrier between the same-index blocks of all ranks for kernels that only LOAD remote data: what the peers
-// will read is in this GPU's memory, so a device-scope fence by every writer orders it before the flag
-__device__ __forceinline__ bool block_barrier_pull(const PeerTable& t, int rank, BlockEpoch& ep) {
-  ep.value += 1;
-  __threadfence();
-  __syncthreads();
-  bool ok = true;
-  if (threadIdx.x < (unsigned)t.world) {
-    const int q = threadIdx.x;
-    st_relaxed_sys(t.sig[q] + blockIdx.x * kMaxRanks + rank, ep.value);
-    ok = wait_flag(t, t.sig[rank] + blockIdx.x * kMaxRanks + q, ep.value);
-  }
-  return __syncthreads_and(ok ? 1 : 0) != 0;
-}
+constexpr int kSegSlots = 4;  // staging slots per block: a source may run this many windows ahead of its readers
 
 template <typename T, int OP>
 __device__ __forceinline__ T red1(T a, T b) {
@@ -89,6 +76,75 @@ __device__ __forceinline__ Vec16 red16(const Vec16& a, const Vec16& b) {
   if constexpr (OP == MP4J_COPY) return a;
   else return vec_reduce<T, OP>(a, b);
 }
+
+// stage 2 of a REDUCE window for a compile-time world size: kB vectors x W source ranks = 8 loads in flight
+// per thread (an NVLink round trip is ~3 us; one vector at a time would make a window 16 round trips long)
+template <typename T, int OP, int W>
+__device__ __forceinline__ void pull_reduce(const SegArgs& a, int erow, unsigned long long slot_rel, int td0, int td1,
+                                            long long dst_rel, long long yva, long long nvec) {
+  const PeerTable& tab = a.tab;
+  constexpr int kB = 8 / W;
+  #pragma unroll 1
+  for (long long v0 = threadIdx.x; v0 < nvec; v0 += (long long)kSegThreads * kB) {
+    Vec16 x[kB][W];
+#pragma unroll
+    for (int j = 0; j < kB; ++j) {
+      const long long v = v0 + (long long)j * kSegThreads;
+#pragma unroll
+      for (int q = 0; q < W; ++q)
+        if (v < nvec) x[j][q] = ld_coherent(tab.heap[q] + slot_rel + yva + v * 16);
+    }
+#pragma unroll
+    for (int j = 0; j < kB; ++j) {
+      const long long v = v0 + (long long)j * kSegThreads;
+      if (v < nvec) {
+        Vec16 acc = x[j][0];
+#pragma unroll
+        for (int q = 1; q < W; ++q) acc = red16<T, OP>(acc, x[j][q]);  // ascending rank order
+        for (int t = td0; t < td1; ++t) st_stream((char*)a.bufs[erow][t] + dst_rel + yva + v * 16, acc);
+      }
+    }
+  }
+}
+
+// stage 1 of a REDUCE window for a compile-time thread count: 2 vectors x NT buffers = 16 independent 16-byte
+// loads in flight per thread, folded in thread-id order
+template <typename T, int OP, int NT>
+__device__ __forceinline__ void fold_reduce(const SegArgs& a, int erow, long long c, long long yva, long long nvec,
+                                            char* slot, bool write_local, int td0, int td1) {
+#pragma unroll 1
+  for (long long v0 = threadIdx.x; v0 < nvec; v0 += (long long)kSegThreads * 2) {
+    Vec16 x[2][NT];
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const long long v = v0 + (long long)j * kSegThreads;
+#pragma unroll
+      for (int t = 0; t < NT; ++t)
+        if (v < nvec) x[j][t] = ld_stream((const char*)a.bufs[erow][t] + (yva - c) + v * 16);
+    }
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const long long v = v0 + (long long)j * kSegThreads;
+      if (v < nvec) {
+        Vec16 acc = x[j][0];
+#pragma unroll
+        for (int t = 1; t < NT; ++t) acc = red16<T, OP>(acc, x[j][t]);
+        const long long y = yva + v * 16;
+        if (slot) st_stream(slot + y, acc);
+        if (write_local)
+          for (int t = td0; t < td1; ++t) st_stream((char*)a.bufs[erow][t] + (y - c), acc);
+      }
+    }
+  }
+}
+
+// One window of the launch: which segment it belongs to and its byte range.
+struct Win {
+  int seg;
+  bool reduce;
+  int src_rank, dst_rank;
+  long long win, ya, yb;
+};
 
 template <typename T, int OP>
 __global__ void __launch_bounds__(kSegThreads, 2) thread_seg_kernel(const __grid_constant__ SegArgs a) {
@@ -102,10 +158,15 @@ __global__ void __launch_bounds__(kSegThreads, 2) thread_seg_kernel(const __grid
   const long long c = a.base_mis;
   BlockEpoch ep;
   ep.load(tab, rank);
-  bool alive = true;
-  long long k = 0;
-  for (long long w = blockIdx.x; w < a.nwindows && alive; w += gridDim.x, ++k) {
-    // ---- which segment, which window of it
+  const uint32_t base = ep.value;
+  // flags. FA: "source rank src finished stage 1 of this block's k-th window" (in the reader's pad);
+  //        FC: "reader rank finished pulling this block's k-th window" (in the source's pad). Values base + k + 1.
+  auto fa = [&](int owner, int src) { return tab.sig[owner] + blockIdx.x * kMaxRanks + src; };
+  auto fc = [&](int owner, int reader) {
+    return (uint32_t*)((char*)tab.sig[owner] + kSigSegFcOff) + blockIdx.x * kMaxRanks + reader;
+  };
+  auto decode = [&](long long w) {
+    Win o;
     int lo_s = 0, hi_s = a.nseg - 1;
     while (lo_s < hi_s) {
       const int mid = (lo_s + hi_s + 1) >> 1;
@@ -113,51 +174,87 @@ __global__ void __launch_bounds__(kSegThreads, 2) thread_seg_kernel(const __grid
       else hi_s = mid - 1;
     }
     const SegItem& sg = a.seg[lo_s];
-    const bool reduce = sg.src_rank == kAll;
-    const bool is_src = reduce || sg.src_rank == rank;
-    const bool is_dst = sg.dst_rank == kAll || sg.dst_rank == rank;
+    o.seg = lo_s;
+    o.reduce = sg.src_rank == kAll;
+    o.src_rank = sg.src_rank;
+    o.dst_rank = sg.dst_rank;
     // virtual byte offsets y = element offset * ES + c: y % 16 == address % 16 in every thread buffer
     const long long ylo = sg.lo * ES + c, yhi = sg.hi * ES + c;
-    const long long win = ylo / CH + (w - sg.first_window);
-    const long long ya = max(ylo, win * CH), yb = min(yhi, (win + 1) * CH);
+    o.win = ylo / CH + (w - sg.first_window);
+    o.ya = max(ylo, o.win * CH);
+    o.yb = min(yhi, (o.win + 1) * CH);
+    return o;
+  };
+  // does rank d pull window `x` out of rank q's slot?
+  auto pulls = [&](const Win& x, int d, int q) {
+    const bool q_src = x.reduce || x.src_rank == q;
+    const bool d_dst = x.dst_rank == kAll || x.dst_rank == d;
+    return q_src && d_dst && d != q;
+  };
+  // waits (threads 0..world-1) until every reader of my slot for window index kk has pulled it
+  auto wait_consumed = [&](long long kk) {
+    bool ok = true;
+    if (threadIdx.x < (unsigned)world) {
+      const Win x = decode((long long)blockIdx.x + kk * gridDim.x);
+      if (pulls(x, (int)threadIdx.x, rank)) ok = wait_flag(tab, fc(rank, (int)threadIdx.x), base + (uint32_t)kk + 1u);
+    }
+    return __syncthreads_and(ok ? 1 : 0) != 0;
+  };
+
+  long long k = 0;
+  bool alive = true;
+  for (long long w = blockIdx.x; w < a.nwindows; w += gridDim.x, ++k) {
+    const Win x = decode(w);
+    const SegItem& sg = a.seg[x.seg];
+    const bool reduce = x.reduce;
+    const bool is_src = reduce || sg.src_rank == rank;
+    const bool is_dst = sg.dst_rank == kAll || sg.dst_rank == rank;
+    const long long win = x.win, ya = x.ya, yb = x.yb;
     long long yva = (ya + 15) & ~15ll, yvb = yb & ~15ll;  // 16-byte aligned interior
-    if (!a.vec_ok || yva >= yvb) yva = yvb = ya;          // all scalar: [ya, yb) = head, no body, no tail
+    if (!a.vec_ok || yva >= yvb) yva = yvb = ya;          // all scalar
     const long long nvec = (yvb - yva) / 16;
-    const long long nhead = (yva - ya) / ES, ntail = (yb - max(yvb, ya)) / ES;  // (yva == yvb == ya: tail = all)
+    const long long nhead = (yva - ya) / ES, ntail = (yb - max(yvb, ya)) / ES;
     const unsigned long long slot_off =
-        a.stg_off + ((unsigned long long)blockIdx.x * 2 + (unsigned long long)(k & 1)) * a.slot_bytes;
-    char* my_slot = tab.heap[rank] + slot_off - win * CH;  // my_slot + y = slot byte of virtual offset y
-    // Is the value final after the local step? COPY: yes. REDUCE: only with one rank.
-    const bool local_final = !reduce || world == 1;
-    // Does anybody else need this rank's contribution through the slot?
+        a.stg_off + ((unsigned long long)blockIdx.x * kSegSlots + (unsigned long long)(k % kSegSlots)) * a.slot_bytes;
+    const unsigned long long slot_rel = slot_off - (unsigned long long)(win * CH);  // heap + slot_rel + y
+    char* my_slot = tab.heap[rank] + slot_rel;
+    const bool local_final = !reduce || world == 1;  // COPY, or one rank: the local value is the result
     const bool to_slot = world > 1 && is_src && (reduce || sg.dst_rank == kAll || sg.dst_rank != rank);
     const int td0 = sg.dst_thread == kAll ? 0 : sg.dst_thread, td1 = sg.dst_thread == kAll ? nT : sg.dst_thread + 1;
+    auto buf = [&](int t, long long y) { return (char*)a.bufs[erow][t] + (y - c); };
+
+    // the slot of this window was last used kSegSlots windows ago: its readers must be done with it
+    if (world > 1 && k >= kSegSlots && !wait_consumed(k - kSegSlots)) {
+      alive = false;
+      break;
+    }
 
     // ================= stage 1: local fold / copy
     if (is_src) {
       const bool write_local = local_final && is_dst;
-      auto buf = [&](int t, long long y) { return (char*)a.bufs[erow][t] + (y - c); };
-      // vector body. REDUCE: the loads of up to 8 thread buffers are in flight together (the accessors are
-      // asm volatile, so a load placed after a dependent reduce would wait for it), thread-id order.
-      // COPY: 4 independent vectors per thread.
       if (reduce) {
+        // the loads of up to 8 thread buffers are in flight together (the accessors are asm volatile, so a
+        // load placed after a dependent reduce would wait for it), thread-id order
+        #pragma unroll 1
         for (long long v = threadIdx.x; v < nvec; v += kSegThreads) {
           const long long y = yva + v * 16;
           Vec16 acc;
+#pragma unroll 1
           for (int t0 = 0; t0 < nT; t0 += 8) {
-            Vec16 x[8];
+            Vec16 xx[8];
 #pragma unroll
             for (int j = 0; j < 8; ++j)
-              if (t0 + j < nT) x[j] = ld_stream(buf(t0 + j, y));
+              if (t0 + j < nT) xx[j] = ld_stream(buf(t0 + j, y));
 #pragma unroll
             for (int j = 0; j < 8; ++j)
-              if (t0 + j < nT) acc = (t0 + j == 0) ? x[j] : red16<T, OP>(acc, x[j]);
+              if (t0 + j < nT) acc = (t0 + j == 0) ? xx[j] : red16<T, OP>(acc, xx[j]);
           }
           if (to_slot) st_stream(my_slot + y, acc);
           if (write_local)
             for (int t = td0; t < td1; ++t) st_stream(buf(t, y), acc);
         }
       } else {
+        #pragma unroll 1
         for (long long v0 = threadIdx.x; v0 < nvec; v0 += (long long)kSegThreads * 4) {
           Vec16 acc[4];
 #pragma unroll
@@ -178,7 +275,7 @@ __global__ void __launch_bounds__(kSegThreads, 2) thread_seg_kernel(const __grid
           }
         }
       }
-      // scalar head and tail
+      #pragma unroll 1
       for (long long i = threadIdx.x; i < nhead + ntail; i += kSegThreads) {
         const long long y = i < nhead ? ya + i * ES : max(yvb, ya) + (i - nhead) * ES;
         T acc;
@@ -196,38 +293,49 @@ __global__ void __launch_bounds__(kSegThreads, 2) thread_seg_kernel(const __grid
     }
     if (world == 1) continue;
 
-    // ================= all ranks meet: the slots of this window are complete everywhere
-    if (!block_barrier_pull(tab, rank, ep)) {
-      alive = false;
-      break;
+    // ================= publish: the slot is in THIS GPU's memory, readers load it through this GPU's L2, so
+    // a device-scope fence by every writer orders it before the (relaxed) flag to each reader
+    if (to_slot) {
+      __threadfence();
+      __syncthreads();
+      if (threadIdx.x < (unsigned)world && pulls(x, (int)threadIdx.x, rank))
+        st_relaxed_sys(fa((int)threadIdx.x, rank), base + (uint32_t)k + 1u);
     }
 
     // ================= stage 2: pull from the source ranks' slots, write the local destinations
     if (is_dst && (reduce || sg.src_rank != rank)) {
-      auto buf = [&](int t, long long y) { return (char*)a.bufs[erow][t] + (y - c); };
-      auto slot_of = [&](int q, long long y) { return tab.heap[q] + slot_off - win * CH + y; };
+      bool ok = true;
+      if (threadIdx.x < (unsigned)world && pulls(x, rank, (int)threadIdx.x))
+        ok = wait_flag(tab, fa(rank, (int)threadIdx.x), base + (uint32_t)k + 1u);
+      if (!__syncthreads_and(ok ? 1 : 0)) {
+        alive = false;
+        break;
+      }
       const int q0 = reduce ? 0 : sg.src_rank, q1 = reduce ? world : sg.src_rank + 1;
       if (reduce) {
-        // all source ranks' loads of a vector are in flight together (one NVLink round trip), rank order
-        for (long long v = threadIdx.x; v < nvec; v += kSegThreads) {
-          const long long y = yva + v * 16;
-          Vec16 x[kMaxRanks];
-#pragma unroll
-          for (int q = 0; q < kMaxRanks; ++q)
-            if (q < world) x[q] = ld_coherent(slot_of(q, y));
-          Vec16 acc = x[0];
-#pragma unroll
-          for (int q = 1; q < kMaxRanks; ++q)
-            if (q < world) acc = red16<T, OP>(acc, x[q]);
-          for (int t = td0; t < td1; ++t) st_stream(buf(t, y), acc);
+        if (world == 2 || world == 4 || world == 8) {
+          switch (world) {
+            case 2: pull_reduce<T, OP, 2>(a, erow, slot_rel, td0, td1, -c, yva, nvec); break;
+            case 4: pull_reduce<T, OP, 4>(a, erow, slot_rel, td0, td1, -c, yva, nvec); break;
+            default: pull_reduce<T, OP, 8>(a, erow, slot_rel, td0, td1, -c, yva, nvec); break;
+          }
+        } else {
+          #pragma unroll 1
+          for (long long v = threadIdx.x; v < nvec; v += kSegThreads) {
+            const long long y = yva + v * 16;
+            Vec16 acc = ld_coherent(tab.heap[0] + slot_rel + y);
+            for (int q = 1; q < world; ++q) acc = red16<T, OP>(acc, ld_coherent(tab.heap[q] + slot_rel + y));
+            for (int t = td0; t < td1; ++t) st_stream(buf(t, y), acc);
+          }
         }
       } else {
+        #pragma unroll 1
         for (long long v0 = threadIdx.x; v0 < nvec; v0 += (long long)kSegThreads * 8) {
           Vec16 acc[8];
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
             const long long v = v0 + (long long)j * kSegThreads;
-            if (v < nvec) acc[j] = ld_coherent(slot_of(q0, yva + v * 16));
+            if (v < nvec) acc[j] = ld_coherent(tab.heap[q0] + slot_rel + yva + v * 16);
           }
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
@@ -237,16 +345,24 @@ __global__ void __launch_bounds__(kSegThreads, 2) thread_seg_kernel(const __grid
           }
         }
       }
+      #pragma unroll 1
       for (long long i = threadIdx.x; i < nhead + ntail; i += kSegThreads) {
         const long long y = i < nhead ? ya + i * ES : max(yvb, ya) + (i - nhead) * ES;
-        T acc = *(const volatile T*)slot_of(q0, y);
-        for (int q = q0 + 1; q < q1; ++q) acc = red1<T, OP>(acc, *(const volatile T*)slot_of(q, y));
+        T acc = *(const volatile T*)(tab.heap[q0] + slot_rel + y);
+        for (int q = q0 + 1; q < q1; ++q) acc = red1<T, OP>(acc, *(const volatile T*)(tab.heap[q] + slot_rel + y));
         for (int t = td0; t < td1; ++t) *(T*)buf(t, y) = acc;
       }
+      // every load of the window has returned (its value was stored above): tell the sources
+      __syncthreads();
+      if (threadIdx.x < (unsigned)world && pulls(x, rank, (int)threadIdx.x))
+        st_relaxed_sys(fc((int)threadIdx.x, rank), base + (uint32_t)k + 1u);
     }
   }
-  // nobody leaves (and lets a later launch reuse the slots) while a peer may still read them
-  if (world > 1 && alive && k > 0) (void)block_barrier_pull(tab, rank, ep);
+  // nobody leaves (and lets a later launch reuse the slots) while a reader may still pull from them
+  if (world > 1 && alive)
+    for (long long kk = k > kSegSlots ? k - kSegSlots : 0; kk < k; ++kk)
+      if (!wait_consumed(kk)) break;
+  ep.value = base + (uint32_t)k;  // k windows on every rank: the per-block counters stay in step
   ep.store();
 }
 
@@ -351,7 +467,7 @@ void GpuPlane::thread_segments(void* const* bufs, int T, int dtype, int op, cons
     throw Error("operator is not defined for this dtype on the fused thread collectives");
   long long cap = (long long)sms_ * seg_blocks_per_sm();
   if (emulated()) cap = std::max(1, sms_ / p);
-  cap = std::min<long long>(cap, (long long)(thread_bytes_ / (2 * CH)));
+  cap = std::min<long long>(cap, (long long)(thread_bytes_ / (kSegSlots * CH)));
   cap = std::min<long long>(cap, kMaxBlocks);
   if (opt_.max_blocks > 0) cap = std::min<long long>(cap, opt_.max_blocks);
   const int grid = (int)std::max<long long>(1, std::min(cap, nwin));

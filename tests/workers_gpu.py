@@ -139,5 +139,59 @@ def thread_gpu(comm, tid):
     torch.cuda.synchronize()
     if r == p - 1 and tid == T - 1:
         assert torch.all(x == p * T)
+    # ---- the other thread collectives on CUDA tensors: ONE fused launch each (thread_seg.cu). Position-
+    # dependent values, so a slice that lands in the wrong place or comes from the wrong thread shows.
+    n, P, me = 50021, p * T, r * T + tid
+    w = (n - 3) // P
+    fr = [[(q * T + t) * w + 3 for t in range(T)] for q in range(p)]
+    to = [[(q * T + t + 1) * w + 3 - (1 if (q + t) % 2 else 0) for t in range(T)] for q in range(p)]
+    idx = torch.arange(n, device="cuda", dtype=torch.float32)
+
+    def pat(k):
+        return idx % 7 + 1000.0 * k
+
+    def sync_call(fn, *a):
+        torch.cuda.synchronize()
+        fn(*a)
+        torch.cuda.synchronize()
+    x = torch.full((n,), -1.0, device="cuda")
+    x[fr[r][tid]:to[r][tid]] = pat(me)[fr[r][tid]:to[r][tid]]
+    sync_call(comm.allgatherArray, x, fop, fr, to)
+    for q in range(p):
+        for t in range(T):
+            assert torch.equal(x[fr[q][t]:to[q][t]], pat(q * T + t)[fr[q][t]:to[q][t]]), ("allgather", q, t)
+    if tid == 0:
+        assert "fused-segments" in comm.gpu.last(), comm.gpu.last()
+    root = (p - 1, T - 1)
+    x = torch.full((n,), -1.0, device="cuda")
+    x[fr[r][tid]:to[r][tid]] = pat(me)[fr[r][tid]:to[r][tid]]
+    sync_call(comm.gatherArray, x, fop, fr, to, root[0], root[1])
+    if (r, tid) == root:
+        for q in range(p):
+            for t in range(T):
+                assert torch.equal(x[fr[q][t]:to[q][t]], pat(q * T + t)[fr[q][t]:to[q][t]]), ("gather", q, t)
+    root = (0, T - 1)
+    x = pat(77) if (r, tid) == root else torch.full((n,), -1.0, device="cuda")
+    sync_call(comm.scatterArray, x, fop, fr, to, root[0], root[1])
+    assert torch.equal(x[fr[r][tid]:to[r][tid]], pat(77)[fr[r][tid]:to[r][tid]]), "scatter"
+    if (r, tid) != root:
+        assert torch.all(x[:fr[r][tid]] == -1.0) and torch.all(x[to[r][tid]:] == -1.0)
+    root = (p - 1, 0)
+    x = pat(5) if (r, tid) == root else torch.full((n,), -1.0, device="cuda")
+    sync_call(comm.broadcastArray, x, fop, 7, n - 9, root[0], root[1])
+    assert torch.equal(x[7:n - 9], pat(5)[7:n - 9]), "broadcast"
+    counts = [[to[q][t] - fr[q][t] for t in range(T)] for q in range(p)]
+    x = pat(me)
+    sync_call(comm.reduceScatterArray, x, fop, Operators.Float.SUM, 3, counts)
+    off = 3 + sum(sum(c) for c in counts[:r]) + sum(counts[r][:tid])
+    want = (idx % 7) * P + 1000.0 * (P * (P - 1) / 2)
+    assert torch.equal(x[off:off + counts[r][tid]], want[off:off + counts[r][tid]]), "reduce_scatter"
+    # ---- pinned host tensors: streamed through the GPU plane (H2D || fused kernel || D2H pipeline)
+    n = (3 << 20) + 5
+    h = torch.full((n,), float(me + 1)).pin_memory()
+    comm.allreduceArray(h, fop, Operators.Float.SUM, 0, n)
+    assert torch.all(h == P * (P + 1) / 2), h[:4]
+    if tid == 0:
+        assert "host-pipeline" in comm.gpu.last(), comm.gpu.last()
     comm.barrier()
     return True

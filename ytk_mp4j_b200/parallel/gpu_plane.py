@@ -90,7 +90,9 @@ def _apply_tuning_table(world):
     except Exception:
         return None
     for key, env in (("oneshot_max_bytes", "MP4J_ONE_SHOT_MAX_BYTES"), ("nvls_min_bytes", "MP4J_NVLS_MIN_BYTES"),
-                     ("nvls_min_world", "MP4J_NVLS_MIN_WORLD")):
+                     ("nvls_min_world", "MP4J_NVLS_MIN_WORLD"), ("rs_nvls_min_bytes", "MP4J_RS_NVLS_MIN_BYTES"),
+                     ("ag_nvls_min_bytes", "MP4J_AG_NVLS_MIN_BYTES"), ("rs_nvls_max_bytes", "MP4J_RS_NVLS_MAX_BYTES"),
+                     ("ag_nvls_max_bytes", "MP4J_AG_NVLS_MAX_BYTES")):
         if key in table and env not in os.environ:
             os.environ[env] = str(int(min(table[key], 1 << 62)))
     return table
@@ -384,6 +386,12 @@ class GpuPlane(_PlaneBase):
         same order). Collectives on it are zero-copy."""
         off = self._alloc_off(int(n) * _ES[operand.code])
         return self._wrap(N.lib.mp4j_gpu_rank(self._g), off, int(n), operand.code)
+
+    def free(self, t):
+        """Returns a tensor obtained from empty() to the symmetric heap (collective, like empty(): every rank
+        frees in the same order; the tensor must not be used afterwards)."""
+        base = N.lib.mp4j_gpu_ptr(self._g, N.lib.mp4j_gpu_rank(self._g), 0)
+        check(N.lib.mp4j_gpu_free(self._g, t.data_ptr() - base))
 
     # --- ProcessCommSlave dispatch targets
     def allreduce(self, t, operand, operator, f, to, algo=N.ALGO_AUTO, stream=None):
