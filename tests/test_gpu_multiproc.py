@@ -36,3 +36,14 @@ def test_single_process_comm_on_gpu():
     # p = 1: every collective short-circuits, thread collectives still run the intra-GPU kernel
     res, code, logs = run_cluster(1, workers_gpu.thread_gpu, (), threads=4, timeout=300)
     assert code == 0 and all(all(x) for x in res)
+
+
+@pytest.mark.parametrize("p,T", [(1, 0), (1, 3), (2, 0), (2, 2), (4, 2)])
+def test_check_matrix_on_cuda_tensors(p, T):
+    """CommCheckTool's matrix with device=cuda (the reference's 128 check classes, arrays of the six primitive
+    types) on 1, 2 or 4 GPUs, process level (T = 0) and thread level."""
+    if _ngpu() < p:
+        pytest.skip("needs %d GPUs" % p)
+    res, code, logs = run_cluster(p, workers_gpu.check_matrix_cuda, (), threads=T, timeout=600)
+    assert code == 0, logs[-20:]
+    assert all(all(x) if isinstance(x, list) else x for x in res)

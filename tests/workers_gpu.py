@@ -195,3 +195,21 @@ def thread_gpu(comm, tid):
         assert "host-pipeline" in comm.gpu.last(), comm.gpu.last()
     comm.barrier()
     return True
+
+
+def check_matrix_cuda(comm, tid=None):
+    """The CommCheckTool matrix with device=cuda: every array collective x every primitive type on CUDA tensors,
+    process level (tid None) or thread level."""
+    from ytk_mp4j_b200.check import checks
+    r = comm.getRank()
+    dev = r % torch.cuda.device_count()
+    torch.cuda.set_device(dev)
+    if tid is None or tid == 0:
+        comm.init_gpu(device=dev, heap_bytes=512 << 20, staging_bytes=32 << 20)
+    if tid is not None:
+        comm.threadBarrier()
+    checks.run_all(comm, tid, 20011, 50, 1, False, False, device="cuda")
+    torch.cuda.synchronize()
+    if tid is None or tid == 0:
+        comm.gpu.check()
+    return True

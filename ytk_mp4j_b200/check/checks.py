@@ -221,6 +221,36 @@ def check_map(ctx, dtype, obj, compress=False, root=0, root_thread=0):
                  lambda: c.broadcastMap({str(i): val(i % 100) for i in range(obj)} if is_root else {}, operand, *rt))
     if len(out) != obj:
         ctx.fail("broadcast %s map error" % dtype)
+    # scatterMap: the root holds one map per participant, participant g receives map g
+    # (checkdouble/ProcessScatterCheck.java:100-131; thread level: [slaveNum][threadNum], TCS:1097)
+    def part(g):
+        return {str(j): val(j % 100) for j in range(g * obj, (g + 1) * obj)}
+    if T:
+        src = [[part(q * ctx.T + th) for th in range(ctx.T)] for q in range(ctx.p)] if is_root else None
+    else:
+        src = [part(q) for q in range(ctx.p)] if is_root else None
+    out = _timed(ctx, "scatter map", dtype, lambda: c.scatterMap(src, operand, *rt))
+    if len(out) != obj or any(num(out.get(str(j), val(-1))) != _wrap(dtype, j % 100)
+                              for j in range(ctx.g * obj, (ctx.g + 1) * obj)):
+        ctx.fail("scatter %s map error" % dtype)
+    # allgatherMap: everybody ends with the list of all processes' maps
+    # (checkdouble/ProcessAllgatherCheck.java:91-119; the T maps of a process are merged first, TCS:706)
+    out = _timed(ctx, "allgather map", dtype, lambda: c.allgatherMap(part(ctx.g), operand))
+    if len(out) != ctx.p:
+        ctx.fail("allgather %s map error: %d maps" % (dtype, len(out)))
+    for q in range(ctx.p):
+        for g in range(q * ctx.T, (q + 1) * ctx.T):
+            if any(num(out[q].get(str(j), val(-1))) != _wrap(dtype, j % 100) for j in range(g * obj, (g + 1) * obj)):
+                ctx.fail("allgather %s map error" % dtype)
+    # reduceScatterMap: everybody contributes one map per participant, participant g gets map g reduced
+    # (checkdouble/ProcessReduceScatterCheck.java:93-122)
+    def ones(g):
+        return {str(j): val(1) for j in range(g * obj, (g + 1) * obj)}
+    src = [[ones(q * ctx.T + th) for th in range(ctx.T)] for q in range(ctx.p)] if T else [ones(q) for q in range(ctx.p)]
+    out = _timed(ctx, "reducescatter map", dtype, lambda: c.reduceScatterMap(src, operand, op))
+    if len(out) != obj or any(num(out.get(str(j), val(0))) != _wrap(dtype, ctx.P)
+                              for j in range(ctx.g * obj, (ctx.g + 1) * obj)):
+        ctx.fail("reducescatter %s map error" % dtype)
 
 
 def check_rpc(ctx, dtype, n, run_time, compress=False):
@@ -255,6 +285,65 @@ def check_sets(ctx, obj, root=0, root_thread=0):
     is_root = ctx.r == root and (not T or ctx.tid == root_thread)
     if is_root and len(u) != obj + ctx.P:
         ctx.fail("reduce set union error")
+    # the other rooted helpers (checkobject/ProcessReduceCheck.java:147, 185, 234)
+    inter = c.reduceSetIntersection(set(s), *rt)
+    if is_root and inter != (set(range(obj)) if ctx.P > 1 else s):
+        ctx.fail("reduce set intersection error")
+    lst = c.reduceListConcat([ctx.g], *rt)
+    if is_root and sorted(lst) != list(range(ctx.P)):
+        ctx.fail("reduce list concat error")
+    # the Map* forms: one set / list per key (checkobject/ProcessAllReduceCheck.java:139-257)
+    keys = ["k%d" % i for i in range(3)]
+    ms = {k: set(s) for k in keys}
+    out = c.allreduceMapSetUnion({k: set(v) for k, v in ms.items()})
+    if sorted(out) != keys or any(len(out[k]) != obj + ctx.P for k in keys):
+        ctx.fail("allreduce map set union error")
+    out = c.allreduceMapSetIntersection({k: set(v) for k, v in ms.items()})
+    if any(out[k] != (set(range(obj)) if ctx.P > 1 else s) for k in keys):
+        ctx.fail("allreduce map set intersection error")
+    out = c.allreduceMapListConcat({k: [ctx.g] for k in keys})
+    if any(sorted(out[k]) != list(range(ctx.P)) for k in keys):
+        ctx.fail("allreduce map list concat error")
+    out = c.reduceMapSetUnion({k: set(v) for k, v in ms.items()}, *rt)
+    if is_root and any(len(out[k]) != obj + ctx.P for k in keys):
+        ctx.fail("reduce map set union error")
+    out = c.reduceMapSetIntersection({k: set(v) for k, v in ms.items()}, *rt)
+    if is_root and any(out[k] != (set(range(obj)) if ctx.P > 1 else s) for k in keys):
+        ctx.fail("reduce map set intersection error")
+    out = c.reduceMapListConcat({k: [ctx.g] for k in keys}, *rt)
+    if is_root and any(sorted(out[k]) != list(range(ctx.P)) for k in keys):
+        ctx.fail("reduce map list concat error")
+
+
+def check_process_passthrough(ctx, dtype, n, obj, compress=False):
+    """The xxxProcess block of the thread checks (checkbyte/ThreadAllReduceCheck.java:160-240): ONE thread of every
+    process calls the process-level collective through the ThreadCommSlave while the others wait at the thread
+    barrier; the participants are then the slaveNum processes, not slaveNum x threadNum."""
+    c = ctx.comm
+    if not ctx.thread:
+        return
+    operand, op = _operand_op(dtype, compress)
+    c.threadBarrier()
+    if ctx.tid == 0:
+        arr = _make(dtype, n, 1, "cpu")
+        c.allreduceArrayProcess(arr, operand, op, 0, n)
+        if not np.all(_vals(arr, dtype) == _wrap(dtype, ctx.p)):
+            ctx.fail("allreduceArrayProcess %s error" % dtype)
+
+        def val(v):
+            return str(v) if dtype == "string" else ({"val": v} if dtype == "object" else PRIMS[dtype][2](v).item())
+
+        def num(v):
+            return int(v) if dtype == "string" else (v["val"] if dtype == "object" else int(v))
+        m = {str(i): val(1) for i in range(obj)}
+        m[str(-(ctx.r + 1))] = val(1)
+        out = c.allreduceMapProcess(m, operand, op)
+        if len(out) != obj + ctx.p or any(num(out[str(i)]) != _wrap(dtype, ctx.p) for i in range(obj)):
+            ctx.fail("allreduceMapProcess %s error" % dtype)
+        one = c.allreduceProcess(val(1), operand, op)
+        if num(one) != _wrap(dtype, ctx.p):
+            ctx.fail("allreduceProcess %s error" % dtype)
+    c.threadBarrier()
 
 
 def run_all(comm, tid, arr_size, obj_size, run_time, compress, test_rpc, device="cpu", types=None):
@@ -270,6 +359,7 @@ def run_all(comm, tid, arr_size, obj_size, run_time, compress, test_rpc, device=
                 check_collective(ctx, coll, dtype, n, compress, device)
             if device == "cpu":
                 check_map(ctx, dtype, obj_size, compress)
+                check_process_passthrough(ctx, dtype, n, obj_size, compress)
         if device == "cpu":
             check_sets(ctx, obj_size)
     if test_rpc and device == "cpu":
