@@ -423,6 +423,26 @@ int64_t mp4j_composite_long(int32_t val, int32_t loc) { return composite_long(va
 int32_t mp4j_composite_long_val(int64_t c) { return composite_long_val(c); }
 int32_t mp4j_composite_long_loc(int64_t c) { return composite_long_loc(c); }
 
+// 64-bit keys for the GPU map kernels from NUL-separated UTF-8 strings: low 32 bits = String.hashCode (so that
+// partition "java32" places a key on the rank the reference would, PCS:2063-2071), high 32 bits = FNV-1a of the
+// bytes (an independent hash: two strings collide only if both 32-bit hashes agree). INT64_MIN, the kernels'
+// free-slot marker, is never produced.
+int mp4j_map_keys64(const char* blob, size_t blob_len, int64_t n, int64_t* out) {
+  size_t pos = 0;
+  for (int64_t i = 0; i < n; ++i) {
+    size_t end = pos;
+    while (end < blob_len && blob[end] != 0) ++end;
+    uint32_t f = 2166136261u;
+    for (size_t j = pos; j < end; ++j) f = (f ^ (unsigned char)blob[j]) * 16777619u;
+    const uint32_t lo = (uint32_t)mp4j_java_string_hash(blob + pos, end - pos);
+    uint64_t k = ((uint64_t)f << 32) | lo;
+    if (k == 0x8000000000000000ull) k ^= 1ull << 32;
+    out[i] = (int64_t)k;
+    pos = end + 1;
+  }
+  return 0;
+}
+
 int32_t mp4j_java_string_hash(const char* s, size_t n) {
   // decode UTF-8 into UTF-16 code units on the fly; h = 31*h + unit (32-bit wrap)
   uint32_t h = 0;

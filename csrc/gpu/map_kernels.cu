@@ -43,6 +43,12 @@ __device__ __forceinline__ int owner_of(long long key, int p, int partition) {
     int m = h % p;                                   // C remainder has Java's sign rule
     return m < 0 ? m + p : m;
   }
+  if (partition == MP4J_MAP_PART_TAGGED) {
+    // the caller chose the destination: it sits in the top 4 bits of the key (reduceScatterMap / scatter-like
+    // uses where the reference addresses rank i with list element i, PCS:1299-1327)
+    const int d = (int)((unsigned long long)key >> 60);
+    return d < p ? d : p - 1;
+  }
   return (int)(splitmix64((unsigned long long)key) % (unsigned)p);
 }
 

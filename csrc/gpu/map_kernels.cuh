@@ -6,6 +6,7 @@
 //   MP4J_MAP_PART_MIX    owner = splitmix64(key) % p                       (integer ids)
 //   MP4J_MAP_PART_JAVA32 owner = ((int32)key) mod p, negatives wrapped     (low 32 bits carry
 //                        java.lang.String.hashCode, so placement matches the reference)
+//   MP4J_MAP_PART_TAGGED owner = top 4 bits of the key (the caller addresses a rank explicitly)
 #pragma once
 #include "peer.cuh"
 
@@ -13,7 +14,7 @@ namespace mp4j {
 
 constexpr long long kMapEmpty = (long long)0x8000000000000000ull;  // reserved key: empty slot
 
-enum MapPartition { MP4J_MAP_PART_MIX = 0, MP4J_MAP_PART_JAVA32 = 1 };
+enum MapPartition { MP4J_MAP_PART_MIX = 0, MP4J_MAP_PART_JAVA32 = 1, MP4J_MAP_PART_TAGGED = 2 };
 
 struct MapExchangeArgs {
   PeerTable tab;

@@ -122,6 +122,9 @@ int32_t mp4j_composite_long_val(int64_t c);
 int32_t mp4j_composite_long_loc(int64_t c);
 /* java.lang.String.hashCode of a UTF-16 code-unit sequence given as UTF-8 (PCS:2066-2070). */
 int32_t mp4j_java_string_hash(const char* utf8, size_t n);
+/* n NUL-separated UTF-8 keys -> 64-bit keys for the GPU map collectives: low word String.hashCode (placement as in
+ * the reference, PCS:2063-2071), high word FNV-1a; never INT64_MIN (the kernels' free-slot marker). */
+int mp4j_map_keys64(const char* blob, size_t blob_len, int64_t n, int64_t* out);
 
 #include "mp4j_gpu.h"
 

@@ -19,7 +19,7 @@ def _ngpu():
 def test_process_collectives_on_gpus(p):
     if _ngpu() < p:
         pytest.skip("needs %d GPUs" % p)
-    res, code, logs = run_cluster(p, workers_gpu.process_gpu, (), timeout=300)
+    res, code, logs = run_cluster(p, workers_gpu.process_gpu, (), timeout=120)
     assert code == 0 and all(r["ok"] for r in res), res
 
 
@@ -28,13 +28,13 @@ def test_process_collectives_on_gpus(p):
 def test_thread_allreduce_on_gpus(p, T):
     if _ngpu() < p:
         pytest.skip("needs %d GPUs" % p)
-    res, code, logs = run_cluster(p, workers_gpu.thread_gpu, (), threads=T, timeout=300)
+    res, code, logs = run_cluster(p, workers_gpu.thread_gpu, (), threads=T, timeout=120)
     assert code == 0 and all(all(x) for x in res)
 
 
 def test_single_process_comm_on_gpu():
     # p = 1: every collective short-circuits, thread collectives still run the intra-GPU kernel
-    res, code, logs = run_cluster(1, workers_gpu.thread_gpu, (), threads=4, timeout=300)
+    res, code, logs = run_cluster(1, workers_gpu.thread_gpu, (), threads=4, timeout=120)
     assert code == 0 and all(all(x) for x in res)
 
 

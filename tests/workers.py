@@ -412,3 +412,26 @@ def native_maps(comm):
     except Mp4jException:
         pass
     return True
+
+
+def map_bridge_worker(comm, mask):
+    """String-key bridge of the GPU map path, host part only (no GPU needed): identical dictionaries on every
+    rank, round trip, and the collision policy (a narrowed hash makes two strings share a key)."""
+    from ytk_mp4j_b200.comm import map_bridge
+    map_bridge._TEST_MASK = mask
+    r, p = comm.getRank(), comm.getSlaveNum()
+    br = map_bridge.MapKeyBridge(comm)
+    shared = ["f%d" % i for i in range(200)]
+    mine = ["rank%d_%d" % (r, i) for i in range(50)] + ["ключ-%d" % r, "鍵%d" % r]
+    ks = br.encode(shared + mine)
+    everything = shared + [s for q in range(p) for s in ["rank%d_%d" % (q, i) for i in range(50)] + ["ключ-%d" % q, "鍵%d" % q]]
+    out = {"broken": br.broken, "n": len(br._rev)}
+    if not br.broken:
+        allk = map_bridge.keys64(everything)
+        out["roundtrip"] = br.decode(allk.tolist()) == everything          # other ranks' strings are known here
+        out["mine"] = br.decode(ks.tolist()) == shared + mine
+        ks2 = br.encode(shared + mine)                                      # nothing new: no string traffic
+        out["stable"] = bool((ks2 == ks).all()) and len(br._rev) == out["n"]
+        tagged = map_bridge.MapKeyBridge.tag(ks, 5)
+        out["tag"] = bool(((tagged.astype("uint64") >> 60) == 5).all()) and br.decode(tagged.tolist(), True) == shared + mine
+    return out

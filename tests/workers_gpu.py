@@ -93,6 +93,22 @@ def process_gpu(comm):
     k, v = comm.gpu.allgather_map(torch.full((3,), r, dtype=torch.int64, device="cuda"),
                                   torch.full((3,), float(r), device="cuda"))
     assert k.tolist() == [q for q in range(p) for _ in range(3)]
+    # ---- Map<String, number> through the PUBLIC API with the GPU plane up: String keys are bridged to 64-bit
+    # keys (comm/map_bridge.py), values reduce on the GPU, result comes back as a dict (PCS:2053, 1299, 666)
+    objn = 3000
+    for rep in range(2):  # second call: every string is already known, no string traffic
+        m = {"f%d" % i: 1.0 for i in range(objn)}
+        m["only-%d" % r] = float(r + 1)
+        out = comm.allreduceMap(m, dop, Operators.Double.SUM)
+        assert "allreduce_map" in comm.gpu.last(), comm.gpu.last()
+        assert len(out) == objn + p and all(out["f%d" % i] == p for i in range(0, objn, 37))
+        assert all(out["only-%d" % q] == q + 1 for q in range(p))
+    lists = [{"k%d" % j: 1 for j in range(q * 100, (q + 1) * 100)} for q in range(p)]
+    out = comm.reduceScatterMap(lists, Operands.LONG_OPERAND(), Operators.Long.SUM)
+    assert "reduce_scatter_map" in comm.gpu.last(), comm.gpu.last()
+    assert sorted(out) == sorted("k%d" % j for j in range(r * 100, (r + 1) * 100)) and all(v == p for v in out.values())
+    outs = comm.allgatherMap({"g%d" % j: float(j) for j in range(r * 10, (r + 1) * 10)}, fop)
+    assert len(outs) == p and all(outs[q] == {"g%d" % j: float(j) for j in range(q * 10, (q + 1) * 10)} for q in range(p))
     torch.cuda.synchronize()
     comm.gpu.check()
     comm.barrier()
@@ -186,6 +202,13 @@ def thread_gpu(comm, tid):
     off = 3 + sum(sum(c) for c in counts[:r]) + sum(counts[r][:tid])
     want = (idx % 7) * P + 1000.0 * (P * (P - 1) / 2)
     assert torch.equal(x[off:off + counts[r][tid]], want[off:off + counts[r][tid]]), "reduce_scatter"
+    # ---- thread-level allreduceMap: the T thread maps of every process go to the GPU unmerged
+    m = {"w%d" % i: 1 for i in range(500)}
+    m["t-%d" % me] = me + 1
+    out = comm.allreduceMap(m, Operands.LONG_OPERAND(), Operators.Long.SUM)
+    assert len(out) == 500 + P and out["w7"] == P and all(out["t-%d" % g] == g + 1 for g in range(P))
+    if tid == 0 and p > 1:
+        assert "allreduce_map" in comm.gpu.last(), comm.gpu.last()
     # ---- pinned host tensors: streamed through the GPU plane (H2D || fused kernel || D2H pipeline)
     n = (3 << 20) + 5
     h = torch.full((n,), float(me + 1)).pin_memory()

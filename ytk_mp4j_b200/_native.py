@@ -104,6 +104,7 @@ _proto("mp4j_composite_long", C.c_int64, C.c_int32, C.c_int32)
 _proto("mp4j_composite_long_val", C.c_int32, C.c_int64)
 _proto("mp4j_composite_long_loc", C.c_int32, C.c_int64)
 _proto("mp4j_java_string_hash", C.c_int32, C.c_char_p, C.c_size_t)
+_proto("mp4j_map_keys64", C.c_int, C.c_char_p, C.c_size_t, C.c_int64, c_i64p)
 
 
 def last_error():

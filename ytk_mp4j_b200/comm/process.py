@@ -380,6 +380,10 @@ class ProcessCommSlave:
         """Returns the list of p maps indexed by origin rank (PCS:666, 714-715)."""
         if self._n == 1:
             return [mapData]
+        if self._gpu_map_ok(operand, None, need_op=False):
+            out = self._gpu_allgather_map([mapData], operand)
+            if out is not None:
+                return out
         return self._ring_allgather(mapData, operand)
 
     # ------------------------------------------------------------------ broadcast
@@ -495,6 +499,10 @@ class ProcessCommSlave:
             return mapDataList[0]
         if len(mapDataList) != self._n:
             raise Mp4jException("reduceScatterMap needs one map per slave")
+        if self._gpu_map_ok(operand, operator):
+            out = self._gpu_reduce_scatter_map(list(enumerate(mapDataList)), operand, operator)
+            if out is not None:
+                return out
         return self._ring_reduce_scatter(list(mapDataList), self._merge_map(operator), operand)
 
     # ------------------------------------------------------------------ reduce
@@ -567,6 +575,10 @@ class ProcessCommSlave:
         merged (PCS:2053-2081). For tensor-backed sparse maps use gpu.allreduce_map."""
         if self._n == 1:
             return mapData
+        if self._gpu_map_ok(operand, operator):
+            out = self._gpu_allreduce_map([mapData], operand, operator)
+            if out is not None:
+                return out
         if self._native_map_ok(operand, operator):
             return self._native_map_reduce(0, 0, mapData, operand, operator)
         mine = self.reduceScatterMap(self._partition_map(mapData), operand, operator)
@@ -657,6 +669,84 @@ class ProcessCommSlave:
         return self.allreduceMapListConcat({"key": listData}, elementSerializer, elementType)["key"]
 
     # ------------------------------------------------------------------ native map path
+    # ------------------------------------------------------------------ Map<String, number> on the GPU
+    def _map_bridge(self):
+        if getattr(self, "_bridge", None) is None:
+            from .map_bridge import MapKeyBridge
+            self._bridge = MapKeyBridge(self)
+        return self._bridge
+
+    def _gpu_map_ok(self, operand, operator, need_op=True):
+        """Maps with float/double/int/long values and SUM/MAX/MIN go through the GPU map kernels once the GPU
+        plane is up (String keys -> 64-bit keys: comm/map_bridge.py). Depends only on state that is the same on
+        every rank; MP4J_GPU_MAPS=0 keeps maps on the host."""
+        if self._gpu is None or self._n == 1 or os.environ.get("MP4J_GPU_MAPS", "1") == "0":
+            return False
+        if not operand.is_primitive or operand.code not in (N.F64, N.F32, N.I64, N.I32):
+            return False
+        if need_op and (operator is None or not operator.is_native or operator.code not in (N.SUM, N.MAX, N.MIN)):
+            return False
+        return not self._map_bridge().broken
+
+    def _gpu_map_tensors(self, maps, operand, tags=None):
+        """(keys, values) CUDA tensors of the concatenation of `maps` (a list of dicts); None if the bridge broke.
+        tags: destination rank per map (partition "tagged")."""
+        import torch
+        br = self._map_bridge()
+        strings = [k for m in maps for k in m.keys()]
+        ks = br.encode(strings)
+        if br.broken:
+            return None
+        if tags is not None:
+            off = 0
+            for m, d in zip(maps, tags):
+                ks[off:off + len(m)] = br.tag(ks[off:off + len(m)], d)
+                off += len(m)
+        vals = np.fromiter((v for m in maps for v in m.values()), dtype=operand.np_dtype, count=len(strings))
+        dev = "cuda:%d" % self._gpu.device
+        return torch.from_numpy(ks).to(dev), torch.from_numpy(vals).to(dev)
+
+    def _gpu_map_result(self, k, v, operand, tagged=False):
+        import torch
+        torch.cuda.current_stream().synchronize()
+        names = self._map_bridge().decode(k.cpu().numpy().tolist(), tagged)
+        return dict(zip(names, v.cpu().numpy().tolist()))
+
+    def _gpu_allreduce_map(self, maps, operand, operator):
+        kv = self._gpu_map_tensors(maps, operand)
+        if kv is None:
+            return None
+        k, v = self._gpu.allreduce_map(kv[0], kv[1], operator, partition="java32")
+        return self._gpu_map_result(k, v, operand)
+
+    def _gpu_reduce_scatter_map(self, maps_by_dest, operand, operator):
+        """maps_by_dest: list of (dest rank, dict); returns this rank's reduced dict."""
+        kv = self._gpu_map_tensors([m for _, m in maps_by_dest], operand, tags=[d for d, _ in maps_by_dest])
+        if kv is None:
+            return None
+        k, v = self._gpu.reduce_scatter_map(kv[0], kv[1], operator, partition="tagged")
+        return self._gpu_map_result(k, v, operand, tagged=True)
+
+    def _gpu_allgather_map(self, maps, operand):
+        """returns the list of every rank's (merged) dict, in rank order."""
+        kv = self._gpu_map_tensors(maps, operand)
+        if kv is None:
+            return None
+        lop = Operands.LONG_OPERAND()
+        counts = np.zeros(self._n, dtype=np.int64)
+        counts[self._rank] = kv[0].numel()
+        self.allgatherArray(counts, lop, list(range(self._n)), list(range(1, self._n + 1)))
+        k, v = self._gpu.allgather_map(kv[0], kv[1])
+        import torch
+        torch.cuda.current_stream().synchronize()
+        names = self._map_bridge().decode(k.cpu().numpy().tolist())
+        vals = v.cpu().numpy().tolist()
+        out, off = [], 0
+        for c in counts.tolist():
+            out.append(dict(zip(names[off:off + c], vals[off:off + c])))
+            off += c
+        return out
+
     @staticmethod
     def _native_map_ok(operand, operator):
         """Maps with primitive values and a predefined operator take the C++ map collective

@@ -530,6 +530,14 @@ class ThreadCommSlave:
         """Result map is SHARED by the threads of a process - clone before mutating (README:254)."""
         if self._T == 1:
             return self.processCommSlave.allreduceMap(mapData, operand, operator)
+        pcs = self.processCommSlave
+        if pcs._gpu_map_ok(operand, operator):
+            # GPU path: the T thread maps go to the device as they are - the merge kernel folds equal keys of
+            # different threads exactly like equal keys of different ranks (TCS:2179-2224 without the host merge)
+            def run_gpu(maps):
+                out = pcs._gpu_allreduce_map(maps, operand, operator)
+                return out if out is not None else pcs.allreduceMap(self._merge_maps(maps, operator), operand, operator)
+            return self._delegate(mapData, run_gpu, 0)
         return self._delegate(mapData, lambda maps: self.processCommSlave.allreduceMap(
             self._merge_maps(maps, operator), operand, operator), 0)
 

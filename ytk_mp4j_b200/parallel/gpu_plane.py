@@ -65,7 +65,7 @@ _P("mp4j_gpu_stats", C.c_int, C.c_void_p, C.c_char_p, C.c_size_t, C.c_int)
 _P("mp4j_rtc_compile", C.c_int, C.c_int, C.c_char_p, C.c_int, C.POINTER(C.c_longlong))
 
 MAP_MODES = {"allreduce": 0, "reduce_scatter": 1, "allgather": 2}
-MAP_PARTITIONS = {"mix": 0, "java32": 1}
+MAP_PARTITIONS = {"mix": 0, "java32": 1, "tagged": 2}
 
 TORCH_DTYPES = {
     N.F64: torch.float64, N.F32: torch.float32, N.I64: torch.int64, N.I32: torch.int32,
