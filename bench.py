@@ -269,12 +269,21 @@ def main():
                "api": "ThreadCommSlave.allreduceArray on pinned host tensors (T python threads); result in "
                       + ("all T host arrays" if rt is None else "thread 0's host array (resultThread=0)")}
 
-    # ---- N >= 2: the rest of the product on the real multi-GPU path, under the driver's eyes
-    correctness = sweep = None
-    if extras:
+    # ---- the other metrics BASELINE.json names (LR step/s, sparse map keys/s, GBDT), at every N
+    consumers = None
+    if not args.no_extras:
         sys.path.insert(0, os.path.join(ROOT, "bench"))
         import driver_extras
         del bufs
+        bufs = None
+        torch.cuda.empty_cache()
+        try:
+            consumers = driver_extras.consumers(pcs, plane, rank, world)
+        except Exception as e:  # noqa: BLE001 - the headline number must still be printed
+            consumers = {"error": repr(e)[:300]}
+    # ---- N >= 2: the rest of the product on the real multi-GPU path, under the driver's eyes
+    correctness = sweep = None
+    if extras:
         torch.cuda.empty_cache()
         correctness = driver_extras.correctness_matrix(pcs, plane, rank, world)
         sweep = driver_extras.dense_sweep(pcs, plane, rank, world, max_bytes=args.sweep_max_bytes)
@@ -320,6 +329,7 @@ def main():
             "clocks": clocks,
             "gpu_launches": K,
             "e2e": e2e,
+            "consumers": consumers,
             "correctness_matrix": correctness,
             "dense_sweep": sweep,
         }

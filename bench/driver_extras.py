@@ -343,3 +343,81 @@ def dense_sweep(pcs, plane, rank, world, max_bytes=1 << 30, with_nccl=True, budg
         torch.cuda.empty_cache()
     plane.check()
     return out
+
+
+def consumers(pcs, plane, rank, world, steps=8):
+    """BASELINE.json's remaining metrics ("sparse map keys/s; LR step/s") and configs 4-5, through the models
+    that ship with the package (ytk_mp4j_b200/models): device-timed whole steps, max over ranks.
+      dense LR   : 65536 rows x 8192 features x 128 classes per GPU, bf16; step = forward GEMM, softmax residual,
+                   fused tcgen05 X^T R + reduce-scatter (K12), sharded update, allgather of the weights
+      sparse LR  : 10M hashed features, 262144 rows x 8 non-zeros per GPU and step; the gradient travels as a map
+                   through map_reduce_local + allreduce_map (K10/K11)
+      GBDT       : 1M rows (split over the GPUs) x 2048 features x 256 bins: histogram build fused with the
+                   reduce-scatter (K13) + split scan + MAX_LOC allreduce
+    """
+    from ytk_mp4j_b200.models.gbdt import HistGBDT
+    from ytk_mp4j_b200.models.lr import DenseLR, SparseLR
+    dop, DMAX = Operands.DOUBLE_OPERAND(), Operators.Double.MAX
+    out = {}
+
+    def timed(fn, k=steps, warm=2):
+        for _ in range(warm):
+            fn()
+        torch.cuda.synchronize()
+        pcs.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(k):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return pcs.allreduce(e0.elapsed_time(e1) / k, dop, DMAX)  # ms per step
+
+    g = torch.Generator(device="cuda").manual_seed(rank)
+    # ---- dense LR
+    F, Cn, rows = 8192, 128, 65536
+    model = DenseLR(pcs, F, Cn, lr=0.1)
+    X = torch.randn(rows, F, device="cuda", generator=g)
+    y = torch.randint(0, Cn, (rows,), device="cuda", generator=g)
+    model.set_data(X, y)
+    del X
+    ms = timed(model.step)
+    out["dense_lr"] = {"steps_per_s": round(1e3 / ms, 2), "ms_per_step": round(ms, 3),
+                       "config": "%d rows x %d features x %d classes per GPU, bf16, N=%d" % (rows, F, Cn, world)}
+    del model
+    torch.cuda.empty_cache()
+    # ---- sparse LR + the map collective alone
+    Fs, n, nnz = 10_000_000, 262144, 8
+    sm = SparseLR(pcs, Fs, lr=0.1)
+    cols = torch.randint(0, Fs, (n * nnz,), device="cuda", generator=g)
+    rws = torch.arange(n, device="cuda").repeat_interleave(nnz)
+    vals = torch.ones(n * nnz, device="cuda")
+    ys = (torch.rand(n, device="cuda", generator=g) > 0.5).float()
+    ms = timed(lambda: sm.step(rws, cols, vals, ys), k=max(3, steps // 2))
+    out["sparse_lr"] = {"steps_per_s": round(1e3 / ms, 2), "ms_per_step": round(ms, 3),
+                        "config": "10M hashed features, %d rows x %d nnz per GPU and step, N=%d" % (n, nnz, world)}
+    keys = cols[: 2_000_000].contiguous()
+    kv = torch.ones(2_000_000, device="cuda")
+    if world > 1:
+        ms = timed(lambda: plane.allreduce_map(keys, kv, Operators.Float.SUM), k=max(3, steps // 2))
+        out["allreduce_map"] = {"Gkeys_per_s": round(world * 2_000_000 / (ms * 1e-3) / 1e9, 2), "ms": round(ms, 3),
+                                "config": "2M (int64 key, fp32) pairs per GPU drawn from 10M ids, N=%d" % world}
+    else:
+        ms = timed(lambda: plane.map_reduce_local(keys, kv, N.SUM), k=max(3, steps // 2))
+        out["map_reduce_local"] = {"Gkeys_per_s": round(2_000_000 / (ms * 1e-3) / 1e9, 2), "ms": round(ms, 3),
+                                   "config": "2M (int64 key, fp32) pairs drawn from 10M ids, one GPU"}
+    del sm, cols, rws, vals
+    torch.cuda.empty_cache()
+    # ---- GBDT split search
+    Fg, rows_g = 2048, 1_000_000 // world
+    gb = HistGBDT(pcs, Fg)
+    gb.set_data(torch.randint(0, 256, (Fg, rows_g), device="cuda", generator=g, dtype=torch.uint8))
+    gr = torch.randn(rows_g, device="cuda", generator=g)
+    he = torch.rand(rows_g, device="cuda", generator=g) + 0.1
+    ms = timed(lambda: gb.best_split(gr, he), k=max(3, steps // 2))
+    out["gbdt_best_split"] = {"ms": round(ms, 3), "splits_per_s": round(1e3 / ms, 1),
+                              "config": "1M rows / %d GPUs x 2048 features x 256 bins" % world}
+    del gb
+    torch.cuda.empty_cache()
+    plane.check()
+    return out

@@ -122,6 +122,13 @@ int mp4j_gpu_map_collective(mp4j_gpu* g, int mode, const int64_t* const* keys, c
 int mp4j_gpu_lr_xtr_reduce_scatter(mp4j_gpu* g, const void* const* xt, const void* const* rt, int F, int C, int64_t K,
                                    float** shard_out, int* feats_per_rank, void* stream);
 
+/* Softmax residual of multinomial LR, fused and transposed - the producer of K12's second operand (consumer:
+ * the reference's LR, README.md:268-278). logits: bf16 [rows, C]; y: int64 labels (< 0 = padding row);
+ * rt: bf16 [C, rows] receives softmax(logits) - onehot(y) (0 for padding rows); *loss (device fp32) is
+ * INCREMENTED by the summed negative log-likelihood of the valid rows. Needs no plane. */
+int mp4j_gpu_lr_softmax_residual(const void* logits_bf16, const int64_t* y, int64_t rows, int C, void* rt_bf16,
+                                 float* loss, void* stream);
+
 /* GBDT histogram build fused with its reduce-scatter (consumer of reduceScatterArray in ytk-learn's
  * GBDT, reference README.md:278). bins: feature-major uint8 [F][pitch] (256 bins per feature, pitch
  * >= rows and a multiple of 16, base 16-byte aligned), grad/hess: fp32 [rows]. Every CTA adds its

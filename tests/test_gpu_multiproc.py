@@ -47,3 +47,17 @@ def test_check_matrix_on_cuda_tensors(p, T):
     res, code, logs = run_cluster(p, workers_gpu.check_matrix_cuda, (), threads=T, timeout=600)
     assert code == 0, logs[-20:]
     assert all(all(x) if isinstance(x, list) else x for x in res)
+
+
+@pytest.mark.parametrize("p", [1, 2, 4])
+def test_lr_and_gbdt_consumers_match_single_process_reference(p):
+    """models/lr.py and models/gbdt.py end to end (the reference's named consumers, README.md:268-278): the loss
+    curve of the data-parallel runs equals a single-process fp32 run on the concatenated data."""
+    if _ngpu() < p:
+        pytest.skip("needs %d GPUs" % p)
+    res, code, logs = run_cluster(p, workers_gpu.models_worker, (), timeout=180)
+    assert code == 0
+    for out in res:
+        assert out["dense_ok"], (out["dense_ours"], out["dense_ref"])
+        assert out["sparse_ok"], (out["sparse_ours"], out["sparse_ref"])
+        assert out["gbdt_ok"], out["gbdt"]

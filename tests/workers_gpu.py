@@ -236,3 +236,98 @@ def check_matrix_cuda(comm, tid=None):
     if tid is None or tid == 0:
         comm.gpu.check()
     return True
+
+
+def models_worker(comm):
+    """The two ML consumers end to end on the GPU plane (reference README.md:268-278): data-parallel logistic
+    regression (dense: fused X^T R GEMM + reduce-scatter; sparse: gradient as a map through allreduce_map) against
+    a single-process fp32 PyTorch run on the concatenated data, and the GBDT split search against a CPU scan."""
+    from ytk_mp4j_b200.models.gbdt import HistGBDT
+    from ytk_mp4j_b200.models.lr import DenseLR, SparseLR
+    p, r = comm.getSlaveNum(), comm.getRank()
+    dev = r % torch.cuda.device_count()
+    torch.cuda.set_device(dev)
+    comm.init_gpu(device=dev, heap_bytes=512 << 20, staging_bytes=32 << 20)
+    out = {}
+    # ---- dense LR: every rank can rebuild every rank's shard from the seeds
+    F, Cn, rows, steps, lr = 256, 16, 2048, 12, 0.5
+    g = torch.Generator().manual_seed(7)
+    Wtrue = torch.randn(F, Cn, generator=g)
+    Xs = [torch.randn(rows, F, generator=g) for _ in range(p)]
+    ys = [(X @ Wtrue + 0.1 * torch.randn(rows, Cn, generator=g)).argmax(1) for X in Xs]
+    model = DenseLR(comm, F, Cn, lr=lr)
+    model.set_data(Xs[r].cuda(), ys[r].cuda())
+    ours = []
+    for _ in range(steps):
+        ours.append(model.loss(model.step()))
+    # reference: full-batch gradient descent in fp32 on all the data (same bf16-rounded inputs)
+    Xall = torch.cat(Xs).to(torch.bfloat16).float()
+    yall = torch.cat(ys)
+    W = torch.zeros(F, Cn)
+    ref = []
+    for _ in range(steps):
+        logp = torch.log_softmax(Xall @ W, 1)
+        ref.append(float(-logp.gather(1, yall[:, None]).sum() / yall.numel()))
+        R = logp.exp()
+        R[torch.arange(yall.numel()), yall] -= 1.0
+        W -= lr / yall.numel() * (Xall.t() @ R)
+    out["dense_ours"], out["dense_ref"] = ours, ref
+    out["dense_ok"] = all(abs(a - b) <= 0.02 * abs(b) + 1e-3 for a, b in zip(ours, ref)) and ours[-1] < 0.8 * ours[0]
+    # ---- sparse LR: binary, hashed features, gradient through allreduce_map
+    Fs, n, nnz_row, steps = 5000, 3000, 8, 8
+    data = []
+    for q in range(p):
+        gq = torch.Generator().manual_seed(100 + q)
+        cols = torch.randint(0, Fs, (n * nnz_row,), generator=gq)
+        rws = torch.arange(n).repeat_interleave(nnz_row)
+        vals = torch.ones(n * nnz_row)
+        wtrue = torch.randn(Fs, generator=torch.Generator().manual_seed(5))
+        y = (torch.zeros(n).index_add_(0, rws, vals * wtrue[cols]) > 0).float()
+        data.append((rws, cols, vals, y))
+    sm = SparseLR(comm, Fs, lr=0.5)
+    rws, cols, vals, y = (t.cuda() for t in data[r])
+    s_ours = []
+    for _ in range(steps):
+        ls = sm.step(rws, cols, vals, y)
+        s_ours.append(comm.allreduce(float(ls), Operands.DOUBLE_OPERAND(), Operators.Double.SUM) / (n * p))
+    w = torch.zeros(Fs)
+    s_ref = []
+    for _ in range(steps):
+        gsum, lsum = torch.zeros(Fs), 0.0
+        for rws_, cols_, vals_, y_ in data:
+            z = torch.zeros(n).index_add_(0, rws_, vals_ * w[cols_])
+            lsum += float(torch.nn.functional.binary_cross_entropy_with_logits(z, y_, reduction="sum"))
+            gsum.index_add_(0, cols_, vals_ * (torch.sigmoid(z) - y_)[rws_])
+        s_ref.append(lsum / (n * p))
+        w -= 0.5 / (n * p) * gsum
+    out["sparse_ours"], out["sparse_ref"] = s_ours, s_ref
+    out["sparse_ok"] = all(abs(a - b) <= 1e-4 * abs(b) + 1e-5 for a, b in zip(s_ours, s_ref)) and s_ours[-1] < s_ours[0]
+    # ---- GBDT: best split of one node over all ranks' rows, real-valued gradients
+    Fg, rws_n = 24, 5000
+    bins_all, g_all, h_all = [], [], []
+    for q in range(p):
+        gq = torch.Generator().manual_seed(200 + q)
+        bins_all.append(torch.randint(0, 256, (Fg, rws_n), generator=gq, dtype=torch.uint8))
+        g_all.append(torch.randn(rws_n, generator=gq))
+        h_all.append(torch.rand(rws_n, generator=gq) + 0.1)
+    gb = HistGBDT(comm, Fg)
+    gb.set_data(bins_all[r].cuda())
+    gain, feat, b = gb.best_split(g_all[r].cuda(), h_all[r].cuda())
+    hist = torch.zeros(Fg, 256, 2, dtype=torch.float64)
+    for q in range(p):
+        idx = bins_all[q].long()
+        for f in range(Fg):
+            hist[f, :, 0].index_add_(0, idx[f], g_all[q].double())
+            hist[f, :, 1].index_add_(0, idx[f], h_all[q].double())
+    gl, hl = hist[..., 0].cumsum(1), hist[..., 1].cumsum(1)
+    gt, ht = gl[:, -1:], hl[:, -1:]
+    gn = gl * gl / (hl + 1.0) + (gt - gl) ** 2 / (ht - hl + 1.0) - gt * gt / (ht + 1.0)
+    gn[:, -1] = -1.0
+    best = float(gn.max())
+    out["gbdt"] = (gain, feat, b, best, float(gn[feat, b]))
+    # the fused histogram is fixed-point: the chosen split must be the best one up to quantisation
+    out["gbdt_ok"] = abs(gain - best) <= 2e-3 * abs(best) + 1e-3 and float(gn[feat, b]) >= best - 2e-3 * abs(best) - 1e-3
+    torch.cuda.synchronize()
+    comm.gpu.check()
+    comm.barrier()
+    return out

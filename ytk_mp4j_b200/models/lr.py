@@ -3,7 +3,7 @@ reference names first (ytk-learn LR / L-BFGS: instance counts, gradients, R/READ
 
 Per step, on every rank (one GPU each):
   logits = X @ W                       bf16 GEMM (cuBLAS: a plain library GEMM)
-  R      = softmax(logits) - onehot(y) fp32, written transposed as bf16 [C, rows]
+  R      = softmax(logits) - onehot(y) one fused kernel (lr_residual.cu), written transposed as bf16 [C, rows]
   G_r    = reduce-scatter over ranks of X^T R    ONE fused kernel: tcgen05 GEMM whose output tiles
                                                   are added into the owner rank's shard (K12)
   W_r   -= lr * G_r / N                 sharded update: rank r owns rows [r*fpr, (r+1)*fpr) of W
@@ -45,18 +45,16 @@ class DenseLR:
         self.valid = (y >= 0)
         self.n_local = int(self.valid.sum())
         self.n_total = self.comm.allreduce(self.n_local, Operands.LONG_OPERAND(), Operators.Long.SUM)
+        self._rt = torch.empty(self.C, self.X.shape[0], dtype=torch.bfloat16, device=self.X.device)
+        self._loss = torch.zeros(1, dtype=torch.float32, device=self.X.device)
 
     def step(self):
+        from ..parallel.gpu_plane import lr_softmax_residual
         W = self.W[: self.F]
-        logits = (self.X @ W.to(self.dtype)).float()
-        logp = torch.log_softmax(logits, dim=1)
-        probs = logp.exp()
-        onehot = torch.zeros_like(probs)
-        idx = self.y.clamp(min=0)
-        onehot.scatter_(1, idx[:, None], 1.0)
-        R = (probs - onehot) * self.valid[:, None]
-        loss_local = -(logp.gather(1, idx[:, None])[:, 0] * self.valid).sum()
-        Rt = R.t().contiguous().to(self.dtype)
+        logits = self.X @ W.to(self.dtype)                               # plain library GEMM (cuBLAS), bf16
+        # softmax, one-hot, mask, loss, transpose and cast in ONE kernel, written K-major for the next one
+        self._loss.zero_()
+        Rt, loss_local = lr_softmax_residual(logits, self.y, self._rt, self._loss)
         shard, fpr = self.plane.lr_xtr_reduce_scatter(self.Xt, Rt)     # fused GEMM + reduce-scatter
         lo = self.r * fpr
         self.W[lo:lo + fpr].add_(shard, alpha=-self.lr / self.n_total)  # sharded update

@@ -57,6 +57,7 @@ _P("mp4j_gpu_lr_xtr_reduce_scatter", C.c_int, C.c_void_p, N.c_vpp, N.c_vpp, C.c_
 _P("mp4j_gpu_gbdt_hist_reduce_scatter", C.c_int, C.c_void_p, N.c_vpp, N.c_i64p, N.c_vpp, N.c_vpp, N.c_i64p, C.c_int,
    N.c_vpp, C.POINTER(C.c_int), C.c_void_p)
 
+_P("mp4j_gpu_lr_softmax_residual", C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p)
 _P("mp4j_gpu_allreduce_wire", C.c_int, C.c_void_p, N.c_vpp, C.c_int64, C.c_int64, C.c_int, C.c_void_p)
 _P("mp4j_gpu_custom_op", C.c_int, C.c_void_p, C.c_int, C.c_char_p, C.POINTER(C.c_int))
 _P("mp4j_gpu_trace", C.c_int, C.c_void_p, C.c_int)
@@ -133,6 +134,21 @@ def _check_tensor(t):
 def _check_host_tensor(t):
     if t.is_cuda or t.dim() != 1 or not t.is_contiguous():
         raise Mp4jException("the host-array pipeline needs 1-D contiguous CPU tensors (pinned for full speed)")
+
+
+def lr_softmax_residual(logits, y, rt=None, loss=None, stream=None):
+    """Fused softmax residual for LR (csrc/gpu/lr_residual.cu): logits bf16 [rows, C], y int64 [rows] (< 0 = padding).
+    Returns (Rt bf16 [C, rows] = softmax - onehot, loss fp32 [1] incremented by the summed NLL)."""
+    rows, Cn = logits.shape
+    if logits.dtype != torch.bfloat16 or not logits.is_contiguous() or y.dtype != torch.int64:
+        raise Mp4jException("lr_softmax_residual needs contiguous bf16 logits and int64 labels")
+    if rt is None:
+        rt = torch.empty(Cn, rows, dtype=torch.bfloat16, device=logits.device)
+    if loss is None:
+        loss = torch.zeros(1, dtype=torch.float32, device=logits.device)
+    check(N.lib.mp4j_gpu_lr_softmax_residual(logits.data_ptr(), y.data_ptr(), rows, Cn, rt.data_ptr(), loss.data_ptr(),
+                                             _stream_ptr(stream)))
+    return rt, loss
 
 
 def _native_op(operator):
