@@ -562,8 +562,10 @@ void GpuPlane::thread_allreduce(void* const* bufs, int T, int dtype, int op, int
     wcap = std::min<long long>(wcap, thread_ws_max_blocks());
     if (opt_.max_blocks > 0) wcap = std::min<long long>(wcap, opt_.max_blocks);
     const int wgrid = (int)std::max<long long>(1, std::min<long long>(wcap, (long long)((nbytes + wslot - 1) / wslot)));
+    // the fused kernels exchange slot-sized pieces whatever the array size: the in-switch reduction pays as soon
+    // as it removes traffic (beyond 2 ranks), independently of the dense collectives' size thresholds
     const bool wnvls = has_multicast() && nvls_supported(dtype, op) &&
-                       (algo >> 16 == MP4J_ALGO_NVLS || (algo >> 16 == MP4J_ALGO_AUTO && nvls_auto(nbytes)));
+                       (algo >> 16 == MP4J_ALGO_NVLS || (algo >> 16 == MP4J_ALGO_AUTO && world() > 2));
     if (tma) {
       last_ = CollStat{"thread_allreduce", wnvls ? "fused-tma-nvls" : "fused-tma-p2p", nbytes, wgrid, false};
       launch_thread_fused_tma(dtype, op, wnvls, a, wgrid, s);
@@ -590,7 +592,7 @@ void GpuPlane::thread_allreduce(void* const* bufs, int T, int dtype, int op, int
   if (opt_.max_blocks > 0) cap = std::min<long long>(cap, opt_.max_blocks);
   const int grid = (int)std::max<long long>(1, std::min<long long>(cap, (long long)((nbytes + slot - 1) / slot)));
   const bool nvls = vec && has_multicast() && nvls_supported(dtype, op) &&
-                    (algo >> 16 == MP4J_ALGO_NVLS || (algo >> 16 == MP4J_ALGO_AUTO && nvls_auto(nbytes)));
+                    (algo >> 16 == MP4J_ALGO_NVLS || (algo >> 16 == MP4J_ALGO_AUTO && world() > 2));
   last_ = CollStat{"thread_allreduce", nvls ? "fused-nvls" : "fused-p2p", nbytes, grid, false};
   launch_thread_allreduce(dtype, op, nvls, a, grid, 0 | vec_flag, s);
 }
