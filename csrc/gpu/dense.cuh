@@ -14,6 +14,7 @@ struct GrsItem {
   unsigned dst_mask;       // which ranks' heaps are written
   void* dst_local;         // optional: element 0 of a local (non-symmetric) output array
   const void* src_local;   // optional: local input copied into this rank's heap first (one-shot)
+  long long adj;           // bytes added to src_off / dst_off for THIS item (staged windows pack one sub-range per rank)
 };
 
 struct GrsArgs {

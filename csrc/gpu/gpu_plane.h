@@ -38,6 +38,10 @@ struct GpuOptions {
   size_t ag_nvls_min_bytes = 0;         // MP4J_AG_NVLS_MIN_BYTES
   size_t rs_nvls_max_bytes = 0;         // >= : two-shot again (0 = no upper end; MP4J_RS_NVLS_MAX_BYTES)
   size_t ag_nvls_max_bytes = 0;         // MP4J_AG_NVLS_MAX_BYTES
+  // 8-byte reductions: multimem.ld_reduce has no vector form for f64/i64 (one 8-byte request per instruction), so
+  // beyond this size the in-switch path is request-bound and two-shot P2P wins (8 GPUs, 1 GiB double: 545 vs
+  // ~650 GB/s; NCCL 711). AUTO only. MP4J_NVLS64_MAX_BYTES
+  size_t nvls64_max_bytes = 16ull << 20;
   int nvls_min_world = 2;               // AUTO uses NVLS only when world > this (MP4J_NVLS_MIN_WORLD)
   bool want_multicast = true;           // MP4J_NVLS=0 disables
   int max_blocks = 0;                   // 0 = occupancy-derived (MP4J_MAX_BLOCKS)

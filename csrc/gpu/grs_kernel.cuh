@@ -54,6 +54,7 @@ __global__ void __launch_bounds__(kThreads) grs_kernel(const __grid_constant__ G
   const int world = tab.world;
   const unsigned full = (world >= 32) ? 0xffffffffu : ((1u << world) - 1u);
 
+  const unsigned long long src_off = a.src_off + (unsigned long long)it.adj, dst_off = a.dst_off + (unsigned long long)it.adj;
   BlockEpoch ep;
   ep.load(tab, rank);
   if (a.dead_rank_p1 != 0 && rank == a.dead_rank_p1 - 1) return;  // test hook: this rank never shows up
@@ -64,15 +65,15 @@ __global__ void __launch_bounds__(kThreads) grs_kernel(const __grid_constant__ G
   const long long n = it.hi > it.lo ? it.hi - it.lo : 0;
   long long head = 0, nvec = 0;
   if (n > 0) {
-    const unsigned mis = (unsigned)((a.src_off + (unsigned long long)it.lo * ES) & 15ull);
+    const unsigned mis = (unsigned)((src_off + (unsigned long long)it.lo * ES) & 15ull);
     head = mis ? (16 - mis) / ES : 0;
     if (head > n) head = n;
     nvec = (n - head) / EPV;
   }
   const long long body_end = head + nvec * EPV;  // scalar set: [0,head) U [body_end, n)
   const long long nscalar = head + (n - body_end);
-  const unsigned long long src_b0 = a.src_off + (unsigned long long)(it.lo + head) * ES;  // body start
-  const unsigned long long dst_b0 = a.dst_off + (unsigned long long)(it.lo + head) * ES;
+  const unsigned long long src_b0 = src_off + (unsigned long long)(it.lo + head) * ES;  // body start
+  const unsigned long long dst_b0 = dst_off + (unsigned long long)(it.lo + head) * ES;
   const long long gstride = (long long)gridDim.x * blockDim.x;
   const long long gtid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
 
@@ -88,7 +89,7 @@ __global__ void __launch_bounds__(kThreads) grs_kernel(const __grid_constant__ G
     if (blockIdx.x == 0) {
       for (long long s = threadIdx.x; s < nscalar; s += blockDim.x) {
         const long long i = it.lo + (s < head ? s : body_end + (s - head));
-        *(T*)(mine + a.src_off + (unsigned long long)i * ES) = ((const T*)sl)[i];
+        *(T*)(mine + src_off + (unsigned long long)i * ES) = ((const T*)sl)[i];
       }
     }
   }
@@ -212,13 +213,13 @@ __global__ void __launch_bounds__(kThreads) grs_kernel(const __grid_constant__ G
       bool first = true;
       for (int q = 0; q < world; ++q) {
         if ((smask >> q) & 1u) {
-          const T x = *(const volatile T*)(tab.heap[q] + a.src_off + (unsigned long long)i * ES);
+          const T x = *(const volatile T*)(tab.heap[q] + src_off + (unsigned long long)i * ES);
           acc = first ? x : reduce_or_first<T, OP>(acc, x);
           first = false;
         }
       }
       for (int q = 0; q < world; ++q)
-        if ((dmask >> q) & 1u) *(volatile T*)(tab.heap[q] + a.dst_off + (unsigned long long)i * ES) = acc;
+        if ((dmask >> q) & 1u) *(volatile T*)(tab.heap[q] + dst_off + (unsigned long long)i * ES) = acc;
       if (it.dst_local != nullptr) ((T*)it.dst_local)[i] = acc;
     }
   }

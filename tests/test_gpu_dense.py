@@ -239,3 +239,44 @@ def test_invalid_operator_raises(planes):
     dev = [torch.zeros(8, dtype=torch.float32).cuda() for _ in range(2)]
     with pytest.raises(Mp4jException):
         plane.allreduce(dev, N.BAND, 0, 8)
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_staged_windows_pack_one_subrange_per_rank(world):
+    """Ordinary (non-symmetric) tensors larger than the staging window: every round carries sub-range j of EVERY
+    rank's segment (gpu_plane.cu run_grs). Ragged segments, from > 0, sizes that do not divide."""
+    from ytk_mp4j_b200.parallel.gpu_plane import EmuPlane
+    plane = EmuPlane(world, 0, heap_bytes=160 << 20, staging_bytes=1 << 20)
+    try:
+        n = 1500007  # 6 MB of fp32 through a 1 MiB window
+        g = torch.Generator().manual_seed(world)
+        host = [torch.randn(n, generator=g) for _ in range(world)]
+        total = host[0].clone()
+        for h in host[1:]:
+            total = total + h
+        cuts = sorted(torch.randint(5, n - 5, (world - 1,), generator=g).tolist())
+        froms, tos = [5] + cuts, cuts + [n - 3]
+        counts = [t - f for f, t in zip(froms, tos)]
+        dev = [h.cuda() for h in host]
+        plane.allreduce(dev, N.SUM, 7, n - 1, algo=N.ALGO_TWOSHOT)
+        torch.cuda.synchronize()
+        for r in range(world):
+            got = dev[r].cpu()
+            assert torch.equal(got[7:n - 1], total[7:n - 1]) and torch.equal(got[:7], host[r][:7]), r
+        dev = [h.cuda() for h in host]
+        plane.reduce_scatter(dev, N.SUM, 5, counts, algo=N.ALGO_TWOSHOT)
+        torch.cuda.synchronize()
+        for r in range(world):
+            assert torch.equal(dev[r].cpu()[froms[r]:tos[r]], total[froms[r]:tos[r]]), r
+        dev = [h.cuda() for h in host]
+        plane.allgather(dev, froms, tos, algo=N.ALGO_TWOSHOT)
+        torch.cuda.synchronize()
+        for r in range(world):
+            got = dev[r].cpu()
+            for q in range(world):
+                assert torch.equal(got[froms[q]:tos[q]], host[q][froms[q]:tos[q]]), (r, q)
+            assert torch.equal(got[:5], host[r][:5]) and torch.equal(got[n - 3:], host[r][n - 3:])
+        plane.check()
+        assert "staged=1" in plane.last()
+    finally:
+        plane.close()
