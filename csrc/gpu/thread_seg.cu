@@ -60,6 +60,7 @@ struct SegArgs {
   unsigned long long stg_off;    // heap offset of the slots: [block][kSegSlots][slot_bytes]
   unsigned long long slot_bytes;
   long long nwindows;
+  long long wstride;             // window visited at position i of the walk: (i * wstride) % nwindows (coprime)
   void* bufs[kMaxRanks][MP4J_MAX_THREADS];  // [rank][thread] in emulation, [0][thread] otherwise
   SegItem seg[kMaxSegs];
 };
@@ -195,7 +196,7 @@ __global__ void __launch_bounds__(kSegThreads, 2) thread_seg_kernel(const __grid
   auto wait_consumed = [&](long long kk) {
     bool ok = true;
     if (threadIdx.x < (unsigned)world) {
-      const Win x = decode((long long)blockIdx.x + kk * gridDim.x);
+      const Win x = decode((((long long)blockIdx.x + kk * gridDim.x) * a.wstride) % a.nwindows);
       if (pulls(x, (int)threadIdx.x, rank)) ok = wait_flag(tab, fc(rank, (int)threadIdx.x), base + (uint32_t)kk + 1u);
     }
     return __syncthreads_and(ok ? 1 : 0) != 0;
@@ -204,7 +205,10 @@ __global__ void __launch_bounds__(kSegThreads, 2) thread_seg_kernel(const __grid
   long long k = 0;
   bool alive = true;
   for (long long w = blockIdx.x; w < a.nwindows; w += gridDim.x, ++k) {
-    const Win x = decode(w);
+    // positions are spread over the whole window list: at any moment the blocks work on windows of MANY segments,
+    // so every rank is pulling (and being pulled from) at the same time. Walking the list in order made the ranks
+    // take turns - consecutive windows belong to one segment, i.e. to one destination rank.
+    const Win x = decode((w * a.wstride) % a.nwindows);
     const SegItem& sg = a.seg[x.seg];
     const bool reduce = x.reduce;
     const bool is_src = reduce || sg.src_rank == rank;
@@ -463,6 +467,14 @@ void GpuPlane::thread_segments(void* const* bufs, int T, int dtype, int op, cons
   a.nseg = n;
   a.nwindows = nwin;
   if (n == 0) return;
+  // stride of the walk: about one segment's worth of windows, coprime with the number of windows
+  a.wstride = 1;
+  if (nwin > 2 * n) {
+    long long st = nwin / n + 1;
+    auto gcd = [](long long x, long long y) { while (y) { long long t = x % y; x = y; y = t; } return x; };
+    while (gcd(st, nwin) != 1) ++st;
+    a.wstride = st % nwin;
+  }
   if (any_reduce && (!plane_op_ok(dtype, op) || op == MP4J_COPY || is_custom_op(op)))
     throw Error("operator is not defined for this dtype on the fused thread collectives");
   long long cap = (long long)sms_ * seg_blocks_per_sm();
