@@ -225,6 +225,19 @@ int mp4j_host_map_reduce(mp4j_comm* c, int mode, int root, const char* keys, siz
   MP4J_API_END
 }
 
+int mp4j_host_map_reduce_scatter(mp4j_comm* c, const char* keys, size_t keys_len, const void* vals, const int64_t* counts,
+                                 int dtype, int op, char** out_keys, size_t* out_keys_len, char** out_vals,
+                                 size_t* out_n) {
+  MP4J_API_BEGIN
+  std::string ok, ov;
+  c->pc->map_reduce_scatter(keys, keys_len, vals, counts, dtype, op, &ok, &ov);
+  *out_keys = dup_bytes(ok);
+  *out_keys_len = ok.size();
+  *out_vals = dup_bytes(ov);
+  *out_n = ov.size() / dtype_size(dtype);
+  MP4J_API_END
+}
+
 int mp4j_comm_send_bytes(mp4j_comm* c, int dest, const void* data, size_t n) {
   MP4J_API_BEGIN
   c->pc->send_bytes(dest, data, n);
@@ -243,6 +256,18 @@ int mp4j_comm_sendrecv_bytes(mp4j_comm* c, int dest, const void* data, size_t n,
   std::string s = c->pc->sendrecv_bytes(dest, data, n, src);
   *out = dup_bytes(s);
   *out_len = s.size();
+  MP4J_API_END
+}
+
+int mp4j_host_blob_collective(mp4j_comm* c, int kind, int root, mp4j_blob_get get, mp4j_blob_put put, void* user) {
+  MP4J_API_BEGIN
+  switch (kind) {
+    case MP4J_REDUCE_SCATTER: c->pc->blob_reduce_scatter(get, put, user); break;
+    case MP4J_ALL_GATHER: c->pc->blob_allgather(get, put, user); break;
+    case MP4J_GATHER: c->pc->blob_gather(root, get, put, user); break;
+    case MP4J_SCATTER: c->pc->blob_scatter(root, get, put, user); break;
+    default: throw Error("blob collective: kind must be reduce-scatter, allgather, gather or scatter");
+  }
   MP4J_API_END
 }
 

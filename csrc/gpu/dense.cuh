@@ -25,6 +25,7 @@ struct GrsArgs {
   int exit_barrier;
   int vec_ok;                  // local src/dst pointers are 16-byte congruent with the heap addresses
   int dead_rank_p1;            // test hook (option dead_rank): rank + 1 that returns at once, 0 = none
+  unsigned long long layout_key;  // where this rank believes the array lives; all ranks must agree (0 = not checked)
   GrsItem item[kMaxRanks];     // indexed by rank in emulation, [0] otherwise
 };
 

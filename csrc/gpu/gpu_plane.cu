@@ -195,6 +195,13 @@ void GpuPlane::free(size_t off) {
 }
 
 void GpuPlane::check_error() {
+  if (err_host_ && *err_host_ >= 2) {
+    poisoned_ = true;
+    *err_host_ = 0;
+    throw Error("GPU collective: the ranks disagree on where the array lives - a symmetric tensor (comm.empty) must be "
+                "the same allocation, at the same offset, on every rank, and symmetric and ordinary tensors must not "
+                "be mixed in one call; the results of that call are undefined and this GPU plane is now unusable");
+  }
   if (err_host_ && *err_host_) {
     poisoned_ = true;
     *err_host_ = 0;
@@ -276,6 +283,7 @@ void GpuPlane::run_grs(const char* name, void* const* arrs, int dtype, int op, c
   last_.algo = nvls_ok ? "nvls" : "p2p";
   if (zero_copy) {
     a.src_off = a.dst_off = sym_off;
+    a.layout_key = 0x5000000000000000ull | (unsigned long long)sym_off;  // "symmetric at this offset"
     for (int i = 0; i < L; ++i) {
       const int q = emulated() ? i : rank();
       GrsItem& it = a.item[i];
@@ -339,6 +347,7 @@ void GpuPlane::run_grs(const char* name, void* const* arrs, int dtype, int op, c
     }
     if (wmax <= 0) continue;
     a.src_off = a.dst_off = (unsigned long long)staging_off_;
+    a.layout_key = 0x6000000000000000ull | (unsigned long long)(nwin << 20) | (unsigned long long)j;  // "staged, round j of nwin"
     for (int i = 0; i < L; ++i) {
       const int q = emulated() ? i : rank();
       GrsItem& it = a.item[i];

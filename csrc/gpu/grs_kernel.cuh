@@ -94,9 +94,16 @@ __global__ void __launch_bounds__(kThreads) grs_kernel(const __grid_constant__ G
     }
   }
 
+  // every rank tells every rank where it believes the array lives (published before the barrier, compared after)
+  if (a.layout_key != 0 && a.entry_barrier && blockIdx.x == 0 && threadIdx.x < (unsigned)world)
+    ((volatile unsigned long long*)((char*)tab.sig[threadIdx.x] + kSigLayoutKeyOff))[rank] = a.layout_key;
   if (a.entry_barrier && !block_barrier_peers(tab, rank, ep)) {
     ep.store();
     return;  // a peer is missing: store nothing; the host raises on the error word
+  }
+  if (a.layout_key != 0 && a.entry_barrier && blockIdx.x == 0 && threadIdx.x < (unsigned)world) {
+    const unsigned long long theirs = ((volatile unsigned long long*)((char*)tab.sig[rank] + kSigLayoutKeyOff))[threadIdx.x];
+    if (theirs != a.layout_key) atomicMax((unsigned*)tab.err, 2u);  // host: "ranks disagree on the array's layout"
   }
 
   const unsigned smask = it.src_mask & full, dmask = it.dst_mask & full;

@@ -38,7 +38,10 @@ constexpr size_t kSigWsTraceOff = kSigWsFcEnd;
 constexpr int kWsTraceChunks = 64;
 // thread_seg.cu: "reader r has pulled this block's k-th window" [block][reader rank]
 constexpr size_t kSigSegFcOff = kSigWsTraceOff + kWsTraceChunks * 8 * 8;
-static_assert(kSigSegFcOff + kSigFlagsBytes <= kSigPadBytes, "signal pad layout overflows");
+// dense collectives: every rank's view of where the array lives (symmetric offset, or "staged window j"), one
+// u64 per source rank, compared after the entry barrier - ranks that disagree must not touch each other's memory
+constexpr size_t kSigLayoutKeyOff = kSigSegFcOff + kSigFlagsBytes;
+static_assert(kSigLayoutKeyOff + kMaxRanks * 8 <= kSigPadBytes, "signal pad layout overflows");
 
 struct PeerTable {
   int world;

@@ -183,4 +183,52 @@ void ProcessComm::map_reduce(int mode, int root, const char* blob, size_t blob_l
   out_vals->assign(result.vals.data(), result.vals.size());
 }
 
+// reduceScatterMap (PCS:1299-1327): the caller addresses rank q with its q-th map. blob / vals hold the p maps back
+// to back (counts[q] entries each); the ring reduce-scatter merges natively; the result is this rank's map.
+void ProcessComm::map_reduce_scatter(const char* blob, size_t blob_len, const void* vals, const int64_t* counts,
+                                     int dtype, int op, std::string* out_blob, std::string* out_vals) {
+  const size_t es = dtype_size(dtype);
+  if (es == 0 || !op_valid_for(dtype, op) || op == MP4J_COPY) throw Error("invalid operator for dtype");
+  const int p = n_;
+  std::vector<Part> parts((size_t)p);
+  {
+    const char* s = blob;
+    const char* end = blob + blob_len;
+    size_t i = 0;
+    for (int q = 0; q < p; ++q) {
+      Part& pt = parts[(size_t)q];
+      for (int64_t k = 0; k < counts[q]; ++k, ++i) {
+        const char* e = (const char*)memchr(s, 0, (size_t)(end - s));
+        if (!e) e = end;
+        const size_t len = (size_t)(e - s);
+        pt.lens.push_back((uint32_t)len);
+        pt.keys.append(s, len);
+        pt.vals.insert(pt.vals.end(), (const char*)vals + i * es, (const char*)vals + (i + 1) * es);
+        s = e < end ? e + 1 : end;
+      }
+    }
+  }
+  if (p > 1) {
+    std::lock_guard<std::mutex> lk(op_mu_);
+    const int next = (rank_ + 1) % p, prev = (rank_ - 1 + p) % p;
+    for (int s = 0; s < p - 1; ++s) {
+      const int sseg = ((rank_ - 1 - s) % p + p) % p, rseg = ((rank_ - 2 - s) % p + p) % p;
+      const std::string out = pack(parts[(size_t)sseg]);
+      const std::string in = sendrecv_bytes(next, out.data(), out.size(), prev);
+      merge(&parts[(size_t)rseg], in, dtype, op, es);
+      parts[(size_t)sseg] = Part();
+    }
+  }
+  const Part& result = parts[(size_t)rank_];
+  out_blob->clear();
+  out_blob->reserve(result.keys.size() + result.n());
+  size_t off = 0;
+  for (size_t i = 0; i < result.n(); ++i) {
+    if (i) out_blob->push_back('\0');
+    out_blob->append(result.keys.data() + off, result.lens[i]);
+    off += result.lens[i];
+  }
+  out_vals->assign(result.vals.data(), result.vals.size());
+}
+
 }  // namespace mp4j

@@ -60,8 +60,18 @@ class ProcessComm {
   // keys: n NUL-separated UTF-8 strings; vals: n elements of dtype. Outputs use the same layout.
   void map_reduce(int mode, int root, const char* blob, size_t blob_len, const void* vals, size_t n, int dtype,
                   int op, std::string* out_blob, std::string* out_vals);
+  // reduceScatterMap: p maps back to back in blob / vals (counts[q] entries each); result = this rank's merged map
+  void map_reduce_scatter(const char* blob, size_t blob_len, const void* vals, const int64_t* counts, int dtype, int op,
+                          std::string* out_blob, std::string* out_vals);
 
   // ---- byte-blob transport (length-prefixed) ----
+  // Collectives on opaque payloads (blob_coll.cc): the ring / tree runs here, the binding supplies the codec.
+  typedef int (*BlobGet)(void* user, int part, const char** data, size_t* n);
+  typedef int (*BlobPut)(void* user, int part, const char* data, size_t n);
+  void blob_reduce_scatter(BlobGet get, BlobPut put, void* user);   // p parts per rank; result = part[rank]
+  void blob_allgather(BlobGet get, BlobPut put, void* user);        // part[rank] is mine; put(q) for the others
+  void blob_gather(int root, BlobGet get, BlobPut put, void* user); // put(q) on the root only
+  void blob_scatter(int root, BlobGet get, BlobPut put, void* user);  // root: get(q) for all q; others: put(rank)
   void send_bytes(int dest, const void* data, size_t n);
   std::string recv_bytes(int src);
   std::string sendrecv_bytes(int dest, const void* data, size_t n, int src);

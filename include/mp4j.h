@@ -83,7 +83,25 @@ int mp4j_host_allreduce_rpc(mp4j_comm* c, void* arr, int dtype, int op, int64_t 
 int mp4j_host_map_reduce(mp4j_comm* c, int mode, int root, const char* keys, size_t keys_len, const void* vals,
                          size_t n, int dtype, int op, char** out_keys, size_t* out_keys_len, char** out_vals,
                          size_t* out_n);
+/* reduceScatterMap (PCS:1299-1327) on (String, primitive) maps: the slaveNum maps of this rank back to back in keys /
+ * vals, counts[q] entries in the q-th (the one addressed to rank q). Result (malloc'd, mp4j_free): this rank's map,
+ * equal keys reduced with `op` during the native ring reduce-scatter. */
+int mp4j_host_map_reduce_scatter(mp4j_comm* c, const char* keys, size_t keys_len, const void* vals, const int64_t* counts,
+                                 int dtype, int op, char** out_keys, size_t* out_keys_len, char** out_vals,
+                                 size_t* out_n);
 int mp4j_host_reduce_into(int dtype, int op, void* dst, const void* src, int64_t n);
+
+/* Collectives on opaque payloads (String / Object operands, ObjectOperand.java:114-156; maps with values the core
+ * cannot reduce): the ring reduce-scatter / ring allgather / binomial gather / binomial scatter of the reference
+ * (PCS:1329, 694, 440, 975) run natively; the binding supplies its codec.
+ *   get(user, part, &data, &n): serialized bytes of local part `part`, valid until the next callback
+ *   put(user, part, data, n)  : deserialize and merge into (reduce-scatter) / store as (others) part `part`
+ * kind: MP4J_REDUCE_SCATTER (p parts per rank, result = part[rank]), MP4J_ALL_GATHER (part[rank] is this rank's,
+ * put(q) delivers rank q's), MP4J_GATHER (put(q) on the root only), MP4J_SCATTER (root: get(q) for every q;
+ * others: put(rank)). Callbacks return 0, or non-zero to abort the collective with an error. */
+typedef int (*mp4j_blob_get)(void* user, int part, const char** data, size_t* n);
+typedef int (*mp4j_blob_put)(void* user, int part, const char* data, size_t n);
+int mp4j_host_blob_collective(mp4j_comm* c, int kind, int root, mp4j_blob_get get, mp4j_blob_put put, void* user);
 
 /* byte-blob transport between slaves (String/Object/map payloads; *out freed with mp4j_free) */
 int mp4j_comm_send_bytes(mp4j_comm* c, int dest, const void* data, size_t n);

@@ -18,6 +18,7 @@ COPY = 15
 LOG_DEBUG, LOG_INFO, LOG_ERROR = 0, 1, 2
 WIRE_LOSSLESS, WIRE_BF16, WIRE_FP8 = 0, 1, 2
 ALGO_AUTO, ALGO_ONESHOT, ALGO_TWOSHOT, ALGO_NVLS = 0, 1, 2, 3
+GATHER, SCATTER, ALL_GATHER, BROADCAST, REDUCE_SCATTER, REDUCE, ALL_REDUCE = range(7)  # mp4j_collective
 MAX_RANKS = 8
 MAX_THREADS = 64
 
@@ -104,6 +105,11 @@ _proto("mp4j_composite_long", C.c_int64, C.c_int32, C.c_int32)
 _proto("mp4j_composite_long_val", C.c_int32, C.c_int64)
 _proto("mp4j_composite_long_loc", C.c_int32, C.c_int64)
 _proto("mp4j_java_string_hash", C.c_int32, C.c_char_p, C.c_size_t)
+_proto("mp4j_host_map_reduce_scatter", C.c_int, C.c_void_p, C.c_char_p, C.c_size_t, C.c_void_p, c_i64p, C.c_int, C.c_int,
+       c_vpp, C.POINTER(C.c_size_t), c_vpp, C.POINTER(C.c_size_t))
+BLOB_GET = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t))
+BLOB_PUT = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_size_t)
+_proto("mp4j_host_blob_collective", C.c_int, C.c_void_p, C.c_int, C.c_int, BLOB_GET, BLOB_PUT, C.c_void_p)
 _proto("mp4j_map_keys64", C.c_int, C.c_char_p, C.c_size_t, C.c_int64, c_i64p)
 
 

@@ -65,6 +65,40 @@ def key_partition(key, p):
     return m + p if m < 0 else m
 
 
+class _MapCodec:
+    """Wire format of Map<String, primitive> payloads on the native blob collectives: [tag 0][u64 n][u64 key bytes]
+    [NUL-separated UTF-8 keys][n values] - no per-entry objects (the role of map_host.cc's Part for the collectives
+    that only MOVE maps: gatherMap, allgatherMap, broadcastMap, scatterMap). Anything that is not a plain dict of
+    str keys (or has NUL inside a key) falls back to the operand's own codec behind tag 1."""
+
+    def __init__(self, operand):
+        self.operand = operand
+        self.dtype = np.dtype(operand.np_dtype)
+
+    def dumps(self, m):
+        if isinstance(m, dict):
+            n = len(m)
+            try:
+                keys = "\0".join(m.keys()).encode("utf-8")
+            except TypeError:
+                keys = None
+            if keys is not None and (n == 0 or keys.count(b"\0") == n - 1):
+                vals = np.fromiter(m.values(), dtype=self.dtype, count=n).tobytes()
+                return b"\0" + n.to_bytes(8, "little") + len(keys).to_bytes(8, "little") + keys + vals
+        return b"\1" + self.operand.dumps(m)
+
+    def loads(self, raw):
+        if raw[:1] == b"\1":
+            return self.operand.loads(raw[1:])
+        n = int.from_bytes(raw[1:9], "little")
+        kl = int.from_bytes(raw[9:17], "little")
+        if n == 0:
+            return {}
+        keys = raw[17:17 + kl].decode("utf-8").split("\0")
+        vals = np.frombuffer(raw, dtype=self.dtype, count=n, offset=17 + kl).tolist()
+        return dict(zip(keys, vals))
+
+
 class ProcessCommSlave:
     def __init__(self, loginName, masterHost, masterPort, rank_hint=None, host=None):
         """Connects to the master, performs the rendezvous and learns rank / peers (PCS:143-210).
@@ -248,64 +282,71 @@ class ProcessCommSlave:
         check(N.lib.mp4j_comm_sendrecv_bytes(self._h, dest, data, len(data), src, C.byref(ptr), C.byref(n)))
         return operand.loads(N.take_bytes(ptr, n))
 
-    # the four data-moving algorithms of the reference, on opaque payloads
+    # the four data-moving algorithms of the reference on opaque payloads: the ring / tree runs in C++
+    # (csrc/host/blob_coll.cc); this side only serializes, deserializes and merges (the operand's job in the
+    # reference too, ObjectOperand.java:114-156). Inner tree nodes forward peers' payloads as raw bytes.
+    def _blob_collective(self, kind, root, get_part, put_part):
+        """get_part(i) -> payload object of local part i; put_part(i, payload) consumes a received payload."""
+        hold, err = [None], []
+
+        def c_get(_user, part, data, n):
+            try:
+                b = get_part(part)
+                hold[0] = b  # keeps the bytes alive until the next callback
+                data[0] = C.cast(C.c_char_p(b), C.c_void_p)
+                n[0] = len(b)
+                return 0
+            except BaseException as e:  # noqa: BLE001 - reported after the native call returns
+                err.append(e)
+                return 1
+
+        def c_put(_user, part, data, n):
+            try:
+                put_part(part, C.string_at(data, n))
+                return 0
+            except BaseException as e:  # noqa: BLE001
+                err.append(e)
+                return 1
+        g, pcb = N.BLOB_GET(c_get), N.BLOB_PUT(c_put)
+        rc = N.lib.mp4j_host_blob_collective(self._h, kind, root, g, pcb, None)
+        if err:
+            raise err[0] if isinstance(err[0], Mp4jException) else Mp4jException(repr(err[0]))
+        check(rc)
+
     def _ring_reduce_scatter(self, parts, merge, operand):
         """parts[i] = this rank's contribution to rank i's result (PCS:1329-1373)."""
-        p, r = self._n, self._rank
-        nxt, prv = (r + 1) % p, (r - 1) % p
-        for s in range(p - 1):
-            sseg, rseg = (r - 1 - s) % p, (r - 2 - s) % p
-            incoming = self._sendrecv(nxt, parts[sseg], prv, operand)
-            parts[rseg] = merge(parts[rseg], incoming)
-        return parts[r]
+        def put(i, raw):
+            parts[i] = merge(parts[i], operand.loads(raw))
+        self._blob_collective(N.REDUCE_SCATTER, 0, lambda i: operand.dumps(parts[i]), put)
+        return parts[self._rank]
 
     def _ring_allgather(self, mine, operand):
         """Returns the p payloads indexed by origin rank (PCS:694-737)."""
-        p, r = self._n, self._rank
-        nxt, prv = (r + 1) % p, (r - 1) % p
-        out = [None] * p
-        out[r] = mine
-        for s in range(p - 1):
-            sseg, rseg = (r - s) % p, (r - 1 - s) % p
-            out[rseg] = self._sendrecv(nxt, out[sseg], prv, operand)
+        out = [None] * self._n
+        out[self._rank] = mine
+
+        def put(i, raw):
+            out[i] = operand.loads(raw)
+        self._blob_collective(N.ALL_GATHER, 0, lambda i: operand.dumps(out[i]), put)
         return out
 
     def _tree_gather(self, mine, root, operand):
         """Binomial gather; returns {rank: payload} (complete on root)."""
-        p, r = self._n, self._rank
-        vr = (r - root) % p
-        acc = {r: mine}
-        m = 1
-        while m < p:
-            if vr & m:
-                self._send((vr - m + root) % p, acc, operand)
-                break
-            if vr + m < p:
-                acc.update(self._recv((vr + m + root) % p, operand))
-            m <<= 1
+        acc = {self._rank: mine}
+
+        def put(i, raw):
+            acc[i] = operand.loads(raw)
+        self._blob_collective(N.GATHER, root, lambda i: operand.dumps(mine), put)
         return acc
 
     def _tree_scatter(self, payloads, root, operand):
         """Binomial scatter of payloads[0..p) held by root; returns this rank's payload."""
-        p, r = self._n, self._rank
-        vr = (r - root) % p
-        top = 1
-        while top < p:
-            top <<= 1
-        top >>= 1
-        if vr == 0:
-            acc = {q: payloads[q] for q in range(p)}
-            m = top
-        else:
-            lsb = vr & -vr
-            acc = self._recv((vr - lsb + root) % p, operand)
-            m = lsb >> 1
-        while m >= 1:
-            if vr + m < p:
-                sub = {(v + root) % p: acc[(v + root) % p] for v in range(vr + m, min(vr + 2 * m, p))}
-                self._send((vr + m + root) % p, sub, operand)
-            m >>= 1
-        return acc[r]
+        box = [payloads[self._rank] if self._rank == root else None]
+
+        def put(i, raw):
+            box[0] = operand.loads(raw)
+        self._blob_collective(N.SCATTER, root, lambda i: operand.dumps(payloads[i]), put)
+        return box[0]
 
     @staticmethod
     def _seg(arr, f, t):
@@ -347,7 +388,7 @@ class ProcessCommSlave:
         self._check_root(rootRank)
         if self._n == 1:
             return mapData
-        acc = self._tree_gather(mapData, rootRank, operand)
+        acc = self._tree_gather(mapData, rootRank, self._map_wire(operand))
         if self._rank != rootRank:
             return {}
         out = {}
@@ -384,7 +425,7 @@ class ProcessCommSlave:
             out = self._gpu_allgather_map([mapData], operand)
             if out is not None:
                 return out
-        return self._ring_allgather(mapData, operand)
+        return self._ring_allgather(mapData, self._map_wire(operand))
 
     # ------------------------------------------------------------------ broadcast
     def broadcastArray(self, arrData, operand, from_, to, rootRank):
@@ -422,9 +463,10 @@ class ProcessCommSlave:
             parts = [dict() for _ in range(self._n)]
             for k, v in mapData.items():
                 parts[key_partition(k, self._n)][k] = v
-        mine = self._tree_scatter(parts, rootRank, operand)
+        wire = self._map_wire(operand)
+        mine = self._tree_scatter(parts, rootRank, wire)
         out = {}
-        for m in self._ring_allgather(mine, operand):
+        for m in self._ring_allgather(mine, wire):
             out.update(m)
         return out
 
@@ -459,7 +501,7 @@ class ProcessCommSlave:
             return mapDataList[0]
         if self._rank == rootRank and len(mapDataList) != self._n:
             raise Mp4jException("scatterMap needs one map per slave on the root")
-        return self._tree_scatter(mapDataList if self._rank == rootRank else None, rootRank, operand)
+        return self._tree_scatter(mapDataList if self._rank == rootRank else None, rootRank, self._map_wire(operand))
 
     def _scatterMapSpecial(self, mapListList, operand, rootRank):
         """T maps per rank (used by ThreadCommSlave.scatterMap, PCS:999)."""
@@ -503,6 +545,8 @@ class ProcessCommSlave:
             out = self._gpu_reduce_scatter_map(list(enumerate(mapDataList)), operand, operator)
             if out is not None:
                 return out
+        if self._native_map_ok(operand, operator) and all(isinstance(m, dict) for m in mapDataList):
+            return self._native_map_reduce_scatter(mapDataList, operand, operator)
         return self._ring_reduce_scatter(list(mapDataList), self._merge_map(operator), operand)
 
     # ------------------------------------------------------------------ reduce
@@ -746,6 +790,36 @@ class ProcessCommSlave:
             out.append(dict(zip(names[off:off + c], vals[off:off + c])))
             off += c
         return out
+
+    def _map_wire(self, operand):
+        """Codec of map payloads on the move-only map collectives: the packed native format for primitive values."""
+        if operand.is_primitive and operand.np_dtype is not None and os.environ.get("MP4J_NATIVE_MAPS", "1") != "0":
+            return _MapCodec(operand)
+        return operand
+
+    def _native_map_reduce_scatter(self, mapDataList, operand, operator):
+        """reduceScatterMap natively (csrc/host/map_host.cc): the p maps back to back, ring reduce-scatter with the
+        native string-keyed merge."""
+        counts = N.i64_array([len(m) for m in mapDataList])
+        n = sum(len(m) for m in mapDataList)
+        try:
+            blob = "\0".join(k for m in mapDataList for k in m.keys()).encode("utf-8")
+        except TypeError:
+            raise Mp4jException("map keys must be str (Map<String, V> in the reference)")
+        if n and blob.count(b"\0") != n - 1:
+            raise Mp4jException("map keys must not contain NUL characters")
+        vals = np.fromiter((v for m in mapDataList for v in m.values()), dtype=operand.np_dtype, count=n)
+        ok, ov = C.c_void_p(), C.c_void_p()
+        okl, on = C.c_size_t(), C.c_size_t()
+        check(N.lib.mp4j_host_map_reduce_scatter(self._h, blob, len(blob), vals.ctypes.data, counts, operand.code,
+                                                 operator.code, C.byref(ok), C.byref(okl), C.byref(ov), C.byref(on)))
+        m = on.value
+        keys_raw = N.take_bytes(ok, okl)
+        vals_raw = N.take_bytes(ov, C.c_size_t(m * np.dtype(operand.np_dtype).itemsize))
+        if m == 0:
+            return {}
+        return dict(zip(keys_raw.decode("utf-8").split("\0"),
+                        np.frombuffer(vals_raw, dtype=operand.np_dtype, count=m).tolist()))
 
     @staticmethod
     def _native_map_ok(operand, operator):
