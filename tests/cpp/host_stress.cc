@@ -12,6 +12,7 @@
 #include <string.h>
 
 #include <atomic>
+#include <algorithm>
 #include <string>
 #include <thread>
 #include <vector>
@@ -238,6 +239,75 @@ static void rank_main(int port, int r, int p, int rounds, int64_t n) {
         mp4j_free(ok);
         mp4j_free(ov);
       }
+    }
+    {  // opaque-payload collectives: the ring / trees run natively, this side is the "codec"
+      struct Ctx {
+        int r, p;
+        std::vector<std::string> parts;   // local parts (serialized form = the string itself)
+        std::vector<std::string> got;
+      } cx{r, p, std::vector<std::string>((size_t)p), std::vector<std::string>((size_t)p)};
+      auto get = [](void* u, int part, const char** d, size_t* n) -> int {
+        Ctx* c2 = (Ctx*)u;
+        *d = c2->parts[(size_t)part].data();
+        *n = c2->parts[(size_t)part].size();
+        return 0;
+      };
+      auto put_store = [](void* u, int part, const char* d, size_t n) -> int {
+        ((Ctx*)u)->got[(size_t)part].assign(d, n);
+        return 0;
+      };
+      auto put_merge = [](void* u, int part, const char* d, size_t n) -> int {  // "reduce" = concatenate sorted digits
+        Ctx* c2 = (Ctx*)u;
+        c2->parts[(size_t)part].append(d, n);
+        std::sort(c2->parts[(size_t)part].begin(), c2->parts[(size_t)part].end());
+        return 0;
+      };
+      // reduce-scatter: part q of rank r = one character 'a' + r; result on rank q = all p characters
+      for (int q = 0; q < p; ++q) cx.parts[(size_t)q] = std::string(1, (char)('a' + r));
+      OK(mp4j_host_blob_collective(c, MP4J_REDUCE_SCATTER, 0, get, put_merge, &cx));
+      if (p > 1) {
+        std::string want;
+        for (int q = 0; q < p; ++q) want.push_back((char)('a' + q));
+        CHECK(cx.parts[(size_t)r] == want, "blob reduce-scatter got %s", cx.parts[(size_t)r].c_str());
+      }
+      // allgather / gather / scatter of variable-length payloads
+      for (int q = 0; q < p; ++q) cx.parts[(size_t)q] = std::string((size_t)(1000 * (r + 1) + q), (char)('A' + r));
+      OK(mp4j_host_blob_collective(c, MP4J_ALL_GATHER, 0, get, put_store, &cx));
+      for (int q = 0; q < p; ++q)
+        if (q != r) CHECK(cx.got[(size_t)q] == std::string((size_t)(1000 * (q + 1) + q), (char)('A' + q)), "blob allgather from %d", q);
+      for (auto& g : cx.got) g.clear();
+      const int root = p - 1;
+      OK(mp4j_host_blob_collective(c, MP4J_GATHER, root, get, put_store, &cx));
+      if (r == root)
+        for (int q = 0; q < p; ++q)
+          if (q != r) CHECK(cx.got[(size_t)q] == std::string((size_t)(1000 * (q + 1) + q), (char)('A' + q)), "blob gather from %d", q);
+      for (auto& g : cx.got) g.clear();
+      OK(mp4j_host_blob_collective(c, MP4J_SCATTER, root, get, put_store, &cx));
+      if (r != root)
+        CHECK(cx.got[(size_t)r] == std::string((size_t)(1000 * (root + 1) + r), (char)('A' + root)), "blob scatter to %d", r);
+    }
+    {  // native reduceScatterMap: p maps per rank, map q = {"q-i": 1.0}, result on rank q = {"q-i": p}
+      std::string blob;
+      std::vector<double> vals;
+      std::vector<int64_t> counts;
+      const int nk = 300;
+      for (int q = 0; q < p; ++q) {
+        counts.push_back(nk);
+        for (int i = 0; i < nk; ++i) {
+          if (!blob.empty()) blob.push_back('\0');
+          blob += std::to_string(q) + "-" + std::to_string(i);
+          vals.push_back(1.0);
+        }
+      }
+      char *ok = nullptr, *ov = nullptr;
+      size_t okl = 0, on = 0;
+      OK(mp4j_host_map_reduce_scatter(c, blob.data(), blob.size(), vals.data(), counts.data(), MP4J_F64, MP4J_SUM, &ok, &okl,
+                                      &ov, &on));
+      CHECK(on == (size_t)nk, "map reduce-scatter entries=%zu", on);
+      for (size_t i = 0; i < on; ++i) CHECK(((const double*)ov)[i] == (double)p, "map reduce-scatter value");
+      CHECK(okl > 2 && ok[0] == (char)('0' + r % 10), "map reduce-scatter keys start with own rank");
+      mp4j_free(ok);
+      mp4j_free(ov);
     }
     {  // process x thread allreduce: 3 threads per rank, every thread's array ends with the global sum
       const int T = 3;
