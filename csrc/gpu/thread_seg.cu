@@ -27,6 +27,8 @@
 //                                REDUCE), write the local destination thread buffers
 // Only what a destination needs crosses NVLink, once. Unaligned segment ends (counts are arbitrary) are
 // handled element-wise; the 16-byte aligned interior of every window moves as 16-byte vectors.
+#include <stdlib.h>
+
 #include <algorithm>
 
 #include "../core/partition.h"
@@ -60,6 +62,7 @@ struct SegArgs {
   unsigned long long stg_off;    // heap offset of the slots: [block][kSegSlots][slot_bytes]
   unsigned long long slot_bytes;
   long long nwindows;
+  int lag, pad_;                 // stage 2 of a window runs `lag` iterations after its stage 1 (1 .. kSegSlots - 1)
   long long wstride;             // window visited at position i of the walk: (i * wstride) % nwindows (coprime)
   void* bufs[kMaxRanks][MP4J_MAX_THREADS];  // [rank][thread] in emulation, [0][thread] otherwise
   SegItem seg[kMaxSegs];
@@ -202,9 +205,20 @@ __global__ void __launch_bounds__(kSegThreads, 2) thread_seg_kernel(const __grid
     return __syncthreads_and(ok ? 1 : 0) != 0;
   };
 
-  long long k = 0;
+  // Software pipeline inside the block: iteration i runs stage 1 of this block's window i and THEN stage 2 of its
+  // window i - D. Every window needs all its source ranks, so a destination that did "stage 1, stage 2" back to
+  // back kept everybody waiting for its next stage 1 while it was pulling (4 GPUs: 1.42 ms for the 8 x 64 Mi
+  // reduce-scatter); with the lag its stage 1 runs D windows ahead and the pull is off the other ranks' path. D must
+  // leave slack in the slot ring (a source reuses a slot kSegSlots windows later and then needs the reader's "pulled"
+  // flag): D = kSegSlots - 1 couples the ranks iteration by iteration again; D = 1 leaves three windows of slack.
+  const long long K = a.nwindows > (long long)blockIdx.x ? (a.nwindows - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+  const long long D = world > 1 ? a.lag : 0;
   bool alive = true;
-  for (long long w = blockIdx.x; w < a.nwindows; w += gridDim.x, ++k) {
+  for (long long it = 0; it < K + D && alive; ++it)
+  for (int ph = 0; ph < 2 && alive; ++ph) {
+    const long long k = ph == 0 ? it : it - D;
+    if (k < 0 || k >= K || (ph == 1 && world == 1)) continue;  // one rank: stage 1 wrote the results already
+    const long long w = (long long)blockIdx.x + k * gridDim.x;
     // positions are spread over the whole window list: at any moment the blocks work on windows of MANY segments,
     // so every rank is pulling (and being pulled from) at the same time. Walking the list in order made the ranks
     // take turns - consecutive windows belong to one segment, i.e. to one destination rank.
@@ -227,6 +241,7 @@ __global__ void __launch_bounds__(kSegThreads, 2) thread_seg_kernel(const __grid
     const int td0 = sg.dst_thread == kAll ? 0 : sg.dst_thread, td1 = sg.dst_thread == kAll ? nT : sg.dst_thread + 1;
     auto buf = [&](int t, long long y) { return (char*)a.bufs[erow][t] + (y - c); };
 
+    if (ph == 0) {
     // the slot of this window was last used kSegSlots windows ago: its readers must be done with it
     if (world > 1 && k >= kSegSlots && !wait_consumed(k - kSegSlots)) {
       alive = false;
@@ -305,8 +320,10 @@ __global__ void __launch_bounds__(kSegThreads, 2) thread_seg_kernel(const __grid
       if (threadIdx.x < (unsigned)world && pulls(x, (int)threadIdx.x, rank))
         st_relaxed_sys(fa((int)threadIdx.x, rank), base + (uint32_t)k + 1u);
     }
+    continue;
+    }  // ph == 0
 
-    // ================= stage 2: pull from the source ranks' slots, write the local destinations
+    // ================= stage 2 (ph == 1): pull from the source ranks' slots, write the local destinations
     if (is_dst && (reduce || sg.src_rank != rank)) {
       bool ok = true;
       if (threadIdx.x < (unsigned)world && pulls(x, rank, (int)threadIdx.x))
@@ -364,9 +381,9 @@ __global__ void __launch_bounds__(kSegThreads, 2) thread_seg_kernel(const __grid
   }
   // nobody leaves (and lets a later launch reuse the slots) while a reader may still pull from them
   if (world > 1 && alive)
-    for (long long kk = k > kSegSlots ? k - kSegSlots : 0; kk < k; ++kk)
+    for (long long kk = K > kSegSlots ? K - kSegSlots : 0; kk < K; ++kk)
       if (!wait_consumed(kk)) break;
-  ep.value = base + (uint32_t)k;  // k windows on every rank: the per-block counters stay in step
+  ep.value = base + (uint32_t)K;  // K windows on every rank: the per-block counters stay in step
   ep.store();
 }
 
@@ -467,6 +484,8 @@ void GpuPlane::thread_segments(void* const* bufs, int T, int dtype, int op, cons
   a.nseg = n;
   a.nwindows = nwin;
   if (n == 0) return;
+  static const int seg_lag = getenv("MP4J_SEG_LAG") ? atoi(getenv("MP4J_SEG_LAG")) : 1;
+  a.lag = std::max(1, std::min(seg_lag, kSegSlots - 1));
   // stride of the walk: about one segment's worth of windows, coprime with the number of windows
   a.wstride = 1;
   if (nwin > 2 * n) {
