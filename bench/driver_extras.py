@@ -391,7 +391,7 @@ def consumers(pcs, plane, rank, world, steps=8):
     torch.cuda.empty_cache()
     # ---- sparse LR + the map collective alone
     Fs, n, nnz = 10_000_000, 262144, 8
-    sm = SparseLR(pcs, Fs, lr=0.1)
+    sm = SparseLR(pcs, Fs, lr=0.1, max_nnz=n * nnz, rows_total=n * world)
     cols = torch.randint(0, Fs, (n * nnz,), device="cuda", generator=g)
     rws = torch.arange(n, device="cuda").repeat_interleave(nnz)
     vals = torch.ones(n * nnz, device="cuda")
@@ -402,7 +402,9 @@ def consumers(pcs, plane, rank, world, steps=8):
     keys = cols[: 2_000_000].contiguous()
     kv = torch.ones(2_000_000, device="cuda")
     if world > 1:
-        ms = timed(lambda: plane.allreduce_map(keys, kv, Operators.Float.SUM), k=max(3, steps // 2))
+        ms = timed(lambda: plane.allreduce_map(keys, kv, Operators.Float.SUM, max_n=2_000_000,
+                                               out_cap=min(2_000_000 * world, 10_000_000), copy=False),
+                   k=max(3, steps // 2))
         out["allreduce_map"] = {"Gkeys_per_s": round(world * 2_000_000 / (ms * 1e-3) / 1e9, 2), "ms": round(ms, 3),
                                 "config": "2M (int64 key, fp32) pairs per GPU drawn from 10M ids, N=%d" % world}
     else:

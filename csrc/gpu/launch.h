@@ -54,6 +54,12 @@ void map_launch_compact(int dtype, const MapTable& t, long long* out_keys, void*
                         unsigned long long* count, unsigned long long out_cap, int grid, cudaStream_t s);
 void map_launch_gather(int dtype, const PeerTable& tab, unsigned long long ocnt_off, unsigned long long okeys_off,
                        unsigned long long ovals_off, unsigned long long out_cap, const long long* const* own_keys,
-                       const void* const* own_vals, const unsigned long long* const* own_count, int nlocal, bool push,
-                       int grid, cudaStream_t s);
+                       const void* const* own_vals, const unsigned long long* const* own_count,
+                       unsigned long long* const* info, unsigned long long overflow_off, int nlocal, bool publish,
+                       bool push, int grid, cudaStream_t s);
+// clear + merge + compact + publish of a map collective in one cooperative kernel (t etc.: one entry per local rank)
+void map_launch_table(int dtype, int op, const PeerTable& tab, const MapTable* t, long long* const* own_keys,
+                      void* const* own_vals, unsigned long long* const* own_count, int nlocal,
+                      unsigned long long own_cap, unsigned long long rkeys_off, unsigned long long rvals_off,
+                      unsigned long long rcnt_off, unsigned long long ocnt_off, long long cap, int sms, cudaStream_t s);
 }  // namespace mp4j

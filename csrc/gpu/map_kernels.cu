@@ -8,13 +8,19 @@
 //        receive region over NVLink (no local bucket copy, no serialisation); per-destination
 //        cursors are warp-aggregated atomics; the last block publishes the counts and meets the
 //        peers at a flag barrier.
-//   K11 map_merge          : the owner inserts what it received into an open-addressing table
-//        (atomicCAS on the key, atomic operator on the value).
-//   map_compact            : table -> dense (key, value) arrays + owned count (published to peers).
+//   K11 map_table          : one cooperative kernel: the owner clears as much of its open-addressing
+//        table as the received counts need, inserts what it received (atomicCAS on the key, atomic
+//        operator on the value), compacts the table into dense (key, value) arrays, publishes the
+//        owned count to the peers and meets them.
 //   map_allgather_push     : every rank pushes its owned pairs to the right offset of every peer's
-//        output (offsets = prefix sums of the published counts, read on the device: no host sync).
+//        output (offsets = prefix sums of the published counts, read on the device: no host sync)
+//        and writes the 4-word info block the caller reads after synchronising.
+// A collective is these three launches and nothing else on the stream (no memsets). The separate
+// clear / merge / compact kernels remain for the local (one GPU, no peers) reduce-by-key.
 // Float sums use atomicAdd: the order of additions, hence the last bits, is not deterministic
 // (the reference's order is arrival order, PCS:1329-1373 - also unspecified).
+#include <cooperative_groups.h>
+
 #include <algorithm>
 #include <mutex>
 #include <string>
@@ -24,6 +30,8 @@
 #include "map_kernels.cuh"
 
 namespace mp4j {
+
+namespace cg = cooperative_groups;
 
 namespace {
 
@@ -250,6 +258,87 @@ __global__ void __launch_bounds__(kMapThreads) map_compact_kernel(MapTable t, lo
   }
 }
 
+// ---------------------------------------------------------------------------------------- K11f
+// One cooperative kernel for everything between the two exchanges of a map collective: clear the part
+// of the table this call needs, merge the p receive regions, compact the table into dense arrays,
+// publish the owned count to every peer and meet the peers. The table is allocated for the worst
+// case (every pair of every rank lands here: 2 * p * cap slots, 512 MiB at 8 GPUs x 2M pairs), but
+// the part that is cleared, probed and scanned is sized on the device from the counts that actually
+// arrived (2x the received pairs, rounded up to a power of two): with balanced keys that is 1/p of it.
+struct MapTableArgs {
+  PeerTable tab;
+  unsigned long long rkeys_off, rvals_off, rcnt_off, ocnt_off;
+  long long cap;
+  unsigned long long own_cap;
+  MapTable t[kMaxRanks];  // indexed by rank in emulation, [0] otherwise (like every per-rank array here)
+  long long* own_keys[kMaxRanks];
+  void* own_vals[kMaxRanks];
+  unsigned long long* own_count[kMaxRanks];
+};
+
+template <typename V, int OP>
+__global__ void __launch_bounds__(kMapThreads) map_table_kernel(const __grid_constant__ MapTableArgs a) {
+  cg::grid_group grid = cg::this_grid();
+  const PeerTable& tab = a.tab;
+  const int rank = my_rank(tab);
+  const int p = tab.world;
+  const int row = tab.emulate ? rank : 0;
+  const unsigned long long* cnt = (const unsigned long long*)(tab.heap[rank] + a.rcnt_off);
+  const long long* rk = (const long long*)(tab.heap[rank] + a.rkeys_off);
+  const V* rv = (const V*)(tab.heap[rank] + a.rvals_off);
+  unsigned long long total = 0;
+  for (int s = 0; s < p; ++s) total += cnt[s];
+  unsigned long long size = 1024;
+  while (size < 2 * total) size <<= 1;
+  if (size > a.t[row].mask + 1) size = a.t[row].mask + 1;
+  const MapTable t{a.t[row].keys, a.t[row].vals, size - 1};
+  const unsigned long long tid = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const unsigned long long nthr = (unsigned long long)gridDim.x * blockDim.x;
+  unsigned long long* count = a.own_count[row];
+  for (unsigned long long i = tid; i < size; i += nthr) {
+    t.keys[i] = kMapEmpty;
+    ((V*)t.vals)[i] = identity<V, OP>();
+  }
+  if (tid == 0) *count = 0;
+  grid.sync();
+  for (int s = 0; s < p; ++s) {
+    const unsigned long long c = cnt[s];
+    for (unsigned long long i = tid; i < c; i += nthr)
+      table_insert<V, OP>(t, rk[(unsigned long long)s * a.cap + i], rv[(unsigned long long)s * a.cap + i]);
+  }
+  grid.sync();
+  {
+    const unsigned lane = threadIdx.x & 31;
+    long long* out_keys = a.own_keys[row];
+    V* out_vals = (V*)a.own_vals[row];
+    for (unsigned long long i0 = (unsigned long long)blockIdx.x * blockDim.x; i0 < size; i0 += nthr) {
+      const unsigned long long i = i0 + threadIdx.x;
+      const bool live = i < size && t.keys[i] != kMapEmpty;
+      const unsigned m = __ballot_sync(0xffffffffu, live);
+      if (m == 0) continue;
+      unsigned long long base = 0;
+      const int leader = __ffs(m) - 1;
+      if ((int)lane == leader) base = atomicAdd(count, (unsigned long long)__popc(m));
+      base = __shfl_sync(0xffffffffu, base, leader);
+      if (live) {
+        const unsigned long long o = base + __popc(m & ((1u << lane) - 1u));
+        if (o < a.own_cap) {
+          out_keys[o] = t.keys[i];
+          out_vals[o] = ((const V*)t.vals)[i];
+        }
+      }
+    }
+  }
+  grid.sync();
+  if (blockIdx.x == 0) {
+    if (threadIdx.x < (unsigned)p)
+      *((volatile unsigned long long*)(tab.heap[threadIdx.x] + a.ocnt_off) + rank) = *(volatile unsigned long long*)count;
+    __syncthreads();
+    // after this barrier: every peer's owned count is here, and no peer still reads its receive regions
+    ctrl_barrier_peers(tab, rank);
+  }
+}
+
 // publishes this rank's owned count to every peer, meets the peers, then pushes the owned pairs to
 // offset sum(counts[q < rank]) of every peer's output arrays; total goes to *total_out.
 struct MapGatherArgs {
@@ -261,6 +350,10 @@ struct MapGatherArgs {
   const long long* own_keys[kMaxRanks];
   const void* own_vals[kMaxRanks];
   const unsigned long long* own_count[kMaxRanks];
+  // what the caller reads after synchronising the stream (pinned, mapped): pairs in the result, receive overflow,
+  // output overflow, pairs this rank owned. Written by block 0 of the push kernel when info[row] is set.
+  unsigned long long* info[kMaxRanks];
+  unsigned long long overflow_off;  // heap: receive-overflow flag of the partition step (0 = none in this mode)
 };
 
 __global__ void __launch_bounds__(kMapThreads) map_publish_count_kernel(const __grid_constant__ MapGatherArgs a) {
@@ -287,6 +380,20 @@ __global__ void __launch_bounds__(kMapThreads) map_allgather_push_kernel(const _
   const V* sv = (const V*)a.own_vals[row];
   BlockEpoch ep;
   ep.load(tab, rank);
+  if (blockIdx.x == 0 && threadIdx.x == 0 && a.info[row]) {
+    unsigned long long total = 0;
+    for (int q = 0; q < p; ++q) total += oc[q];
+    unsigned long long* info = a.info[row];
+    info[0] = total < a.out_cap ? total : a.out_cap;
+    info[1] = 0;
+    if (a.overflow_off) {  // read and re-arm: the flag is not sticky across calls
+      volatile unsigned long long* f = (volatile unsigned long long*)(tab.heap[rank] + a.overflow_off);
+      info[1] = *f;
+      *f = 0;
+    }
+    info[2] = total > a.out_cap ? 1 : 0;
+    info[3] = *a.own_count[row];
+  }
   for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < mine;
        i += (unsigned long long)gridDim.x * blockDim.x) {
     if (off + i >= a.out_cap) break;
@@ -315,16 +422,17 @@ void launch_partition(const MapExchangeArgs& a, int grid, cudaStream_t s) {
 }
 
 template <typename V>
-void launch_gather(const MapGatherArgs& a, bool push, int grid, cudaStream_t s) {
+void launch_gather(const MapGatherArgs& a, bool publish, bool push, int grid, cudaStream_t s) {
   if (a.tab.emulate) {
     void* params[] = {(void*)&a};
-    MP4J_CUDA(cudaLaunchCooperativeKernel((const void*)map_publish_count_kernel, dim3(1, a.tab.world),
-                                          dim3(kMapThreads), params, 0, s));
+    if (publish)
+      MP4J_CUDA(cudaLaunchCooperativeKernel((const void*)map_publish_count_kernel, dim3(1, a.tab.world),
+                                            dim3(kMapThreads), params, 0, s));
     if (push)
       MP4J_CUDA(cudaLaunchCooperativeKernel((const void*)map_allgather_push_kernel<V>, dim3(grid, a.tab.world),
                                             dim3(kMapThreads), params, 0, s));
   } else {
-    map_publish_count_kernel<<<1, kMapThreads, 0, s>>>(a);
+    if (publish) map_publish_count_kernel<<<1, kMapThreads, 0, s>>>(a);
     if (push) map_allgather_push_kernel<V><<<grid, kMapThreads, 0, s>>>(a);
     MP4J_CUDA(cudaGetLastError());
   }
@@ -400,10 +508,42 @@ void map_launch_compact(int dtype, const MapTable& t, long long* out_keys, void*
   MP4J_CUDA(cudaGetLastError());
 }
 
+void map_launch_table(int dtype, int op, const PeerTable& tab, const MapTable* t, long long* const* own_keys,
+                      void* const* own_vals, unsigned long long* const* own_count, int nlocal,
+                      unsigned long long own_cap, unsigned long long rkeys_off, unsigned long long rvals_off,
+                      unsigned long long rcnt_off, unsigned long long ocnt_off, long long cap, int sms, cudaStream_t s) {
+  MapTableArgs a{};
+  a.tab = tab;
+  a.rkeys_off = rkeys_off;
+  a.rvals_off = rvals_off;
+  a.rcnt_off = rcnt_off;
+  a.ocnt_off = ocnt_off;
+  a.cap = cap;
+  a.own_cap = own_cap;
+  for (int i = 0; i < nlocal; ++i) {
+    a.t[i] = t[i];
+    a.own_keys[i] = own_keys[i];
+    a.own_vals[i] = own_vals[i];
+    a.own_count[i] = own_count[i];
+  }
+  dispatch_v(dtype, [&](auto v) {
+    dispatch_op(op, [&](auto o) {
+      auto kfn = map_table_kernel<decltype(v), decltype(o)::value>;
+      int per_sm = 0;
+      MP4J_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kfn, kMapThreads, 0));
+      const int rows = tab.emulate ? tab.world : 1;
+      const int grid = std::max(1, std::min(per_sm, 4) * sms / rows);  // co-resident: the kernel has grid-wide syncs
+      void* params[] = {(void*)&a};
+      MP4J_CUDA(cudaLaunchCooperativeKernel((const void*)kfn, dim3(grid, rows), dim3(kMapThreads), params, 0, s));
+    });
+  });
+}
+
 void map_launch_gather(int dtype, const PeerTable& tab, unsigned long long ocnt_off, unsigned long long okeys_off,
                        unsigned long long ovals_off, unsigned long long out_cap, const long long* const* own_keys,
-                       const void* const* own_vals, const unsigned long long* const* own_count, int nlocal, bool push,
-                       int grid, cudaStream_t s) {
+                       const void* const* own_vals, const unsigned long long* const* own_count,
+                       unsigned long long* const* info, unsigned long long overflow_off, int nlocal, bool publish,
+                       bool push, int grid, cudaStream_t s) {
   MapGatherArgs a{};
   a.tab = tab;
   a.ocnt_off = ocnt_off;
@@ -414,8 +554,10 @@ void map_launch_gather(int dtype, const PeerTable& tab, unsigned long long ocnt_
     a.own_keys[i] = own_keys[i];
     a.own_vals[i] = own_vals[i];
     a.own_count[i] = own_count[i];
+    a.info[i] = info ? info[i] : nullptr;
   }
-  dispatch_v(dtype, [&](auto v) { launch_gather<decltype(v)>(a, push, grid, s); });
+  a.overflow_off = overflow_off;
+  dispatch_v(dtype, [&](auto v) { launch_gather<decltype(v)>(a, publish, push, grid, s); });
 }
 
 // =========================================================================================

@@ -30,7 +30,7 @@ struct GpuPlane::MapWork {
 
 namespace {
 
-__global__ void map_info_kernel(const unsigned long long* ocnt, int p, const unsigned long long* cursor_overflow,
+__global__ void map_info_kernel(const unsigned long long* ocnt, int p, unsigned long long* cursor_overflow,
                                 const unsigned long long* own_count, unsigned long long out_cap, int mode,
                                 unsigned long long* info) {
   if (threadIdx.x == 0 && blockIdx.x == 0) {
@@ -40,6 +40,7 @@ __global__ void map_info_kernel(const unsigned long long* ocnt, int p, const uns
       for (int q = 0; q < p; ++q) total += ocnt[q];
     info[0] = total < out_cap ? total : out_cap;
     info[1] = cursor_overflow ? *cursor_overflow : 0;
+    if (cursor_overflow) *cursor_overflow = 0;  // not sticky across calls
     info[2] = total > out_cap ? 1 : 0;
     info[3] = *own_count;
   }
@@ -185,20 +186,24 @@ void GpuPlane::map_collective(int mode, const long long* const* keys, const void
   // Owned counts are published into the peers' memory BEFORE the barrier of this call, i.e. possibly
   // while a slower peer still runs the info kernel of the previous call: alternate between two slots.
   const size_t ocnt_off = w.ocnt_off + (size_t)(w.calls++ & 1) * 128;
-  const int blocks = std::max(1, std::min(sms_ * 4, kMaxBlocks - 2));
   const PeerTable tab = table();
   const long long* own_k[kMaxRanks];
   const void* own_v[kMaxRanks];
   const unsigned long long* own_c[kMaxRanks];
 
+  unsigned long long* own_cw[kMaxRanks];
+  unsigned long long* info_dev[kMaxRanks];
+  for (int i = 0; i < L; ++i) {
+    own_cw[i] = w.local[i].own_count;
+    own_c[i] = w.local[i].own_count;
+    info_dev[i] = w.local[i].info_dev;
+    info_host[i] = w.local[i].info_host;
+  }
+  int ggrid = std::max(1, std::min(sms_ * 2, kMaxBlocks - 2));
+  if (emulated()) ggrid = std::max(1, sms_ / p);
   if (mode != 2) {
-    // 1. clear tables, 2. partition + push to owners, 3. merge, 4. compact
-    for (int i = 0; i < L; ++i) {
-      auto& l = w.local[i];
-      MapTable t{l.tkeys, l.tvals, l.tsize - 1};
-      map_launch_clear(dtype, op, t, blocks, s);
-      MP4J_CUDA(cudaMemsetAsync(l.own_count, 0, 8, s));
-    }
+    // launch 1: partition + push to owners (meets the peers); launch 2: clear + merge + compact + publish (meets
+    // the peers again: nobody starts the next call's pushes into a rank that is still merging)
     MapExchangeArgs ea{};
     ea.tab = tab;
     ea.partition = partition;
@@ -211,67 +216,56 @@ void GpuPlane::map_collective(int mode, const long long* const* keys, const void
       ea.keys[i] = keys[i];
       ea.vals[i] = vals[i];
       ea.n[i] = n[i];
-      const int r = emulated() ? i : rank();  // overflow flag of the previous call is not sticky
-      MP4J_CUDA(cudaMemsetAsync(heap_.base(r) + w.cursor_off + (size_t)p * 8, 0, 8, s));
     }
     int pgrid = (int)std::max<long long>(1, std::min<long long>((max_n + map_threads() - 1) / map_threads(), sms_ * 2));
     if (emulated()) pgrid = std::max(1, std::min(pgrid, sms_ * 2 / p));
     map_launch_partition(dtype, ea, pgrid, s);
+    MapTable tt[kMaxRanks];
+    long long* own_kw[kMaxRanks];
+    void* own_vw[kMaxRanks];
     for (int i = 0; i < L; ++i) {
       auto& l = w.local[i];
-      const int r = emulated() ? i : rank();
-      MapTable t{l.tkeys, l.tvals, l.tsize - 1};
-      map_launch_merge(dtype, op, tab, r, t, w.rkeys_off, w.rvals_off, w.rcnt_off, w.cap, blocks, s);
-      map_launch_compact(dtype, t, l.own_keys, l.own_vals, l.own_count, l.own_cap, blocks, s);
+      tt[i] = MapTable{l.tkeys, l.tvals, l.tsize - 1};
+      own_kw[i] = l.own_keys;
+      own_vw[i] = l.own_vals;
       own_k[i] = l.own_keys;
       own_v[i] = l.own_vals;
-      own_c[i] = l.own_count;
     }
+    map_launch_table(dtype, op, tab, tt, own_kw, own_vw, own_cw, L, w.local[0].own_cap, w.rkeys_off, w.rvals_off,
+                     w.rcnt_off, ocnt_off, w.cap, sms_, s);
   } else {
     for (int i = 0; i < L; ++i) {
-      auto& l = w.local[i];
-      map_set_count_kernel<<<1, 32, 0, s>>>(l.own_count, (unsigned long long)n[i]);
+      map_set_count_kernel<<<1, 32, 0, s>>>(w.local[i].own_count, (unsigned long long)n[i]);
       own_k[i] = keys[i];
       own_v[i] = vals[i];
-      own_c[i] = l.own_count;
     }
   }
-  int ggrid = std::max(1, std::min(sms_ * 2, kMaxBlocks - 2));
-  if (emulated()) ggrid = std::max(1, sms_ / p);
+  const unsigned long long overflow_off = w.cursor_off + (size_t)p * 8;
   if (mode == 1) {
-    // no allgather, but still meet the peers: nobody may start the next call's pushes into a rank
-    // that is still merging this call's receive regions
-    map_launch_gather(dtype, tab, ocnt_off, w.okeys_off, w.ovals_off, (unsigned long long)w.out_cap, own_k, own_v, own_c,
-                      L, false, ggrid, s);
     for (int i = 0; i < L; ++i) {
       auto& l = w.local[i];
       const int r = emulated() ? i : rank();
-      map_info_kernel<<<1, 32, 0, s>>>(nullptr, p, (const unsigned long long*)(heap_.base(r) + w.cursor_off) + p,
-                                       l.own_count, l.own_cap, mode, l.info_dev);
+      map_info_kernel<<<1, 32, 0, s>>>(nullptr, p, (unsigned long long*)(heap_.base(r) + overflow_off), l.own_count,
+                                       l.own_cap, mode, l.info_dev);
       out_keys[i] = l.own_keys;
       out_vals[i] = l.own_vals;
-      info_host[i] = l.info_host;
     }
     MP4J_CUDA(cudaGetLastError());
-    last_ = CollStat{"reduce_scatter_map", "partition+merge", (size_t)max_n * (8 + vs), blocks, false};
+    last_ = CollStat{"reduce_scatter_map", "partition+table", (size_t)max_n * (8 + vs), ggrid, false};
     return;
   }
-  // 5. publish owned counts, push owned pairs to every peer's output at the right offset
-  map_launch_gather(dtype, tab, ocnt_off, w.okeys_off, w.ovals_off, (unsigned long long)w.out_cap, own_k, own_v, own_c,
-                    L, true, ggrid, s);
+  // launch 3: push owned pairs to every peer's output at the right offset (the counts were published by launch 2;
+  // allgather-only calls publish them here) and write the info block
+  map_launch_gather(dtype, tab, ocnt_off, w.okeys_off, w.ovals_off, (unsigned long long)out_cap, own_k, own_v, own_c,
+                    info_dev, mode == 0 ? overflow_off : 0, L, mode == 2, true, ggrid, s);
   for (int i = 0; i < L; ++i) {
-    auto& l = w.local[i];
     const int r = emulated() ? i : rank();
-    map_info_kernel<<<1, 32, 0, s>>>((const unsigned long long*)(heap_.base(r) + ocnt_off), p,
-                                     mode == 0 ? (const unsigned long long*)(heap_.base(r) + w.cursor_off) + p : nullptr,
-                                     l.own_count, (unsigned long long)out_cap, mode, l.info_dev);
     out_keys[i] = (long long*)(heap_.base(r) + w.okeys_off);
     out_vals[i] = heap_.base(r) + w.ovals_off;
-    info_host[i] = l.info_host;
   }
   MP4J_CUDA(cudaGetLastError());
-  last_ = CollStat{mode == 0 ? "allreduce_map" : "allgather_map", mode == 0 ? "partition+merge+gather" : "gather",
-                   (size_t)max_n * (8 + vs), blocks, false};
+  last_ = CollStat{mode == 0 ? "allreduce_map" : "allgather_map", mode == 0 ? "partition+table+gather" : "gather",
+                   (size_t)max_n * (8 + vs), ggrid, false};
 }
 
 }  // namespace mp4j

@@ -284,7 +284,8 @@ def models_worker(comm):
         wtrue = torch.randn(Fs, generator=torch.Generator().manual_seed(5))
         y = (torch.zeros(n).index_add_(0, rws, vals * wtrue[cols]) > 0).float()
         data.append((rws, cols, vals, y))
-    sm = SparseLR(comm, Fs, lr=0.5)
+    # odd ranks tell the model its sizes up front? no: the sizes must agree, so all ranks do, every other test run
+    sm = SparseLR(comm, Fs, lr=0.5, max_nnz=n * nnz_row, rows_total=n * p) if p % 2 == 0 else SparseLR(comm, Fs, lr=0.5)
     rws, cols, vals, y = (t.cuda() for t in data[r])
     s_ours = []
     for _ in range(steps):

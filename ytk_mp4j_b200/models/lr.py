@@ -74,10 +74,14 @@ class SparseLR:
     n_features weights, so it travels as a sparse map (keys = feature ids) through allreduce_map
     (the GPU form of the reference's allreduceMap, PCS:2053)."""
 
-    def __init__(self, comm, n_features, lr=0.1):
+    def __init__(self, comm, n_features, lr=0.1, max_nnz=None, rows_total=None):
+        """max_nnz: an upper bound of the non-zeros of any rank's minibatch; rows_total: rows of a minibatch over all
+        ranks. Both must be the same on every rank. When given, a step involves no host communication (the map
+        collective gets its sizes from them); when not, they are agreed through host allreduces every step."""
         self.comm, self.lr, self.F = comm, lr, n_features
         self.plane = comm.init_gpu()
         self.w = torch.zeros(n_features, device="cuda")
+        self.max_nnz, self.rows_total = max_nnz, rows_total
 
     def step(self, rows, cols, vals, y):
         """COO minibatch: rows/cols int64, vals float32, y float32 in {0,1} of length n_rows."""
@@ -86,7 +90,13 @@ class SparseLR:
         r = torch.sigmoid(z) - y
         g_vals = vals * r[rows]
         keys, g = self.plane.map_reduce_local(cols, g_vals, N.SUM)       # local pre-aggregation by feature
-        keys, g = self.plane.allreduce_map(keys, g, Operators.Float.SUM)  # sparse allreduce over ranks
-        n_total = self.comm.allreduce(n, Operands.LONG_OPERAND(), Operators.Long.SUM)
+        if self.max_nnz is not None:                                     # sparse allreduce over ranks
+            cap = min(self.max_nnz * self.comm.getSlaveNum(), self.F)
+            keys, g = self.plane.allreduce_map(keys, g, Operators.Float.SUM, max_n=self.max_nnz, out_cap=cap,
+                                               copy=False)
+        else:
+            keys, g = self.plane.allreduce_map(keys, g, Operators.Float.SUM, copy=False)
+        n_total = self.rows_total if self.rows_total is not None else \
+            self.comm.allreduce(n, Operands.LONG_OPERAND(), Operators.Long.SUM)
         self.w.index_add_(0, keys, g, alpha=-self.lr / n_total)
         return torch.nn.functional.binary_cross_entropy_with_logits(z, y, reduction="sum")

@@ -456,22 +456,31 @@ class GpuPlane(_PlaneBase):
         return shards[0], fpr
 
     # --- sparse maps on (int64 keys, values) tensors
-    def _map_sizes(self, n, out_cap):
+    def _map_sizes(self, n, out_cap, max_n=None):
+        """The kernels need two numbers that are the same on every rank: the largest input size and the capacity
+        of the result. A caller that knows them (an iterative job with a fixed minibatch) passes them and the call
+        involves no host communication at all; otherwise they are agreed through two host allreduces."""
         from ..operands import Operands
         from ..operators import Operators
         lop = Operands.LONG_OPERAND()
-        max_n = self._comm.allreduce(int(n), lop, Operators.Long.MAX)
+        if max_n is None:
+            max_n = self._comm.allreduce(int(n), lop, Operators.Long.MAX)
+        elif n > max_n:
+            raise Mp4jException("map collective: this rank has %d pairs, more than max_n = %d" % (n, max_n))
         if out_cap is None:
             out_cap = max(1, self._comm.allreduce(int(n), lop, Operators.Long.SUM))
-        return max_n, out_cap
+        return int(max_n), int(out_cap)
 
-    def allreduce_map(self, keys, vals, operator, out_cap=None, partition="mix", stream=None):
+    def allreduce_map(self, keys, vals, operator, out_cap=None, partition="mix", stream=None, max_n=None, copy=True):
         """allreduceMap on tensors (PCS:2053): every rank gets the merged (keys, values); entries
         with equal keys are reduced with `operator` (SUM/MAX/MIN). Order of the result is
-        unspecified (like a HashMap's). out_cap defaults to the sum of all ranks' sizes."""
-        max_n, out_cap = self._map_sizes(keys.numel(), out_cap)
+        unspecified (like a HashMap's). out_cap defaults to the sum of all ranks' sizes.
+        max_n (largest input size over all ranks) and out_cap, when both given, must be the same on every rank and
+        spare the call its two host allreduces; copy=False returns views of plane memory that stay valid until the
+        next map collective instead of clones."""
+        max_n, out_cap = self._map_sizes(keys.numel(), out_cap, max_n)
         k, v, _ = self._map_collective("allreduce", [keys], [vals], max_n, out_cap, _native_op(operator), partition,
-                                       stream)[0]
+                                       stream, clone=copy)[0]
         return k, v
 
     def reduce_scatter_map(self, keys, vals, operator, partition="mix", stream=None):
