@@ -39,6 +39,7 @@ void GpuOptions::load_env() {
   rs_nvls_max_bytes = env_size("MP4J_RS_NVLS_MAX_BYTES", rs_nvls_max_bytes);
   ag_nvls_max_bytes = env_size("MP4J_AG_NVLS_MAX_BYTES", ag_nvls_max_bytes);
   nvls64_max_bytes = env_size("MP4J_NVLS64_MAX_BYTES", nvls64_max_bytes);
+  map_nvls = (int)env_size("MP4J_MAP_NVLS", (size_t)map_nvls);
   max_blocks = (int)env_size("MP4J_MAX_BLOCKS", (size_t)max_blocks);
   nvls_min_world = (int)env_size("MP4J_NVLS_MIN_WORLD", (size_t)nvls_min_world);
   poll_ns = (int)env_size("MP4J_POLL_NS", (size_t)poll_ns);
@@ -68,6 +69,7 @@ bool GpuPlane::set_option(const std::string& name, long long v) {
   else if (name == "rs_nvls_max_bytes") opt_.rs_nvls_max_bytes = (size_t)v;
   else if (name == "ag_nvls_max_bytes") opt_.ag_nvls_max_bytes = (size_t)v;
   else if (name == "nvls64_max_bytes") opt_.nvls64_max_bytes = (size_t)v;
+  else if (name == "map_nvls") opt_.map_nvls = (int)v;
   else if (name == "oneshot_max_bytes") opt_.oneshot_max_bytes = std::min((size_t)v, oneshot_slot_bytes_);
   else if (name == "max_blocks") opt_.max_blocks = (int)v;
   else if (name == "poll_ns") opt_.poll_ns = (int)v;

@@ -42,6 +42,7 @@ struct GpuOptions {
   // beyond this size the in-switch path is request-bound and two-shot P2P wins (8 GPUs, 1 GiB double: 545 vs
   // ~650 GB/s; NCCL 711). AUTO only. MP4J_NVLS64_MAX_BYTES
   size_t nvls64_max_bytes = 16ull << 20;
+  int map_nvls = 1;  // map collectives: push the result through the multicast mapping (multimem.st) when there is one
   int nvls_min_world = 2;               // AUTO uses NVLS only when world > this (MP4J_NVLS_MIN_WORLD)
   bool want_multicast = true;           // MP4J_NVLS=0 disables
   int max_blocks = 0;                   // 0 = occupancy-derived (MP4J_MAX_BLOCKS)

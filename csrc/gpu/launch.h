@@ -56,7 +56,7 @@ void map_launch_gather(int dtype, const PeerTable& tab, unsigned long long ocnt_
                        unsigned long long ovals_off, unsigned long long out_cap, const long long* const* own_keys,
                        const void* const* own_vals, const unsigned long long* const* own_count,
                        unsigned long long* const* info, unsigned long long overflow_off, int nlocal, bool publish,
-                       bool push, int grid, cudaStream_t s);
+                       bool push, bool use_mc, int grid, cudaStream_t s);
 // clear + merge + compact + publish of a map collective in one cooperative kernel (t etc.: one entry per local rank)
 void map_launch_table(int dtype, int op, const PeerTable& tab, const MapTable* t, long long* const* own_keys,
                       void* const* own_vals, unsigned long long* const* own_count, int nlocal,

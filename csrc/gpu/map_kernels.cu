@@ -354,6 +354,7 @@ struct MapGatherArgs {
   // output overflow, pairs this rank owned. Written by block 0 of the push kernel when info[row] is set.
   unsigned long long* info[kMaxRanks];
   unsigned long long overflow_off;  // heap: receive-overflow flag of the partition step (0 = none in this mode)
+  int use_mc;                       // push through the multicast mapping when the plane has one
 };
 
 __global__ void __launch_bounds__(kMapThreads) map_publish_count_kernel(const __grid_constant__ MapGatherArgs a) {
@@ -364,6 +365,36 @@ __global__ void __launch_bounds__(kMapThreads) map_publish_count_kernel(const __
     *((volatile unsigned long long*)(tab.heap[threadIdx.x] + a.ocnt_off) + rank) = *a.own_count[row];
   __syncthreads();
   ctrl_barrier_peers(tab, rank);
+}
+
+// src[0, n) -> element offset `off` of the array at heap offset `base_off` of EVERY rank
+template <typename E>
+__device__ __forceinline__ void mc_broadcast(const PeerTable& tab, unsigned long long base_off, unsigned long long off,
+                                             const E* src, unsigned long long n, unsigned long long tid,
+                                             unsigned long long nthr) {
+  constexpr unsigned long long kPer = 16 / sizeof(E);
+  const unsigned long long head = min(n, (kPer - (off % kPer)) % kPer);  // elements before the first aligned vector
+  const unsigned long long nvec = (n - head) / kPer;
+  const unsigned long long tail0 = head + nvec * kPer;
+  for (unsigned long long v = tid; v < nvec; v += nthr) {
+    const E* s = src + head + v * kPer;
+    Vec16 x;
+    if constexpr (sizeof(E) == 8) {
+      const unsigned long long a0 = ((const unsigned long long*)s)[0], a1 = ((const unsigned long long*)s)[1];
+      x.x = (uint32_t)a0, x.y = (uint32_t)(a0 >> 32), x.z = (uint32_t)a1, x.w = (uint32_t)(a1 >> 32);
+    } else {
+      const uint32_t* u = (const uint32_t*)s;
+      x.x = u[0], x.y = u[1], x.z = u[2], x.w = u[3];
+    }
+    multimem_st(tab.mc_heap + base_off + (off + head + v * kPer) * sizeof(E), x);
+  }
+  // ragged ends: at most 2 * (kPer - 1) elements
+  const unsigned long long nrag = head + (n - tail0);
+  for (unsigned long long j = tid; j < nrag; j += nthr) {
+    const unsigned long long i = j < head ? j : tail0 + (j - head);
+    const E e = src[i];
+    for (int q = 0; q < tab.world; ++q) ((E*)(tab.heap[q] + base_off))[off + i] = e;
+  }
 }
 
 template <typename V>
@@ -394,14 +425,23 @@ __global__ void __launch_bounds__(kMapThreads) map_allgather_push_kernel(const _
     info[2] = total > a.out_cap ? 1 : 0;
     info[3] = *a.own_count[row];
   }
-  for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < mine;
-       i += (unsigned long long)gridDim.x * blockDim.x) {
-    if (off + i >= a.out_cap) break;
-    const long long k = sk[i];
-    const V v = sv[i];
-    for (int q = 0; q < p; ++q) {
-      ((long long*)(tab.heap[q] + a.okeys_off))[off + i] = k;
-      ((V*)(tab.heap[q] + a.ovals_off))[off + i] = v;
+  const unsigned long long tid = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const unsigned long long nthr = (unsigned long long)gridDim.x * blockDim.x;
+  const unsigned long long end = off + mine < a.out_cap ? mine : (off < a.out_cap ? a.out_cap - off : 0);  // pairs to push
+  if (tab.mc_heap && a.use_mc) {
+    // NVLS: one multimem.st of 16 bytes lands in every rank's output (the switch replicates it), so this rank
+    // sends its owned pairs once instead of p times. 16-byte stores need a 16-byte aligned destination: the
+    // few elements before the first aligned one and after the last full vector go out as per-peer stores.
+    mc_broadcast<long long>(tab, a.okeys_off, off, sk, end, tid, nthr);
+    mc_broadcast<V>(tab, a.ovals_off, off, sv, end, tid, nthr);
+  } else {
+    for (unsigned long long i = tid; i < end; i += nthr) {
+      const long long k = sk[i];
+      const V v = sv[i];
+      for (int q = 0; q < p; ++q) {
+        ((long long*)(tab.heap[q] + a.okeys_off))[off + i] = k;
+        ((V*)(tab.heap[q] + a.ovals_off))[off + i] = v;
+      }
     }
   }
   if (!block_barrier_peers(tab, rank, ep)) return;  // all pushes landed everywhere before anyone reads its output
@@ -543,7 +583,7 @@ void map_launch_gather(int dtype, const PeerTable& tab, unsigned long long ocnt_
                        unsigned long long ovals_off, unsigned long long out_cap, const long long* const* own_keys,
                        const void* const* own_vals, const unsigned long long* const* own_count,
                        unsigned long long* const* info, unsigned long long overflow_off, int nlocal, bool publish,
-                       bool push, int grid, cudaStream_t s) {
+                       bool push, bool use_mc, int grid, cudaStream_t s) {
   MapGatherArgs a{};
   a.tab = tab;
   a.ocnt_off = ocnt_off;
@@ -557,6 +597,7 @@ void map_launch_gather(int dtype, const PeerTable& tab, unsigned long long ocnt_
     a.info[i] = info ? info[i] : nullptr;
   }
   a.overflow_off = overflow_off;
+  a.use_mc = use_mc ? 1 : 0;
   dispatch_v(dtype, [&](auto v) { launch_gather<decltype(v)>(a, publish, push, grid, s); });
 }
 

@@ -254,10 +254,12 @@ void GpuPlane::map_collective(int mode, const long long* const* keys, const void
     last_ = CollStat{"reduce_scatter_map", "partition+table", (size_t)max_n * (8 + vs), ggrid, false};
     return;
   }
+  // map_nvls: 1 = multicast push when AUTO would use NVLS for a dense collective (world > nvls_min_world), 2 = always
+  const bool use_mc = opt_.map_nvls >= 2 || (opt_.map_nvls == 1 && p > opt_.nvls_min_world);
   // launch 3: push owned pairs to every peer's output at the right offset (the counts were published by launch 2;
   // allgather-only calls publish them here) and write the info block
   map_launch_gather(dtype, tab, ocnt_off, w.okeys_off, w.ovals_off, (unsigned long long)out_cap, own_k, own_v, own_c,
-                    info_dev, mode == 0 ? overflow_off : 0, L, mode == 2, true, ggrid, s);
+                    info_dev, mode == 0 ? overflow_off : 0, L, mode == 2, true, use_mc, ggrid, s);
   for (int i = 0; i < L; ++i) {
     const int r = emulated() ? i : rank();
     out_keys[i] = (long long*)(heap_.base(r) + w.okeys_off);

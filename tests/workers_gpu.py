@@ -93,6 +93,18 @@ def process_gpu(comm):
     k, v = comm.gpu.allgather_map(torch.full((3,), r, dtype=torch.int64, device="cuda"),
                                   torch.full((3,), float(r), device="cuda"))
     assert k.tolist() == [q for q in range(p) for _ in range(3)]
+    # the same results when the gather step goes through the multicast mapping (one multimem.st lands in every
+    # rank's output; default only beyond 2 ranks): unaligned offsets (3 and big + odd counts), 4- and 8-byte values
+    comm.gpu.set_option("map_nvls", 2)
+    for dt in (torch.float32, torch.float64):
+        k, v = comm.gpu.allreduce_map(sets[r].to(torch.int64).cuda(), torch.ones(big, device="cuda", dtype=dt),
+                                      Operators.Float.SUM if dt == torch.float32 else Operators.Double.SUM)
+        assert k.numel() == int((cnt > 0).sum()), (k.numel(), int((cnt > 0).sum()))
+        assert torch.equal(v.cpu().float(), cnt[k.cpu()])
+        k, v = comm.gpu.allgather_map(torch.full((3 + r,), r, dtype=torch.int64, device="cuda"),
+                                      torch.full((3 + r,), float(r), device="cuda", dtype=dt))
+        assert k.tolist() == [q for q in range(p) for _ in range(3 + q)] and v.tolist() == [float(x) for x in k.tolist()]
+    comm.gpu.set_option("map_nvls", 1)
     # ---- Map<String, number> through the PUBLIC API with the GPU plane up: String keys are bridged to 64-bit
     # keys (comm/map_bridge.py), values reduce on the GPU, result comes back as a dict (PCS:2053, 1299, 666)
     objn = 3000

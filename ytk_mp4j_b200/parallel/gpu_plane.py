@@ -459,16 +459,20 @@ class GpuPlane(_PlaneBase):
     def _map_sizes(self, n, out_cap, max_n=None):
         """The kernels need two numbers that are the same on every rank: the largest input size and the capacity
         of the result. A caller that knows them (an iterative job with a fixed minibatch) passes them and the call
-        involves no host communication at all; otherwise they are agreed through two host allreduces."""
-        from ..operands import Operands
-        from ..operators import Operators
-        lop = Operands.LONG_OPERAND()
-        if max_n is None:
-            max_n = self._comm.allreduce(int(n), lop, Operators.Long.MAX)
-        elif n > max_n:
+        involves no host communication at all; otherwise they come from ONE host allgather of the sizes."""
+        if max_n is not None and n > max_n:
             raise Mp4jException("map collective: this rank has %d pairs, more than max_n = %d" % (n, max_n))
-        if out_cap is None:
-            out_cap = max(1, self._comm.allreduce(int(n), lop, Operators.Long.SUM))
+        if max_n is None or out_cap is None:
+            from ..operands import Operands
+            p, r = self._comm.getSlaveNum(), self._comm.getRank()
+            sizes = np.zeros(p, dtype=np.int64)
+            sizes[r] = int(n)
+            if p > 1:
+                self._comm.allgatherArray(sizes, Operands.LONG_OPERAND(), list(range(p)), list(range(1, p + 1)))
+            if max_n is None:
+                max_n = int(sizes.max())
+            if out_cap is None:
+                out_cap = max(1, int(sizes.sum()))
         return int(max_n), int(out_cap)
 
     def allreduce_map(self, keys, vals, operator, out_cap=None, partition="mix", stream=None, max_n=None, copy=True):
@@ -476,7 +480,7 @@ class GpuPlane(_PlaneBase):
         with equal keys are reduced with `operator` (SUM/MAX/MIN). Order of the result is
         unspecified (like a HashMap's). out_cap defaults to the sum of all ranks' sizes.
         max_n (largest input size over all ranks) and out_cap, when both given, must be the same on every rank and
-        spare the call its two host allreduces; copy=False returns views of plane memory that stay valid until the
+        spare the call its host allgather of the sizes; copy=False returns views of plane memory that stay valid until the
         next map collective instead of clones."""
         max_n, out_cap = self._map_sizes(keys.numel(), out_cap, max_n)
         k, v, _ = self._map_collective("allreduce", [keys], [vals], max_n, out_cap, _native_op(operator), partition,
