@@ -202,6 +202,7 @@ public class ProcessCommSlave {
     /** rank i's [sendfroms[i], sendtos[i]) lands at the same offsets of root's array (PCS:535) */
     public synchronized <T> T gatherArray(T arrData, Operand operand, int[] sendfroms, int[] sendtos, int rootRank) throws Mp4jException {
         CommUtils.isfromsTosLegal(sendfroms, sendtos);
+        CommUtils.isRangeInArray(arrData, CommUtils.maxEnd(sendtos));
         checkRoot(rootRank);
         if (slaveNum == 1) return arrData;
         if (nativePath(operand, null) && isNativeArray(arrData)) {
@@ -218,6 +219,7 @@ public class ProcessCommSlave {
     /** every rank ends with all p segments (PCS:620) */
     public synchronized <T> T allgatherArray(T arrData, Operand operand, int[] froms, int[] tos) throws Mp4jException {
         CommUtils.isfromsTosLegal(froms, tos);
+        CommUtils.isRangeInArray(arrData, CommUtils.maxEnd(tos));
         if (slaveNum == 1) return arrData;
         if (nativePath(operand, null) && isNativeArray(arrData)) {
             check(Native.hostAllgather(handle, arrData, operand.dtype, toLong(froms), toLong(tos)));
@@ -231,6 +233,7 @@ public class ProcessCommSlave {
     /** root's [from, to) to everybody = scatter of p balanced chunks + allgather (PCS:750-770) */
     public synchronized <T> T broadcastArray(T arrData, Operand operand, int from, int to, int rootRank) throws Mp4jException {
         CommUtils.isFromToLegal(from, to);
+        CommUtils.isRangeInArray(arrData, to);
         checkRoot(rootRank);
         if (slaveNum == 1) return arrData;
         if (nativePath(operand, null) && isNativeArray(arrData)) {
@@ -245,6 +248,7 @@ public class ProcessCommSlave {
     /** rank i receives root's [recvfroms[i], recvtos[i]) at the same offsets (PCS:900) */
     public synchronized <T> T scatterArray(T arrData, Operand operand, int[] recvfroms, int[] recvtos, int rootRank) throws Mp4jException {
         CommUtils.isfromsTosLegal(recvfroms, recvtos);
+        CommUtils.isRangeInArray(arrData, CommUtils.maxEnd(recvtos));
         checkRoot(rootRank);
         if (slaveNum == 1) return arrData;
         if (nativePath(operand, null) && isNativeArray(arrData)) {
@@ -264,6 +268,7 @@ public class ProcessCommSlave {
     /** rank r ends with the fully reduced [from + sum(counts[&lt;r]), + counts[r]) (PCS:1174) */
     public synchronized <T> T reduceScatterArray(T arrData, Operand operand, IOperator operator, int from, int[] counts) throws Mp4jException {
         CommUtils.isFromCountsLegal(from, counts);
+        CommUtils.isRangeInArray(arrData, CommUtils.endOfCounts(from, counts));
         if (slaveNum == 1) return arrData;
         if (nativePath(operand, operator) && isNativeArray(arrData)) {
             check(Native.hostReduceScatter(handle, arrData, operand.dtype, operator.nativeCode(), from, toLong(counts)));
@@ -279,6 +284,7 @@ public class ProcessCommSlave {
     /** = reduce-scatter + gather (PCS:1390-1416) */
     public synchronized <T> T reduceArray(T arrData, Operand operand, IOperator operator, int from, int to, int rootRank) throws Mp4jException {
         CommUtils.isFromToLegal(from, to);
+        CommUtils.isRangeInArray(arrData, to);
         checkRoot(rootRank);
         if (slaveNum == 1) return arrData;
         if (nativePath(operand, operator) && isNativeArray(arrData)) {
@@ -293,6 +299,7 @@ public class ProcessCommSlave {
     /** = reduce-scatter + allgather (PCS:1733-1763) */
     public synchronized <T> T allreduceArray(T arrData, Operand operand, IOperator operator, int from, int to) throws Mp4jException {
         CommUtils.isFromToLegal(from, to);
+        CommUtils.isRangeInArray(arrData, to);
         if (slaveNum == 1) return arrData;
         if (nativePath(operand, operator) && isNativeArray(arrData)) {
             check(Native.hostAllreduce(handle, arrData, operand.dtype, operator.nativeCode(), from, to));

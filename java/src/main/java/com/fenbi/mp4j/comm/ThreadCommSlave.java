@@ -150,6 +150,7 @@ public class ThreadCommSlave {
         final int[] pf = CommUtils.getProcessFroms(sendfroms), pt = CommUtils.getProcessTos(sendtos);
         if (threadNum == 1) return process.gatherArray(arrData, operand, pf, pt, rootRank);
         CommUtils.isfromsTosLegal(sendfroms, sendtos, threadNum);
+        CommUtils.isRangeInArray(arrData, CommUtils.maxEnd(sendtos));
         final int rr = realRoot(rootRank, rootThreadId), r = getRank();
         delegate(arrData, rr, new Body() {
             @Override public Object run(Object[] arrs) throws Mp4jException {
@@ -166,6 +167,7 @@ public class ThreadCommSlave {
         final int[] pf = CommUtils.getProcessFroms(froms), pt = CommUtils.getProcessTos(tos);
         if (threadNum == 1) return process.allgatherArray(arrData, operand, pf, pt);
         CommUtils.isfromsTosLegal(froms, tos, threadNum);
+        CommUtils.isRangeInArray(arrData, CommUtils.maxEnd(tos));
         final int r = getRank();
         delegate(arrData, 0, new Body() {
             @Override public Object run(Object[] arrs) throws Mp4jException {
@@ -183,6 +185,7 @@ public class ThreadCommSlave {
                                 int rootThreadId) throws Mp4jException {
         if (threadNum == 1) return process.broadcastArray(arrData, operand, from, to, rootRank);
         CommUtils.isFromToLegal(from, to);
+        CommUtils.isRangeInArray(arrData, to);
         final int rr = realRoot(rootRank, rootThreadId);
         delegate(arrData, rr, new Body() {
             @Override public Object run(Object[] arrs) throws Mp4jException {
@@ -200,6 +203,7 @@ public class ThreadCommSlave {
         final int[] pf = CommUtils.getProcessFroms(recvfroms), pt = CommUtils.getProcessTos(recvtos);
         if (threadNum == 1) return process.scatterArray(arrData, operand, pf, pt, rootRank);
         CommUtils.isfromsTosLegal(recvfroms, recvtos, threadNum);
+        CommUtils.isRangeInArray(arrData, CommUtils.maxEnd(recvtos));
         final int rr = realRoot(rootRank, rootThreadId), r = getRank();
         delegate(arrData, rr, new Body() {
             @Override public Object run(Object[] arrs) throws Mp4jException {
@@ -216,6 +220,7 @@ public class ThreadCommSlave {
                                     final int[][] counts) throws Mp4jException {
         if (threadNum == 1) return process.reduceScatterArray(arrData, operand, operator, from, firstColumn(counts));
         CommUtils.isFromCountsLegal(from, counts);
+        CommUtils.isRangeInArray(arrData, CommUtils.endOfCounts(from, counts));
         final int r = getRank();
         final int[] pcounts = rowSums(counts);
         int total = 0;
@@ -242,6 +247,7 @@ public class ThreadCommSlave {
                              final int rootRank, int rootThreadId) throws Mp4jException {
         if (threadNum == 1) return process.reduceArray(arrData, operand, operator, from, to, rootRank);
         CommUtils.isFromToLegal(from, to);
+        CommUtils.isRangeInArray(arrData, to);
         final int rr = realRoot(rootRank, rootThreadId);
         delegate(arrData, rr, new Body() {
             @Override public Object run(Object[] arrs) throws Mp4jException {
@@ -257,6 +263,7 @@ public class ThreadCommSlave {
     public <T> T allreduceArray(final T arrData, final Operand operand, final IOperator operator, final int from, final int to) throws Mp4jException {
         if (threadNum == 1) return process.allreduceArray(arrData, operand, operator, from, to);
         CommUtils.isFromToLegal(from, to);
+        CommUtils.isRangeInArray(arrData, to);
         delegate(arrData, 0, new Body() {
             @Override public Object run(Object[] arrs) throws Mp4jException {
                 localReduce(arrs, operator, from, to, 0);

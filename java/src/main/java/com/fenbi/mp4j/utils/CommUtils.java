@@ -47,6 +47,39 @@ public final class CommUtils {
         if (from > to) throw new Mp4jException("from must be <= to!");
     }
 
+    /** The ranges of a collective must lie inside the array that is handed to native code: the reference gets an
+     *  ArrayIndexOutOfBoundsException from the JVM there, a native memcpy would read past the buffer.
+     *  `hi` is the largest exclusive end index the call touches. */
+    public static void isRangeInArray(Object arr, long hi) throws Mp4jException {
+        if (arr == null || !arr.getClass().isArray()) return;
+        int len = java.lang.reflect.Array.getLength(arr);
+        if (hi > len) throw new Mp4jException("range end " + hi + " is beyond the array length " + len);
+    }
+
+    public static long maxEnd(int[] tos) {
+        long m = 0;
+        for (int t : tos) m = Math.max(m, t);
+        return m;
+    }
+
+    public static long maxEnd(int[][] tos) {
+        long m = 0;
+        for (int[] row : tos) m = Math.max(m, maxEnd(row));
+        return m;
+    }
+
+    public static long endOfCounts(int from, int[] counts) {
+        long e = from;
+        for (int c : counts) e += c;
+        return e;
+    }
+
+    public static long endOfCounts(int from, int[][] counts) {
+        long e = from;
+        for (int[] row : counts) for (int c : row) e += c;
+        return e;
+    }
+
     public static int[] getFromsFromCount(int from, int[] counts, int slaveNum) {
         int[] froms = new int[slaveNum];
         for (int i = 0; i < slaveNum; i++) {
