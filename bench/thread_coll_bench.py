@@ -20,6 +20,7 @@ def main():
     ap.add_argument("--threads", type=int, default=8)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--out", default="")
+    ap.add_argument("--only", default="", help="comma-separated subset of the collectives")
     args = ap.parse_args()
     import torch
     from ytk_mp4j_b200 import CommMaster, Operands, Operators, ThreadCommSlave
@@ -62,7 +63,10 @@ def main():
            "allgather": S / world + T * S, "gather": S / world + S / world, "scatter": S / world + S / world,
            "broadcast": S / world + T * S}
     rows = []
+    only = [x for x in args.only.split(",") if x]
     for name, fn in cases.items():
+        if only and name not in only:
+            continue
         for _ in range(3):
             fn()
         torch.cuda.synchronize()

@@ -40,6 +40,8 @@ void GpuOptions::load_env() {
   ag_nvls_max_bytes = env_size("MP4J_AG_NVLS_MAX_BYTES", ag_nvls_max_bytes);
   nvls64_max_bytes = env_size("MP4J_NVLS64_MAX_BYTES", nvls64_max_bytes);
   map_nvls = (int)env_size("MP4J_MAP_NVLS", (size_t)map_nvls);
+  seg_relay = (int)env_size("MP4J_SEG_RELAY", (size_t)seg_relay);
+  seg_relay_min_bytes = env_size("MP4J_SEG_RELAY_MIN_BYTES", seg_relay_min_bytes);
   max_blocks = (int)env_size("MP4J_MAX_BLOCKS", (size_t)max_blocks);
   nvls_min_world = (int)env_size("MP4J_NVLS_MIN_WORLD", (size_t)nvls_min_world);
   poll_ns = (int)env_size("MP4J_POLL_NS", (size_t)poll_ns);
@@ -70,6 +72,8 @@ bool GpuPlane::set_option(const std::string& name, long long v) {
   else if (name == "ag_nvls_max_bytes") opt_.ag_nvls_max_bytes = (size_t)v;
   else if (name == "nvls64_max_bytes") opt_.nvls64_max_bytes = (size_t)v;
   else if (name == "map_nvls") opt_.map_nvls = (int)v;
+  else if (name == "seg_relay") opt_.seg_relay = (int)v;
+  else if (name == "seg_relay_min_bytes") opt_.seg_relay_min_bytes = (size_t)v;
   else if (name == "oneshot_max_bytes") opt_.oneshot_max_bytes = std::min((size_t)v, oneshot_slot_bytes_);
   else if (name == "max_blocks") opt_.max_blocks = (int)v;
   else if (name == "poll_ns") opt_.poll_ns = (int)v;

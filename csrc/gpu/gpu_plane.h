@@ -42,6 +42,8 @@ struct GpuOptions {
   // beyond this size the in-switch path is request-bound and two-shot P2P wins (8 GPUs, 1 GiB double: 545 vs
   // ~650 GB/s; NCCL 711). AUTO only. MP4J_NVLS64_MAX_BYTES
   size_t nvls64_max_bytes = 16ull << 20;
+  int seg_relay = 1;  // rooted thread collectives (broadcast, reduce) beyond 2 ranks: two launches through all ports
+  size_t seg_relay_min_bytes = 4ull << 20;
   int map_nvls = 1;  // map collectives: push the result through the multicast mapping (multimem.st) when there is one
   int nvls_min_world = 2;               // AUTO uses NVLS only when world > this (MP4J_NVLS_MIN_WORLD)
   bool want_multicast = true;           // MP4J_NVLS=0 disables
@@ -198,6 +200,7 @@ class GpuPlane {
   std::map<size_t, size_t> used_;  // off -> bytes
   CollStat last_;
   bool poisoned_ = false;  // a kernel hit the peer-wait watchdog
+  bool in_relay_ = false;  // thread_segments is running one of the two launches of a relay
   int dead_rank_p1_ = 0;   // test hook, see GrsArgs::dead_rank_p1
   void entry_check();      // start of every collective: surfaces a timeout of an earlier (asynchronous) one
   std::string last_algo_store_;  // backing store when last_.algo is composed at run time

@@ -30,6 +30,7 @@
 #include <stdlib.h>
 
 #include <algorithm>
+#include <vector>
 
 #include "../core/partition.h"
 #include "cuda_check.h"
@@ -446,6 +447,49 @@ void GpuPlane::thread_segments(void* const* bufs, int T, int dtype, int op, cons
   if (es == 0) throw Error("unknown dtype");
   const int p = world();
   const int L = local_ranks();
+  // Relay for the two collectives with ONE root (broadcastArray, reduceArray). As a single launch everybody pulls
+  // from the root's slots (broadcast) or the root pulls from everybody's (reduce): (p - 1) x the array through one
+  // NVLink port. Two launches move (p - 1) / p of the array through every port instead: scatter + allgather for a
+  // broadcast, reduce-scatter + gather for a reduce (the decomposition the reference uses at process level,
+  // PCS:750-770 and 1390-1416). Piece q rests in thread 0 of rank q between the launches (in the root thread on the
+  // root rank); a destination rank writes its own buffers, so stream order is all the two launches need.
+  if (opt_.seg_relay && nseg == 1 && p > 2 && !in_relay_) {
+    const int64_t* g = segs;
+    const bool bcast = g[2] != kAll && g[3] != kAll && g[4] == kAll && g[5] == kAll;
+    const bool red = g[2] == kAll && g[3] == kAll && g[4] != kAll && g[5] != kAll;
+    const int64_t len = g[1] - g[0];
+    if ((bcast || red) && g[0] >= 0 && len > 0 && (size_t)len * es >= opt_.seg_relay_min_bytes) {
+      const int64_t we = (int64_t)(std::max<size_t>(opt_.thread_slot_bytes, 64 << 10) / 16 * 16 / es);
+      const int64_t per = ((len + p - 1) / p + we - 1) / we * we;  // whole windows per piece
+      const int r0 = (int)(bcast ? g[2] : g[4]), t0 = (int)(bcast ? g[3] : g[5]);
+      if (r0 < 0 || r0 >= p || t0 < 0 || t0 >= T) throw Error("segment endpoint out of range");
+      std::vector<int64_t> s1, s2;
+      for (int q = 0; q < p; ++q) {
+        const int64_t lo = std::min<int64_t>(g[0] + q * per, g[1]), hi = std::min<int64_t>(lo + per, g[1]);
+        if (hi <= lo) continue;
+        const int64_t hold = q == r0 ? t0 : 0;
+        if (bcast) {
+          if (q != r0) s1.insert(s1.end(), {lo, hi, r0, t0, q, 0});
+          s2.insert(s2.end(), {lo, hi, q, hold, kAll, kAll});
+        } else {
+          s1.insert(s1.end(), {lo, hi, kAll, kAll, q, hold});
+          if (q != r0) s2.insert(s2.end(), {lo, hi, q, 0, r0, t0});
+        }
+      }
+      in_relay_ = true;
+      try {
+        thread_segments(bufs, T, dtype, op, s1.data(), (int)(s1.size() / 6), name, s);
+        thread_segments(bufs, T, dtype, op, s2.data(), (int)(s2.size() / 6), name, s);
+      } catch (...) {
+        in_relay_ = false;
+        throw;
+      }
+      in_relay_ = false;
+      last_.algo = "fused-segments-relay";
+      last_.bytes = (size_t)len * es;
+      return;
+    }
+  }
   bool any_reduce = false;
   SegArgs a{};
   a.tab = table();

@@ -192,3 +192,43 @@ def test_thread_segments_misaligned_views(planes):
     torch.cuda.synchronize()
     plane.check()
     assert torch.equal(dev[1][2].cpu(), _total(host))
+
+
+@pytest.mark.parametrize("world,T,root", [(4, 3, (2, 1)), (8, 2, (5, 0)), (8, 4, (0, 3))])
+def test_rooted_collectives_relay_through_all_ranks(planes, world, T, root):
+    """broadcastArray / reduceArray beyond 2 ranks and beyond seg_relay_min_bytes run as two launches (scatter +
+    allgather, reduce-scatter + gather) so that no single NVLink port carries (p - 1) x the array. Same results,
+    bit for bit; like the reference's reduce (reduce-scatter + gather in place, PCS:1390-1416) the relay uses
+    [from, to) of thread 0 of the non-root ranks as scratch."""
+    plane = planes(world)
+    plane.set_option("seg_relay_min_bytes", 0)
+    try:
+        n, f, to = 600011, 13, 599990
+        host, dev = _make(world, T, n, torch.float32, seed=11)
+        plane.thread_segments("thread_broadcast", dev, N.COPY, [(f, to, root[0], root[1], -1, -1)])
+        torch.cuda.synchronize()
+        plane.check()
+        assert "relay" in plane.last(), plane.last()
+        src = host[root[0]][root[1]]
+        for q in range(world):
+            for t in range(T):
+                want = host[q][t].clone()
+                want[f:to] = src[f:to]
+                assert torch.equal(dev[q][t].cpu(), want), (q, t)
+        for dtype, op in [(torch.float32, N.SUM), (torch.int64, N.MAX)]:
+            host, dev = _make(world, T, n, dtype, seed=12)
+            plane.thread_segments("thread_reduce", dev, op, [(f, to, -1, -1, root[0], root[1])])
+            torch.cuda.synchronize()
+            plane.check()
+            assert "relay" in plane.last(), plane.last()
+            total = _total(host, op)
+            for q in range(world):
+                for t in range(T):
+                    got = dev[q][t].cpu()
+                    assert torch.equal(got[:f], host[q][t][:f]) and torch.equal(got[to:], host[q][t][to:]), (q, t)
+                    if (q, t) == root:
+                        assert torch.equal(got[f:to], total[f:to])
+                    elif t != 0 or q == root[0]:
+                        assert torch.equal(got, host[q][t]), (q, t)
+    finally:
+        plane.set_option("seg_relay_min_bytes", 4 << 20)

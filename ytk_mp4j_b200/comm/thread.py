@@ -335,6 +335,10 @@ class ThreadCommSlave:
         return arrData
 
     def reduceArray(self, arrData, operand, operator, from_, to, rootRank, rootThreadId):
+        """The root thread's array gets the reduction over all slaveNum x threadNum arrays (TCS:1396). As in the
+        reference (reduce-scatter + gather in place, PCS:1390-1416) [from, to) of the other arrays is scratch: the
+        host path reduces into the delegate thread's array, the GPU relay (beyond 2 ranks and 4 MiB) rests partial
+        results in thread 0 of every non-root rank."""
         if self._T == 1:
             return self.processCommSlave.reduceArray(arrData, operand, operator, from_, to, rootRank)
         rr = self._real_root(rootRank, rootThreadId)
