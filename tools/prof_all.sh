@@ -1,10 +1,13 @@
 #!/bin/bash
 # One `ncu --set full` capture per kernel family on ONE GPU (emulated ranks), after a plain run of the same
 # command exited 0. Reports go to gpurun_out/ncu/<name>.ncu-rep; read them with tools/ncu_summary.py.
+# Usage: tools/prof_all.sh [name ...]   (no names = every family)
 set -u
 mkdir -p gpurun_out/ncu
+only=" $* "
 run() {  # name, --which, kernel regex, launches to skip
   local name=$1 which=$2 regex=$3 skip=$4
+  if [ "$only" != "  " ] && [[ "$only" != *" $name "* ]]; then return; fi
   python tools/prof_all.py --which $which --iters 3 > gpurun_out/ncu/$name.plain.log 2>&1 || { echo "$name: plain run failed"; tail -3 gpurun_out/ncu/$name.plain.log; return; }
   timeout 600 ncu --set full --clock-control none --import-source on -k regex:$regex -s $skip -c 1 \
       -o gpurun_out/ncu/$name -f python tools/prof_all.py --which $which --iters 3 > gpurun_out/ncu/$name.ncu.log 2>&1
@@ -21,7 +24,8 @@ run thread_ws ws thread_fused_ws_kernel 1
 run seg_rs seg_rs thread_seg_kernel 1
 run seg_ag seg_ag thread_seg_kernel 1
 run map_partition map map_partition_push_kernel 1
-run map_merge map map_merge_kernel 1
+run map_table map map_table_kernel 1
+run map_gather map map_allgather_push_kernel 1
 run gbdt gbdt gbdt_hist 1
 run codec codec codec_allreduce_kernel 1
 run lr_xtr lr lr_xtr 1
