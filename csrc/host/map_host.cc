@@ -1,12 +1,15 @@
-// Host map collectives on (String key, primitive value) maps: allreduceMap / reduceMap of the reference
-// (PCS:2053-2081, 1490-1516: hash-partition by String.hashCode() % p, ring reduce-scatter with
-// recv-and-merge DOP:225-257, allgather / gather, union), natively.
+// Host map collectives on (String key, primitive value) maps: allreduceMap / reduceMap / reduceScatterMap of
+// the reference (PCS:2053-2081, 1490-1516, 1299-1327: hash-partition by String.hashCode() % p, reduce-scatter
+// with recv-and-merge DOP:225-257, allgather / gather, union), natively.
 //
-// The binding hands over the map as one key blob (NUL-separated UTF-8) plus one value array; every ring
-// step ships a partition as [u64 n][u32 key lengths][key bytes][values] over the byte transport and the
-// receiver merges it into a hash table of string views - no per-entry (de)serialisation objects and no
-// boxing, which is where the reference (Kryo + HashMap<String, Double>) and a pure-Python ring spend
-// their time.
+// The binding hands over the map as one key blob (NUL-separated UTF-8) plus one value array. The reduce-scatter
+// is a direct exchange over the persistent mesh: at step s every rank sends rank (r + s)'s partition to it and
+// receives its own partition from rank (r - s) - p - 1 full-duplex steps like the reference's ring, but every
+// message is an original partition (the ring forwards partial results that grow on the way) and all merging for
+// a key happens in ONE open-addressing table on its owner (64-bit hash + entry index per slot, keys compared only
+// on a hash match). A message is [u64 n][u32 key lengths][key bytes][values]: no per-entry (de)serialisation
+// objects and no boxing, which is where the reference (Kryo + HashMap<String, Double>) and a pure-Python ring
+// spend their time.
 #include <string.h>
 
 #include <string>
@@ -61,40 +64,117 @@ PartView view(const std::string& buf, size_t es) {
   return v;
 }
 
-// local = local (+) incoming: op(local value, incoming value) on common keys, insert otherwise (DOP:225-257)
-void merge(Part* local, const std::string& incoming_buf, int dtype, int op, size_t es) {
-  PartView in = view(incoming_buf, es);
-  std::unordered_map<std::string_view, size_t> index;
-  index.reserve((size_t)(local->n() + in.n) * 2);
-  // string_views into local->keys would dangle when it grows: index the local keys by offset first,
-  // append new keys into a side buffer and splice once at the end
-  {
+inline uint64_t hash_bytes(const char* s, size_t n) {
+  uint64_t h = 0x9e3779b97f4a7c15ull ^ (n * 0xff51afd7ed558ccdull);
+  while (n >= 8) {
+    uint64_t w;
+    memcpy(&w, s, 8);
+    h = (h ^ w) * 0xff51afd7ed558ccdull;
+    h ^= h >> 32;
+    s += 8;
+    n -= 8;
+  }
+  if (n) {
+    uint64_t w = 0;
+    memcpy(&w, s, n);
+    h = (h ^ w) * 0xc4ceb9fe1a85ec53ull;
+    h ^= h >> 29;
+  }
+  h *= 0x9e3779b97f4a7c15ull;
+  return h ^ (h >> 32);
+}
+
+// Index of the keys of ONE Part: open addressing; a slot holds the key's 64-bit hash, where its bytes start, its
+// length and its entry number, so that a probe touches one slot, then (on a hash match) the key bytes and the value.
+class KeyTable {
+ public:
+  explicit KeyTable(Part* part, size_t expect) : part_(part) {
+    size_t cap = 1024;
+    while (cap < 2 * expect) cap <<= 1;
+    slots_.assign(cap, Slot{});
     size_t off = 0;
-    for (size_t i = 0; i < local->n(); ++i) {
-      index.emplace(std::string_view(local->keys.data() + off, local->lens[i]), i);
-      off += local->lens[i];
+    for (size_t i = 0; i < part->n(); ++i) {
+      place(Slot{hash_bytes(part->keys.data() + off, part->lens[i]), off, (uint32_t)i + 1, part->lens[i]});
+      off += part->lens[i];
     }
   }
-  std::string new_keys;
-  std::vector<uint32_t> new_lens;
-  std::vector<char> new_vals;
-  // (an incoming message is a map: its keys are distinct, so new keys need no index of their own)
-  size_t off = 0;
-  for (uint64_t i = 0; i < in.n; ++i) {
-    std::string_view k(in.keys + off, in.lens[i]);
-    off += in.lens[i];
-    auto it = index.find(k);
-    if (it != index.end()) {
-      host_reduce_into(dtype, op, local->vals.data() + it->second * es, in.vals + i * es, 1);
-    } else {
-      new_lens.push_back(in.lens[i]);
-      new_keys.append(k.data(), k.size());
-      new_vals.insert(new_vals.end(), in.vals + i * es, in.vals + (i + 1) * es);
+  // part (+)= incoming message: op(local value, incoming value) on common keys, insert otherwise (DOP:225-257)
+  void merge(const std::string& incoming_buf, int dtype, int op, size_t es) {
+    const PartView in = view(incoming_buf, es);
+    Part& pt = *part_;
+    // hashes first, so that the probe loop can prefetch the home slot of the key 16 places ahead
+    std::vector<uint64_t> hs((size_t)in.n);
+    {
+      size_t off = 0;
+      for (uint64_t i = 0; i < in.n; ++i) {
+        hs[(size_t)i] = hash_bytes(in.keys + off, in.lens[i]);
+        off += in.lens[i];
+      }
+    }
+    constexpr uint64_t kAhead = 16;
+    size_t off = 0;
+    for (uint64_t i = 0; i < in.n; ++i) {
+      if (i + kAhead < in.n) __builtin_prefetch(&slots_[hs[(size_t)(i + kAhead)] & (slots_.size() - 1)]);
+      const char* k = in.keys + off;
+      const uint32_t len = in.lens[i];
+      off += len;
+      const uint64_t h = hs[(size_t)i];
+      size_t slot = h & (slots_.size() - 1);
+      bool found = false;
+      while (slots_[slot].ent) {
+        const Slot& sl = slots_[slot];
+        if (sl.hash == h && sl.len == len && memcmp(pt.keys.data() + sl.off, k, len) == 0) {
+          host_reduce_into(dtype, op, pt.vals.data() + (size_t)(sl.ent - 1) * es, in.vals + i * es, 1);
+          found = true;
+          break;
+        }
+        slot = (slot + 1) & (slots_.size() - 1);
+      }
+      if (found) continue;
+      if (pt.n() >= 0xfffffffeull) throw Error("map collective: more than 2^32 keys in one partition");
+      slots_[slot] = Slot{h, pt.keys.size(), (uint32_t)pt.n() + 1, len};
+      pt.lens.push_back(len);
+      pt.keys.append(k, len);
+      pt.vals.insert(pt.vals.end(), in.vals + i * es, in.vals + (i + 1) * es);
+      if (2 * pt.n() > slots_.size()) grow();
     }
   }
-  local->lens.insert(local->lens.end(), new_lens.begin(), new_lens.end());
-  local->keys.append(new_keys);
-  local->vals.insert(local->vals.end(), new_vals.begin(), new_vals.end());
+
+ private:
+  struct Slot {
+    uint64_t hash = 0;
+    uint64_t off = 0;   // byte offset of the key in part_->keys
+    uint32_t ent = 0;   // entry number + 1; 0 = free
+    uint32_t len = 0;
+  };
+  void place(const Slot& s) {
+    size_t slot = s.hash & (slots_.size() - 1);
+    while (slots_[slot].ent) slot = (slot + 1) & (slots_.size() - 1);
+    slots_[slot] = s;
+  }
+  void grow() {  // rehash from the stored hashes: no key bytes are touched
+    std::vector<Slot> old;
+    old.swap(slots_);
+    slots_.assign(old.size() * 2, Slot{});
+    for (const Slot& s : old)
+      if (s.ent) place(s);
+  }
+  Part* part_;
+  std::vector<Slot> slots_;
+};
+
+// The reduce-scatter step of all three collectives: parts[q] goes to rank q, parts[rank] absorbs what the others
+// hold for this rank. p - 1 full-duplex exchanges over the mesh.
+void exchange_and_merge(ProcessComm* pc, std::vector<Part>* parts, int rank, int p, int dtype, int op, size_t es) {
+  Part& mine = (*parts)[(size_t)rank];
+  KeyTable table(&mine, mine.n() * 2 + 16);
+  for (int s = 1; s < p; ++s) {
+    const int dst = (rank + s) % p, src = (rank - s + p) % p;
+    const std::string out = pack((*parts)[(size_t)dst]);
+    (*parts)[(size_t)dst] = Part();  // consumed
+    const std::string in = pc->sendrecv_bytes(dst, out.data(), out.size(), src);
+    table.merge(in, dtype, op, es);
+  }
 }
 
 void append(Part* dst, const std::string& buf, size_t es) {
@@ -144,14 +224,7 @@ void ProcessComm::map_reduce(int mode, int root, const char* blob, size_t blob_l
   } else {
     std::lock_guard<std::mutex> lk(op_mu_);
     const int next = (rank_ + 1) % p, prev = (rank_ - 1 + p) % p;
-    // ---- ring reduce-scatter: step s sends partition (rank-1-s), merges what arrives into (rank-2-s)
-    for (int s = 0; s < p - 1; ++s) {
-      const int sseg = ((rank_ - 1 - s) % p + p) % p, rseg = ((rank_ - 2 - s) % p + p) % p;
-      const std::string out = pack(parts[(size_t)sseg]);
-      const std::string in = sendrecv_bytes(next, out.data(), out.size(), prev);
-      merge(&parts[(size_t)rseg], in, dtype, op, es);
-      parts[(size_t)sseg] = Part();  // consumed
-    }
+    exchange_and_merge(this, &parts, rank_, p, dtype, op, es);
     Part& mine = parts[(size_t)rank_];
     if (mode == 0) {
       // ---- ring allgather of the owned partitions (disjoint key sets: plain concatenation)
@@ -210,14 +283,7 @@ void ProcessComm::map_reduce_scatter(const char* blob, size_t blob_len, const vo
   }
   if (p > 1) {
     std::lock_guard<std::mutex> lk(op_mu_);
-    const int next = (rank_ + 1) % p, prev = (rank_ - 1 + p) % p;
-    for (int s = 0; s < p - 1; ++s) {
-      const int sseg = ((rank_ - 1 - s) % p + p) % p, rseg = ((rank_ - 2 - s) % p + p) % p;
-      const std::string out = pack(parts[(size_t)sseg]);
-      const std::string in = sendrecv_bytes(next, out.data(), out.size(), prev);
-      merge(&parts[(size_t)rseg], in, dtype, op, es);
-      parts[(size_t)sseg] = Part();
-    }
+    exchange_and_merge(this, &parts, rank_, p, dtype, op, es);
   }
   const Part& result = parts[(size_t)rank_];
   out_blob->clear();
