@@ -45,9 +45,10 @@ namespace mp4j {
 int map_threads();
 void map_launch_partition(int dtype, const MapExchangeArgs& a, int grid, cudaStream_t s);
 void map_launch_clear(int dtype, int op, const MapTable& t, int grid, cudaStream_t s);
-void map_launch_merge(int dtype, int op, const PeerTable& tab, int rank, const MapTable& t,
-                      unsigned long long rkeys_off, unsigned long long rvals_off, unsigned long long rcnt_off,
-                      long long cap, int grid, cudaStream_t s);
+// clear + insert + compact of a local array in one cooperative launch
+void map_launch_local(int dtype, int op, const MapTable& t, const long long* keys, const void* vals, long long n,
+                      long long* out_keys, void* out_vals, unsigned long long* count, unsigned long long out_cap,
+                      int sms, cudaStream_t s);
 void map_launch_merge_local(int dtype, int op, const MapTable& t, const long long* keys, const void* vals,
                             long long n, int grid, cudaStream_t s);
 void map_launch_compact(int dtype, const MapTable& t, long long* out_keys, void* out_vals,

@@ -204,25 +204,6 @@ __device__ __forceinline__ void table_insert(const MapTable& t, long long key, V
   }
 }
 
-// merges the p receive regions of this rank (counts in the heap) into its table
-template <typename V, int OP>
-__global__ void __launch_bounds__(kMapThreads) map_merge_kernel(PeerTable tab, int rank_arg, MapTable t,
-                                                                unsigned long long rkeys_off,
-                                                                unsigned long long rvals_off,
-                                                                unsigned long long rcnt_off, long long cap) {
-  const int rank = rank_arg;
-  const int p = tab.world;
-  const unsigned long long* cnt = (const unsigned long long*)(tab.heap[rank] + rcnt_off);
-  const long long* rk = (const long long*)(tab.heap[rank] + rkeys_off);
-  const V* rv = (const V*)(tab.heap[rank] + rvals_off);
-  for (int s = 0; s < p; ++s) {
-    const unsigned long long c = cnt[s];
-    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < c;
-         i += (unsigned long long)gridDim.x * blockDim.x)
-      table_insert<V, OP>(t, rk[(unsigned long long)s * cap + i], rv[(unsigned long long)s * cap + i]);
-  }
-}
-
 // merges a plain local array of pairs (thread-level map reduce / local pre-aggregation)
 template <typename V, int OP>
 __global__ void __launch_bounds__(kMapThreads) map_merge_local_kernel(MapTable t, const long long* keys,
@@ -240,6 +221,46 @@ __global__ void __launch_bounds__(kMapThreads) map_compact_kernel(MapTable t, lo
   const unsigned lane = threadIdx.x & 31;
   for (unsigned long long i0 = (unsigned long long)blockIdx.x * blockDim.x; i0 < size;
        i0 += (unsigned long long)gridDim.x * blockDim.x) {
+    const unsigned long long i = i0 + threadIdx.x;
+    const bool live = i < size && t.keys[i] != kMapEmpty;
+    const unsigned m = __ballot_sync(0xffffffffu, live);
+    if (m == 0) continue;
+    unsigned long long base = 0;
+    const int leader = __ffs(m) - 1;
+    if ((int)lane == leader) base = atomicAdd(count, (unsigned long long)__popc(m));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    if (live) {
+      const unsigned long long o = base + __popc(m & ((1u << lane) - 1u));
+      if (o < out_cap) {
+        out_keys[o] = t.keys[i];
+        out_vals[o] = ((const V*)t.vals)[i];
+      }
+    }
+  }
+}
+
+// Reduce-by-key of a plain local array in ONE cooperative launch (thread-level map merge, local pre-aggregation
+// of a sparse gradient): clear the table, insert, compact. The three kernels above remain for the allocation-free
+// entry point, which must not depend on cooperative launch limits.
+template <typename V, int OP>
+__global__ void __launch_bounds__(kMapThreads) map_local_kernel(MapTable t, const long long* keys, const V* vals,
+                                                                long long n, long long* out_keys, V* out_vals,
+                                                                unsigned long long* count,
+                                                                unsigned long long out_cap) {
+  cg::grid_group grid = cg::this_grid();
+  const unsigned long long size = t.mask + 1;
+  const unsigned long long tid = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const unsigned long long nthr = (unsigned long long)gridDim.x * blockDim.x;
+  for (unsigned long long i = tid; i < size; i += nthr) {
+    t.keys[i] = kMapEmpty;
+    ((V*)t.vals)[i] = identity<V, OP>();
+  }
+  if (tid == 0) *count = 0;
+  grid.sync();
+  for (unsigned long long i = tid; i < (unsigned long long)n; i += nthr) table_insert<V, OP>(t, keys[i], vals[i]);
+  grid.sync();
+  const unsigned lane = threadIdx.x & 31;
+  for (unsigned long long i0 = (unsigned long long)blockIdx.x * blockDim.x; i0 < size; i0 += nthr) {
     const unsigned long long i = i0 + threadIdx.x;
     const bool live = i < size && t.keys[i] != kMapEmpty;
     const unsigned m = __ballot_sync(0xffffffffu, live);
@@ -516,16 +537,26 @@ void map_launch_clear(int dtype, int op, const MapTable& t, int grid, cudaStream
   MP4J_CUDA(cudaGetLastError());
 }
 
-void map_launch_merge(int dtype, int op, const PeerTable& tab, int rank, const MapTable& t,
-                      unsigned long long rkeys_off, unsigned long long rvals_off, unsigned long long rcnt_off,
-                      long long cap, int grid, cudaStream_t s) {
+void map_launch_local(int dtype, int op, const MapTable& t, const long long* keys, const void* vals, long long n,
+                      long long* out_keys, void* out_vals, unsigned long long* count, unsigned long long out_cap,
+                      int sms, cudaStream_t s) {
   dispatch_v(dtype, [&](auto v) {
+    using V = decltype(v);
     dispatch_op(op, [&](auto o) {
-      map_merge_kernel<decltype(v), decltype(o)::value><<<grid, kMapThreads, 0, s>>>(tab, rank, t, rkeys_off, rvals_off,
-                                                                                    rcnt_off, cap);
+      auto kfn = map_local_kernel<V, decltype(o)::value>;
+      int per_sm = 0;
+      MP4J_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kfn, kMapThreads, 0));
+      const unsigned long long work = std::max<unsigned long long>(t.mask + 1, (unsigned long long)n);
+      const int grid = (int)std::max<unsigned long long>(
+          1, std::min<unsigned long long>((unsigned long long)std::min(per_sm, 4) * sms, (work + kMapThreads - 1) / kMapThreads));
+      MapTable tt = t;
+      const V* vv = (const V*)vals;
+      V* ov = (V*)out_vals;
+      void* params[] = {(void*)&tt, (void*)&keys, (void*)&vv, (void*)&n, (void*)&out_keys, (void*)&ov, (void*)&count,
+                        (void*)&out_cap};
+      MP4J_CUDA(cudaLaunchCooperativeKernel((const void*)kfn, dim3(grid), dim3(kMapThreads), params, 0, s));
     });
   });
-  MP4J_CUDA(cudaGetLastError());
 }
 
 void map_launch_merge_local(int dtype, int op, const MapTable& t, const long long* keys, const void* vals,

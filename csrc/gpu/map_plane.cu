@@ -94,10 +94,7 @@ void GpuPlane::map_reduce_local(int local_rank, const long long* keys, const voi
   // use only as much of the table as this call needs: clearing dominates small calls otherwise
   MapTable t{l.tkeys, l.tvals, tsize - 1};
   const int blocks = std::max(1, std::min(sms_ * 4, kMaxBlocks - 2));
-  map_launch_clear(dtype, op, t, blocks, s);
-  MP4J_CUDA(cudaMemsetAsync(out_count, 0, 8, s));
-  if (n > 0) map_launch_merge_local(dtype, op, t, keys, vals, n, blocks, s);
-  map_launch_compact(dtype, t, out_keys, out_vals, out_count, (unsigned long long)out_cap, blocks, s);
+  map_launch_local(dtype, op, t, keys, vals, n, out_keys, out_vals, out_count, (unsigned long long)out_cap, sms_, s);
   last_ = CollStat{"map_reduce_local", "hash-merge", (size_t)n * (8 + dtype_size(dtype)), blocks, false};
 }
 
