@@ -20,9 +20,6 @@ thread_local std::string g_last_error;
 struct mp4j_master {
   Master* m;
 };
-struct mp4j_tgroup {
-  ThreadComm* tc;
-};
 
 extern "C" {
 

@@ -5,6 +5,7 @@
 
 namespace mp4j {
 class ProcessComm;
+class ThreadComm;
 extern thread_local std::string g_last_error;
 }  // namespace mp4j
 
@@ -12,6 +13,10 @@ struct mp4j_comm {
   mp4j::ProcessComm* pc = nullptr;
   void* gpu = nullptr;                      // mp4j::GpuPlane*, owned; set by mp4j_gpu_init
   void (*gpu_dtor)(mp4j_comm*) = nullptr;   // installed by the GPU half so the host half stays CUDA-free
+};
+
+struct mp4j_tgroup {
+  mp4j::ThreadComm* tc = nullptr;
 };
 
 #define MP4J_API_BEGIN try {

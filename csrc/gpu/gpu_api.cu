@@ -1,9 +1,13 @@
 // extern "C" surface of the GPU data plane (include/mp4j_gpu.h).
 #include <string.h>
 
+#include <string>
+#include <vector>
+
 #include "../../include/mp4j.h"
 #include "../capi/capi_util.h"
 #include "../host/process_comm.h"
+#include "../host/thread_comm.h"
 #include "custom_op.h"
 #include "gpu_plane.h"
 
@@ -206,6 +210,55 @@ int mp4j_gpu_thread_allreduce(mp4j_gpu* g, void* const* bufs, int T, int dtype, 
   TraceScope trace_scope(g->g, (cudaStream_t)stream, "mp4j.thread_allreduce");
   g->g->thread_allreduce(bufs, T, dtype, op, from, to, fanout, dst, local_only != 0,
                          (thread_algo & 0xff) | (algo << 16), (cudaStream_t)stream);
+  MP4J_API_END
+}
+
+// ---- ThreadCommSlave on device (or pinned host) buffers, called by ALL T threads of a process with their own
+// buffer: the rendezvous, the election of the launching thread and the propagation of its error to every thread
+// happen natively (ThreadComm::delegate), so that every binding gets them from the C ABI instead of rebuilding them.
+static std::vector<void*> thread_bufs(const std::vector<uint64_t>& args) {
+  std::vector<void*> bufs(args.size());
+  for (size_t t = 0; t < args.size(); ++t) {
+    bufs[t] = (void*)(uintptr_t)args[t];
+    // a binding whose own argument check failed on one thread still joins the rendezvous (with no buffer), so
+    // that the other T - 1 threads get an error instead of waiting for it forever
+    if (!bufs[t]) throw Error("thread " + std::to_string(t) + " passed no usable buffer to a thread-level collective");
+  }
+  return bufs;
+}
+
+int mp4j_thread_gpu_allreduce(mp4j_tgroup* tg, mp4j_gpu* g, int tid, void* buf, int dtype, int op, int64_t from,
+                              int64_t to, int fanout, int dst, int local_only, int thread_algo, int algo,
+                              void* stream) {
+  MP4J_API_BEGIN
+  tg->tc->delegate(tid, 0, (uint64_t)(uintptr_t)buf, [&](const std::vector<uint64_t>& args) {
+    std::vector<void*> bufs = thread_bufs(args);
+    if (mp4j_gpu_thread_allreduce(g, bufs.data(), (int)bufs.size(), dtype, op, from, to, fanout, dst, local_only,
+                                  thread_algo, algo, stream) != 0)
+      throw Error(g_last_error);
+  });
+  MP4J_API_END
+}
+
+int mp4j_thread_gpu_allreduce_host(mp4j_tgroup* tg, mp4j_gpu* g, int tid, void* hbuf, int dtype, int op, int64_t from,
+                                   int64_t to, int fanout, int dst, void* stream) {
+  MP4J_API_BEGIN
+  tg->tc->delegate(tid, 0, (uint64_t)(uintptr_t)hbuf, [&](const std::vector<uint64_t>& args) {
+    std::vector<void*> bufs = thread_bufs(args);
+    if (mp4j_gpu_thread_allreduce_host(g, bufs.data(), (int)bufs.size(), dtype, op, from, to, fanout, dst, stream) != 0)
+      throw Error(g_last_error);
+  });
+  MP4J_API_END
+}
+
+int mp4j_thread_gpu_segments(mp4j_tgroup* tg, mp4j_gpu* g, int tid, int launch_tid, void* buf, int dtype, int op,
+                             const int64_t* segs, int nseg, const char* name, void* stream) {
+  MP4J_API_BEGIN
+  tg->tc->delegate(tid, launch_tid, (uint64_t)(uintptr_t)buf, [&](const std::vector<uint64_t>& args) {
+    std::vector<void*> bufs = thread_bufs(args);
+    if (mp4j_gpu_thread_segments(g, bufs.data(), (int)bufs.size(), dtype, op, segs, nseg, name, stream) != 0)
+      throw Error(g_last_error);
+  });
   MP4J_API_END
 }
 

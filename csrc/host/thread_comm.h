@@ -9,8 +9,11 @@
 #pragma once
 #include <stdint.h>
 
+#include <exception>
 #include <string>
+#include <vector>
 
+#include "../core/error.h"
 #include "process_comm.h"
 #include "thread_group.h"
 
@@ -29,6 +32,35 @@ class ThreadComm {
   // allgather), counts likewise (reduce-scatter).
   void collective(ProcessComm& pc, int tid, int kind, void* arr, int dtype, int op, int64_t from, int64_t to,
                   const int64_t* lo, const int64_t* hi, const int64_t* counts, int root_rank, int root_tid);
+
+  // The rendezvous every thread-level collective is built on, for steps that ONE thread performs for all (a fused
+  // GPU kernel over the T device buffers, a host pipeline): every thread deposits `my_arg` (a pointer), thread
+  // `root` runs fn(args of all T threads), everybody returns when it has finished; an exception thrown by fn is
+  // rethrown as mp4j::Error on ALL T threads. Replaces the Exchanger tree + volatile metadata of the reference
+  // (TCS:259-303) and is what the bindings' own delegate loops (Python: thread.py _delegate) do for objects.
+  template <typename F>
+  void delegate(int tid, int root, uint64_t my_arg, F&& fn) {
+    const int T = tg_.size();
+    if (tid < 0 || tid >= T || root < 0 || root >= T) throw Error("threadId out of range");
+    tg_.set_slot(tid, 0, my_arg);
+    if (tid == root) tg_.set_slot(root, 1, 0);  // error flag of this call
+    tg_.barrier();
+    if (tid == root) {
+      try {
+        std::vector<uint64_t> args((size_t)T);
+        for (int t = 0; t < T; ++t) args[(size_t)t] = tg_.get_slot(t, 0);
+        fn(args);
+      } catch (const std::exception& e) {
+        tg_.set_slot(root, 1, 1);
+        error_ = e.what();
+      }
+    }
+    tg_.barrier();
+    const bool failed = tg_.get_slot(root, 1) != 0;
+    const std::string err = failed ? error_ : std::string();
+    tg_.barrier();  // error_ and the slots stay untouched until everybody has read them
+    if (failed) throw Error(err);
+  }
 
  private:
   ThreadGroup tg_;

@@ -100,6 +100,22 @@ int mp4j_gpu_thread_segments(mp4j_gpu* g, void* const* bufs, int T, int dtype, i
 int mp4j_gpu_thread_allreduce_host(mp4j_gpu* g, void* const* hbufs, int T, int dtype, int op, int64_t from,
                                    int64_t to, int fanout, int dst, void* stream);
 
+/* ThreadCommSlave collectives (TCS:448-1963) called the way the reference's are: by EVERY one of the T threads of a
+ * process (threads of `tg`, ids 0..T-1), each with its own buffer. The rendezvous, the election of the launching
+ * thread (thread 0; `launch_tid` for the segment form, the reference's root thread rule TCS:486) and the delivery of
+ * its error to all T threads are native (mp4j::ThreadComm::delegate), so a binding needs no thread machinery of its
+ * own. All threads must pass the same dtype / op / range / segment table; `stream` of the launching thread is used.
+ * buf: device pointer (allreduce, segments) or host pointer, pinned for full speed (allreduce_host); a thread
+ * whose own argument check failed passes NULL and every thread gets an error. Other arguments as in the
+ * mp4j_gpu_thread_* forms above. */
+int mp4j_thread_gpu_allreduce(mp4j_tgroup* tg, mp4j_gpu* g, int tid, void* buf, int dtype, int op, int64_t from,
+                              int64_t to, int fanout, int dst, int local_only, int thread_algo, int algo,
+                              void* stream);
+int mp4j_thread_gpu_allreduce_host(mp4j_tgroup* tg, mp4j_gpu* g, int tid, void* hbuf, int dtype, int op, int64_t from,
+                                   int64_t to, int fanout, int dst, void* stream);
+int mp4j_thread_gpu_segments(mp4j_tgroup* tg, mp4j_gpu* g, int tid, int launch_tid, void* buf, int dtype, int op,
+                             const int64_t* segs, int nseg, const char* name, void* stream);
+
 /* Sparse (map container) collectives on (int64 key, value) device arrays: allreduceMap (mode 0,
  * PCS:2053), reduceScatterMap (mode 1, PCS:1299: every rank receives the keys it owns) and
  * allgatherMap (mode 2, PCS:666: concatenation in rank order). One entry per LOCAL rank in every

@@ -17,6 +17,7 @@
 #include <thread>
 #include <vector>
 
+#include "../../csrc/host/thread_comm.h"
 #include "../../include/mp4j.h"
 
 static std::atomic<int> g_fail{0};
@@ -401,6 +402,41 @@ int main(int argc, char** argv) {
       });
     for (auto& t : tt) t.join();
     mp4j_tgroup_destroy(g);
+  }
+  // ThreadComm::delegate (what the thread-level GPU collectives stand on): one thread runs the step with everybody's
+  // argument; a failure of that step reaches all T threads, and the group is usable afterwards
+  {
+    mp4j::ThreadComm tc(5);
+    std::atomic<int> errors_seen{0};
+    std::atomic<uint64_t> sum_seen{0};
+    std::vector<std::thread> tt;
+    for (int t = 0; t < 5; ++t)
+      tt.emplace_back([&, t] {
+        for (int i = 0; i < 100; ++i) {
+          const int root = i % 5;
+          const bool fail = i % 7 == 3;
+          try {
+            tc.delegate(t, root, (uint64_t)(i * 10 + t), [&](const std::vector<uint64_t>& a) {
+              uint64_t sacc = 0;
+              for (uint64_t x : a) sacc += x;
+              if (sacc != (uint64_t)(i * 50 + 10)) g_fail.fetch_add(1);
+              if (fail) throw mp4j::Error("step failed on purpose");
+              sum_seen.fetch_add(sacc);
+            });
+            if (fail) g_fail.fetch_add(1);  // every thread must see the failure
+          } catch (const mp4j::Error& e) {
+            if (!fail || std::string(e.what()).find("on purpose") == std::string::npos) g_fail.fetch_add(1);
+            errors_seen.fetch_add(1);
+          }
+        }
+      });
+    for (auto& t : tt) t.join();
+    int nfail = 0;
+    for (int i = 0; i < 100; ++i) nfail += i % 7 == 3;
+    if (errors_seen.load() != 5 * nfail) {
+      fprintf(stderr, "delegate: %d threads saw an error, want %d\n", errors_seen.load(), 5 * nfail);
+      g_fail.fetch_add(1);
+    }
   }
   mp4j_master_destroy(m);
   printf("host_stress p=%d rounds=%d n=%lld: %s (%d failures)\n", p, rounds, (long long)n, g_fail.load() ? "FAILED" : "ok",

@@ -7,11 +7,13 @@ lg T full-length passes (TCS:259-303), then thread 0 runs the process collective
 copy the result out behind two barriers (TCS:1941-1957). Here the T threads deposit their
 arguments in per-thread slots, meet at a native spin-then-sleep barrier (csrc/host/thread_group.cc)
 and ONE delegate thread does the work for all:
-  * CUDA tensors: a single fused kernel reads the T thread buffers, reduces them in registers,
-    runs the inter-GPU step over NVLink and fans the result out to the T buffers
-    (csrc/gpu/thread_allreduce.cu) - never T x the data on the wire;
-  * host data: the delegate reduces/merges in thread-id order, calls the process collective and
-    copies results back.
+  * CUDA tensors and pinned host tensors: every thread calls into the C ABI with its own buffer; the rendezvous, the
+    launch by one thread and the delivery of its error to all threads are native (mp4j::ThreadComm::delegate,
+    csrc/host/thread_comm.h). The launch is a single fused kernel that reads the T thread buffers, reduces them in
+    registers, runs the inter-GPU step over NVLink and fans the result out - never T x the data on the wire;
+  * native host arrays: mp4j::ThreadComm, all T threads combine and fan out in parallel;
+  * Python objects (maps, scalars, lists): `_delegate` below - the delegate reduces/merges in thread-id order, calls
+    the process collective and hands results back.
 Root-thread delegation follows SURVEY §2.7-14: only the root process honours rootThreadId, every
 other process delegates through thread 0; non-root threads keep their own input (arrays) or get
 None (maps). Map results are shared by reference among the threads of a process (TCS:2214-2217).
@@ -164,10 +166,7 @@ class ThreadCommSlave:
         if not self.gpu.thread_segments_ok([arrData], operand, operator, len(segs)):
             return False
 
-        def run(arrs):
-            self.gpu.thread_segments(name, arrs, operand, operator, segs)
-            return None
-        self._delegate(arrData, run, root_thread)
+        self.gpu.thread_native_segments(self._tg, self.getThreadId(), root_thread, name, arrData, operand, operator, segs)
         return True
 
     def _real_root(self, rootRank, rootThreadId):
@@ -376,11 +375,8 @@ class ThreadCommSlave:
         if self.processCommSlave._gpu_host_ok(arrData, operand, operator):
             # pinned host tensors with the GPU plane up: thread 0 streams all T arrays through the GPU
             # (H2D || fused kernel || D2H pipeline in the library); every thread's array gets the result
-            def run_host(arrs):
-                self.gpu.thread_allreduce_host(arrs, operand, operator, from_, to, fanout=resultThread is None,
-                                               dst=resultThread or 0)
-                return None
-            self._delegate(arrData, run_host, 0)
+            self.gpu.thread_native_allreduce(self._tg, self.getThreadId(), arrData, operand, operator, from_, to,
+                                             host=True, fanout=resultThread is None, dst=resultThread or 0)
             return arrData
         if not _is_cuda(arrData):
             # host arrays + predefined operator: native path in which ALL T threads take part (each
@@ -391,10 +387,13 @@ class ThreadCommSlave:
                                                   a.ctypes.data, operand.code, operator.code, from_, to))
                 return arrData
 
+        if _is_cuda(arrData):
+            # CUDA tensors: the fused thread-reduce + inter-GPU + fan-out kernel, launched by thread 0 from the
+            # native rendezvous (every thread calls in with its own tensor)
+            self.gpu.thread_native_allreduce(self._tg, self.getThreadId(), arrData, operand, operator, from_, to)
+            return arrData
+
         def run(arrs):
-            if _is_cuda(arrs[0]):
-                self.gpu.thread_allreduce(arrs, operand, operator, from_, to)
-                return None
             self._local_reduce(arrs, operand, operator, from_, to, 0)
             self.processCommSlave.allreduceArray(arrs[0], operand, operator, from_, to)
             for t in range(1, self._T):

@@ -62,6 +62,12 @@ _P("mp4j_gpu_allreduce_wire", C.c_int, C.c_void_p, N.c_vpp, C.c_int64, C.c_int64
 _P("mp4j_gpu_custom_op", C.c_int, C.c_void_p, C.c_int, C.c_char_p, C.POINTER(C.c_int))
 _P("mp4j_gpu_trace", C.c_int, C.c_void_p, C.c_int)
 _P("mp4j_gpu_set_option", C.c_int, C.c_void_p, C.c_char_p, C.c_longlong)
+_P("mp4j_thread_gpu_allreduce", C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int64,
+   C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p)
+_P("mp4j_thread_gpu_allreduce_host", C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int64,
+   C.c_int64, C.c_int, C.c_int, C.c_void_p)
+_P("mp4j_thread_gpu_segments", C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int,
+   C.POINTER(C.c_int64), C.c_int, C.c_char_p, C.c_void_p)
 _P("mp4j_gpu_stats", C.c_int, C.c_void_p, C.c_char_p, C.c_size_t, C.c_int)
 _P("mp4j_rtc_compile", C.c_int, C.c_int, C.c_char_p, C.c_int, C.POINTER(C.c_longlong))
 
@@ -534,6 +540,44 @@ class GpuPlane(_PlaneBase):
             _check_tensor(t)
         op = N.COPY if operator is None else self._op(operator, operand.code)
         self._thread_segments(ts, len(ts), _code_of(ts[0], operand), op, segs, name, stream)
+
+    # --- the same three, called by EVERY thread of a ThreadCommSlave with its own tensor: rendezvous, launch by one
+    # thread and error delivery to all T threads are native (mp4j_thread_gpu_*, ThreadComm::delegate); the GIL is
+    # released while a thread waits. A thread whose own argument check fails still joins (with no buffer): the other
+    # threads get an error instead of waiting for it forever, and it raises its own message afterwards.
+    def _thread_native(self, tid, launch_tid, t, operand, operator, host, call):
+        err, ptr, code, op = None, 0, 0, N.COPY
+        try:
+            (_check_host_tensor if host else _check_tensor)(t)
+            code = _code_of(t, operand)
+            if tid == launch_tid and operator is not None:
+                op = self._op(operator, operand.code)
+            ptr = t.data_ptr() or 16  # an empty tensor has no address; no element of it is touched
+        except Exception as e:  # noqa: BLE001 - surfaced below, after the rendezvous
+            err = e
+        rc = call(ptr, code, op)
+        if err is not None:
+            raise err if isinstance(err, Mp4jException) else Mp4jException(repr(err))
+        check(rc)
+
+    def thread_native_allreduce(self, tg, tid, t, operand, operator, f, to, host=False, fanout=True, dst=0, stream=None):
+        local = self.world == 1
+        sp = _stream_ptr(stream)
+        if host:
+            call = lambda ptr, code, op: N.lib.mp4j_thread_gpu_allreduce_host(  # noqa: E731
+                tg, self._g, tid, ptr, code, op, f, to, 1 if fanout else 0, dst, sp)
+        else:
+            call = lambda ptr, code, op: N.lib.mp4j_thread_gpu_allreduce(  # noqa: E731
+                tg, self._g, tid, ptr, code, op, f, to, 1 if fanout else 0, dst, 1 if local else 0,
+                self.thread_algo if local else 0, N.ALGO_AUTO, sp)
+        self._thread_native(tid, 0, t, operand, operator, host, call)
+
+    def thread_native_segments(self, tg, tid, launch_tid, name, t, operand, operator, segs, stream=None):
+        flat = N.i64_array([int(x) for s in segs for x in s])
+        sp = _stream_ptr(stream)
+        self._thread_native(tid, launch_tid, t, operand, operator, False,
+                            lambda ptr, code, op: N.lib.mp4j_thread_gpu_segments(
+                                tg, self._g, tid, launch_tid, ptr, code, op, flat, len(segs), name.encode(), sp))
 
     def thread_reduce(self, ts, operand, operator, f, to, dst, stream=None):
         """Intra-process reduce of the T buffers into ts[dst] (thread path of DOP:441-457)."""
