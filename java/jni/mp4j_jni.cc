@@ -190,3 +190,20 @@ FN(jint, gpuBroadcast)(JNIEnv*, jclass, jlong g, jlong ptr, jint dt, jlong from,
   void* arrs[1] = {(void*)ptr};
   return mp4j_gpu_broadcast((mp4j_gpu*)g, arrs, dt, from, to, root, 0, (void*)stream);
 }
+
+// ---- ThreadCommSlave on device buffers: every Java thread calls with its own buffer (include/mp4j_gpu.h)
+FN(jlong, tgroupCreate)(JNIEnv*, jclass, jint threadNum) {
+  mp4j_tgroup* tg = nullptr;
+  if (mp4j_tgroup_create(threadNum, &tg) != 0) return 0;
+  return (jlong)tg;
+}
+FN(void, tgroupDestroy)(JNIEnv*, jclass, jlong tg) { mp4j_tgroup_destroy((mp4j_tgroup*)tg); }
+FN(jint, threadGpuAllreduce)(JNIEnv*, jclass, jlong tg, jlong g, jint tid, jlong ptr, jint dt, jint op, jlong from, jlong to, jlong stream) {
+  return mp4j_thread_gpu_allreduce((mp4j_tgroup*)tg, (mp4j_gpu*)g, tid, (void*)ptr, dt, op, from, to, 1, 0, 0, 0, 0, (void*)stream);
+}
+FN(jint, threadGpuSegments)(JNIEnv* env, jclass, jlong tg, jlong g, jint tid, jint launchTid, jlong ptr, jint dt, jint op, jlongArray segs, jstring name, jlong stream) {
+  Longs sg(env, segs);
+  Str nm(env, name);
+  return mp4j_thread_gpu_segments((mp4j_tgroup*)tg, (mp4j_gpu*)g, tid, launchTid, (void*)ptr, dt, op, sg.get(),
+                                  (int)(env->GetArrayLength(segs) / 6), nm.c, (void*)stream);
+}

@@ -41,4 +41,9 @@ final class Native {
     static native int gpuReduceScatter(long g, long devPtr, int dtype, int op, long from, long[] counts, long stream);
     static native int gpuAllgather(long g, long devPtr, int dtype, long[] froms, long[] tos, long stream);
     static native int gpuBroadcast(long g, long devPtr, int dtype, long from, long to, int root, long stream);
+    // ThreadCommSlave on device buffers: every thread calls with its own buffer, the rendezvous is native
+    static native long tgroupCreate(int threadNum);
+    static native void tgroupDestroy(long tg);
+    static native int threadGpuAllreduce(long tg, long g, int tid, long devPtr, int dtype, int op, long from, long to, long stream);
+    static native int threadGpuSegments(long tg, long g, int tid, int launchTid, long devPtr, int dtype, int op, long[] segs, String name, long stream);
 }

@@ -556,7 +556,9 @@ public class ProcessCommSlave {
         gpu = Native.gpuInit(handle, device, heapBytes, stagingBytes);
         if (gpu == 0) throw new Mp4jException(Native.lastError());
     }
-    private static int deviceOp(IOperator op) throws Mp4jException {
+    /** handle of the GPU plane for the thread-level device methods of ThreadCommSlave (0 before initGpu) */
+    long gpuHandle() { return gpu; }
+    static int deviceOp(IOperator op) throws Mp4jException {
         if (op.nativeCode() < 0) throw new Mp4jException("device collectives take the predefined operators of Operators.*");
         return op.nativeCode();
     }

@@ -595,4 +595,94 @@ public class ThreadCommSlave {
     public <E> List<E> allreduceListConcatProcess(List<E> listData) throws Mp4jException {
         return process.allreduceListConcat(listData);
     }
+    // ------------------------------------------------------------------ device buffers (GPU plane)
+    // The thread-level collectives on raw CUDA addresses (one buffer per thread, e.g. from a CUDA binding of the
+    // caller's choice). Every thread calls with its own buffer; deposit, launch by one thread and delivery of its
+    // error to all threads are native (mp4j_thread_gpu_*, mp4j::ThreadComm::delegate). One fused kernel per call:
+    // thread reduce + inter-GPU step + fan-out (allreduce: csrc/gpu/thread_fused_ws.cu, the others: thread_seg.cu).
+    private volatile long tgroup = 0;
+
+    /** call once (any one thread) before the ...Device methods */
+    public synchronized void initGpu(int device, long heapBytes, long stagingBytes) throws Mp4jException {
+        process.initGpu(device, heapBytes, stagingBytes);
+        if (tgroup == 0) tgroup = Native.tgroupCreate(threadNum);
+        if (tgroup == 0) throw new Mp4jException(Native.lastError());
+    }
+
+    private long plane() throws Mp4jException {
+        if (tgroup == 0 || process.gpuHandle() == 0) throw new Mp4jException("call initGpu first");
+        return process.gpuHandle();
+    }
+
+    private void segments(String name, long devPtr, Operand operand, int op, long[] segs, int launchTid, long stream) throws Mp4jException {
+        if (Native.threadGpuSegments(tgroup, plane(), getThreadId(), launchTid, devPtr, operand.dtype, op, segs, name, stream) != 0)
+            throw new Mp4jException(Native.lastError());
+    }
+
+    /** segment table rows: lo, hi, srcRank, srcThread, dstRank, dstThread (-1 = all) */
+    private long[] table(int[][] lo, int[][] hi, boolean fromAll, int srcRank, int srcThread, int dstRank, int dstThread) {
+        int p = getSlaveNum();
+        long[] segs = new long[p * threadNum * 6];
+        int k = 0;
+        for (int q = 0; q < p; q++) for (int t = 0; t < threadNum; t++) {
+            segs[k++] = lo[q][t];
+            segs[k++] = hi[q][t];
+            segs[k++] = fromAll ? -1 : (srcRank == -2 ? q : srcRank);
+            segs[k++] = fromAll ? -1 : (srcRank == -2 ? t : srcThread);
+            segs[k++] = dstRank == -2 ? q : dstRank;
+            segs[k++] = dstRank == -2 ? t : dstThread;
+        }
+        return segs;
+    }
+
+    private int launcher(int rootRank, int rootThreadId) { return getRank() == rootRank ? rootThreadId : 0; }  // TCS:486
+
+    public void allreduceArrayDevice(long devPtr, Operand operand, IOperator operator, long from, long to, long stream) throws Mp4jException {
+        if (from < 0 || to < from) throw new Mp4jException("from must be >= 0 and <= to!");
+        if (Native.threadGpuAllreduce(tgroup, plane(), getThreadId(), devPtr, operand.dtype, ProcessCommSlave.deviceOp(operator), from, to, stream) != 0)
+            throw new Mp4jException(Native.lastError());
+    }
+
+    /** thread (q, t) ends with the reduced [from + counts before it, + counts[q][t]) (TCS:1174) */
+    public void reduceScatterArrayDevice(long devPtr, Operand operand, IOperator operator, int from, int[][] counts, long stream) throws Mp4jException {
+        CommUtils.isFromCountsLegal(from, counts);
+        int p = getSlaveNum();
+        int[][] lo = new int[p][threadNum], hi = new int[p][threadNum];
+        int off = from;
+        for (int q = 0; q < p; q++) for (int t = 0; t < threadNum; t++) {
+            lo[q][t] = off;
+            off += counts[q][t];
+            hi[q][t] = off;
+        }
+        segments("thread_reduce_scatter", devPtr, operand, ProcessCommSlave.deviceOp(operator), table(lo, hi, true, 0, 0, -2, 0), 0, stream);
+    }
+
+    public void reduceArrayDevice(long devPtr, Operand operand, IOperator operator, int from, int to, int rootRank, int rootThreadId, long stream) throws Mp4jException {
+        CommUtils.isFromToLegal(from, to);
+        segments("thread_reduce", devPtr, operand, ProcessCommSlave.deviceOp(operator), new long[]{from, to, -1, -1, rootRank, rootThreadId},
+                launcher(rootRank, rootThreadId), stream);
+    }
+
+    public void broadcastArrayDevice(long devPtr, Operand operand, int from, int to, int rootRank, int rootThreadId, long stream) throws Mp4jException {
+        CommUtils.isFromToLegal(from, to);
+        segments("thread_broadcast", devPtr, operand, 0 /* MP4J_COPY is ignored: no segment reduces */, new long[]{from, to, rootRank, rootThreadId, -1, -1},
+                launcher(rootRank, rootThreadId), stream);
+    }
+
+    public void allgatherArrayDevice(long devPtr, Operand operand, int[][] froms, int[][] tos, long stream) throws Mp4jException {
+        CommUtils.isfromsTosLegal(froms, tos, threadNum);
+        segments("thread_allgather", devPtr, operand, 0, table(froms, tos, false, -2, 0, -1, -1), 0, stream);
+    }
+
+    public void gatherArrayDevice(long devPtr, Operand operand, int[][] sendfroms, int[][] sendtos, int rootRank, int rootThreadId, long stream) throws Mp4jException {
+        CommUtils.isfromsTosLegal(sendfroms, sendtos, threadNum);
+        segments("thread_gather", devPtr, operand, 0, table(sendfroms, sendtos, false, -2, 0, rootRank, rootThreadId),
+                launcher(rootRank, rootThreadId), stream);
+    }
+
+    public void scatterArrayDevice(long devPtr, Operand operand, int[][] recvfroms, int[][] recvtos, int rootRank, int rootThreadId, long stream) throws Mp4jException {
+        CommUtils.isfromsTosLegal(recvfroms, recvtos, threadNum);
+        segments("thread_scatter", devPtr, operand, 0, table(recvfroms, recvtos, false, rootRank, rootThreadId, -2, 0),
+                launcher(rootRank, rootThreadId), stream);
+    }
 }

@@ -78,6 +78,9 @@ FN(jint, hostReduceScatter)(JNIEnv*, jclass, jlong, jobject, jint, jint, jlong, 
 FN(jint, hostAllgather)(JNIEnv*, jclass, jlong, jobject, jint, jlongArray, jlongArray);
 FN(jint, hostBroadcast)(JNIEnv*, jclass, jlong, jobject, jint, jlong, jlong, jint);
 FN(jbyteArray, sendrecvBytes)(JNIEnv*, jclass, jlong, jint, jbyteArray, jint);
+FN(jlong, tgroupCreate)(JNIEnv*, jclass, jint);
+FN(void, tgroupDestroy)(JNIEnv*, jclass, jlong);
+FN(jint, threadGpuAllreduce)(JNIEnv*, jclass, jlong, jlong, jint, jlong, jint, jint, jlong, jlong, jlong);
 #define CALL(name) Java_com_fenbi_mp4j_comm_Native_##name
 
 template <typename T>
@@ -169,6 +172,14 @@ int main(int argc, char** argv) {
   const int code = CALL(masterWait)(&env, nullptr, m);
   CHECK(code == 0, "master exit code %d", code);
   CALL(masterDestroy)(&env, nullptr, m);
+  {  // thread group handle of the thread-level device methods: created and destroyed without a GPU; a call with a
+     // thread id outside the group fails with a message instead of touching the (absent) GPU plane
+    jlong tg = CALL(tgroupCreate)(&env, nullptr, 4);
+    CHECK(tg != 0, "tgroupCreate");
+    CHECK(CALL(threadGpuAllreduce)(&env, nullptr, tg, 0, 7, 0, MP4J_F32, MP4J_SUM, 0, 16, 0) != 0, "bad thread id must fail");
+    CHECK(strstr(CALL(lastError)(&env, nullptr)->utf, "threadId") != nullptr, "error text: %s", CALL(lastError)(&env, nullptr)->utf);
+    CALL(tgroupDestroy)(&env, nullptr, tg);
+  }
   CHECK(g_open_critical.load() == 0, "critical regions left open");
   if (g_fail.load() == 0) printf("jni harness ok (p=%d)\n", p);
   return g_fail.load() ? 1 : 0;
