@@ -61,3 +61,13 @@ def test_lr_and_gbdt_consumers_match_single_process_reference(p):
         assert out["dense_ok"], (out["dense_ours"], out["dense_ref"])
         assert out["sparse_ok"], (out["sparse_ours"], out["sparse_ref"])
         assert out["gbdt_ok"], out["gbdt"]
+
+
+@pytest.mark.parametrize("T", [0, 3])
+def test_cuda_tensors_without_a_gpu_plane_go_through_the_host_plane(T):
+    """Ranks on several machines cannot share a GPU plane (one NVLink domain). MP4J_GPU_PLANE=0 puts a one-machine job
+    in that state: collectives on CUDA tensors are staged through the host plane, init_gpu refuses with a reason."""
+    fn = workers_gpu.staged_thread if T else workers_gpu.staged_process
+    res, code, logs = run_cluster(2, fn, (), threads=T, timeout=120, env={"MP4J_GPU_PLANE": "0"})
+    assert code == 0
+    assert all(all(x) if isinstance(x, list) else x for x in res)

@@ -99,3 +99,13 @@ def test_string_key_maps_native_and_generic(p, native, monkeypatch):
     monkeypatch.setenv("MP4J_NATIVE_MAPS", native)
     res, code, _ = run_cluster(p, workers.native_maps)
     assert res == [True] * p and code == 0
+
+
+def test_gpu_plane_decision_is_the_same_on_every_rank():
+    """The GPU plane is one NVLink domain; whether a job can have one is decided by all ranks together (hosts and
+    MP4J_GPU_PLANE gathered through the master). One rank opting out must switch every rank to the host-staged path,
+    otherwise the ranks would run different collectives."""
+    res, code, _ = run_cluster(3, workers.plane_blocker, (-1,), timeout=60)
+    assert code == 0 and all(r == "" for r in res), res
+    res, code, _ = run_cluster(3, workers.plane_blocker, (1,), timeout=60)
+    assert code == 0 and all(r == "MP4J_GPU_PLANE=0" for r in res), res

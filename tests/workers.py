@@ -435,3 +435,13 @@ def map_bridge_worker(comm, mask):
         tagged = map_bridge.MapKeyBridge.tag(ks, 5)
         out["tag"] = bool(((tagged.astype("uint64") >> 60) == 5).all()) and br.decode(tagged.tolist(), True) == shared + mine
     return out
+
+
+def plane_blocker(comm, off_rank):
+    """What every rank concludes about the GPU plane when ONE rank sets MP4J_GPU_PLANE=0 (off_rank < 0: nobody)."""
+    import os
+    if comm.getRank() == off_rank:
+        os.environ["MP4J_GPU_PLANE"] = "0"
+    else:
+        os.environ.pop("MP4J_GPU_PLANE", None)
+    return comm._gpu_plane_blocker()

@@ -344,3 +344,65 @@ def models_worker(comm):
     comm.gpu.check()
     comm.barrier()
     return out
+
+
+def staged_process(comm):
+    """CUDA tensors in a job WITHOUT a GPU plane (MP4J_GPU_PLANE=0 stands in for ranks on several machines): every
+    array collective goes device -> host plane -> device and gives the results of the host path."""
+    p, r = comm.getSlaveNum(), comm.getRank()
+    torch.cuda.set_device(0)
+    assert comm._gpu_plane_blocker() and comm._cuda_plane() is None
+    fop, dop = Operands.FLOAT_OPERAND(), Operands.DOUBLE_OPERAND()
+    n = 10007
+    x = torch.full((n,), float(r + 1), device="cuda")
+    comm.allreduceArray(x, fop, Operators.Float.SUM, 3, n - 2)
+    want = p * (p + 1) / 2
+    assert torch.all(x[3:n - 2] == want) and x[0] == r + 1 and x[n - 1] == r + 1
+    froms, tos = CommUtils.createProcessArrayFroms(n, p), CommUtils.createProcessArrayTos(n, p)
+    counts = [t - f for f, t in zip(froms, tos)]
+    y = torch.full((n,), float(r + 1), device="cuda", dtype=torch.float64)
+    comm.reduceScatterArray(y, dop, Operators.Double.MAX, 0, counts)
+    assert torch.all(y[froms[r]:tos[r]] == p)
+    comm.allgatherArray(y, dop, froms, tos)
+    assert torch.all(y == p)
+    z = torch.full((n,), float(r), device="cuda")
+    comm.broadcastArray(z, fop, 5, n - 5, p - 1)
+    assert torch.all(z[5:n - 5] == p - 1) and z[0] == r
+    g = torch.full((n,), float(r), device="cuda")
+    comm.gatherArray(g, fop, froms, tos, 0)
+    if r == 0:
+        assert all(torch.all(g[froms[q]:tos[q]] == q) for q in range(p))
+    s = torch.arange(n, device="cuda", dtype=torch.float32) if r == 1 else torch.zeros(n, device="cuda")
+    comm.scatterArray(s, fop, froms, tos, 1)
+    assert torch.equal(s[froms[r]:tos[r]].cpu(), torch.arange(froms[r], tos[r], dtype=torch.float32))
+    w = torch.full((n,), float(r + 1), device="cuda")
+    comm.reduceArray(w, fop, Operators.Float.SUM, 0, n, p - 1)
+    if r == p - 1:
+        assert torch.all(w == want)
+    try:
+        comm.init_gpu()
+        raise AssertionError("init_gpu must refuse")
+    except Exception as e:
+        assert "GPU plane cannot be set up" in str(e), e
+    return {"ok": True}
+
+
+def staged_thread(comm, tid):
+    """Thread-level collectives on CUDA tensors without a GPU plane: thread step with torch ops, process step staged."""
+    p, r, T = comm.getSlaveNum(), comm.getRank(), comm.getThreadNum()
+    torch.cuda.set_device(0)
+    fop = Operands.FLOAT_OPERAND()
+    n = 6001
+    x = torch.full((n,), float(r * T + tid + 1), device="cuda")
+    comm.allreduceArray(x, fop, Operators.Float.SUM, 1, n)
+    total = p * T * (p * T + 1) / 2
+    assert comm._cuda_plane() is None
+    assert torch.all(x[1:] == total) and x[0] == r * T + tid + 1, x[:3]
+    b = torch.full((n,), float(r * T + tid), device="cuda")
+    comm.broadcastArray(b, fop, 0, n, p - 1, T - 1)
+    assert torch.all(b == (p - 1) * T + T - 1)
+    m = torch.full((n,), float(r * T + tid), device="cuda")
+    comm.reduceArray(m, fop, Operators.Float.MAX, 0, n, 0, 1 % T)
+    if r == 0 and tid == 1 % T:
+        assert torch.all(m == p * T - 1)
+    return True

@@ -11,6 +11,7 @@ Three data paths behind one API:
 """
 import ctypes as C
 import os
+import socket
 import threading
 import time
 import traceback
@@ -118,6 +119,7 @@ class ProcessCommSlave:
         self._gpu = None
         self._lock = threading.RLock()
         self.stats = []  # per-collective records from the GPU plane
+        self._plane_blocker = None  # '' = the GPU plane can span this job, text = why not (decided on first use)
         self.info("this slave init finished!", onlyRank0=False)  # PCS:209
 
     # ------------------------------------------------------------------ identity / lifecycle
@@ -196,11 +198,68 @@ class ProcessCommSlave:
     # ------------------------------------------------------------------ GPU plane
     def init_gpu(self, device=None, heap_bytes=None, staging_bytes=None):
         """Sets up the GPU data plane: symmetric heap, peer mapping, signal pads, multicast.
-        Collective: every rank must call it. Called lazily by the first CUDA-tensor collective."""
+        Collective: every rank must call it. Called lazily by the first CUDA-tensor collective.
+        The plane is one NVLink domain: when the ranks of the job sit on several machines (or MP4J_GPU_PLANE=0)
+        it cannot be built and this raises; collectives on CUDA tensors then go through the host plane
+        (see _staged)."""
         if self._gpu is None:
+            why = self._gpu_plane_blocker()
+            if why:
+                raise Mp4jException("the GPU plane cannot be set up: " + why)
             from ..parallel.gpu_plane import GpuPlane
             self._gpu = GpuPlane(self, device=device, heap_bytes=heap_bytes, staging_bytes=staging_bytes)
         return self._gpu
+
+    def _gather_all_bytes(self, data):
+        """Every rank's byte string, in rank order, on every rank (through the master mailbox)."""
+        ptr, n = C.c_void_p(), C.c_size_t()
+        check(N.lib.mp4j_comm_gather_all(self._h, data, len(data), C.byref(ptr), C.byref(n)))
+        raw, out, off = N.take_bytes(ptr, n), [], 0
+        for _ in range(self._n):
+            ln = int.from_bytes(raw[off:off + 8], "little")
+            out.append(raw[off + 8:off + 8 + ln])
+            off += 8 + ln
+        return out
+
+    def _gpu_plane_blocker(self):
+        """Why the GPU plane cannot span this job ('' = it can). Decided once, by all ranks together (collective):
+        the plane maps every rank's heap into every other rank (VMM handles passed as file descriptors, NVLink
+        peer access), which works inside one machine only."""
+        if self._plane_blocker is None:
+            try:
+                with open("/proc/sys/kernel/random/boot_id") as f:
+                    boot = f.read().strip()
+            except OSError:
+                boot = ""
+            me = "%s|%s|%s" % (socket.gethostname(), boot, os.environ.get("MP4J_GPU_PLANE", "1"))
+            everyone = [b.decode() for b in self._gather_all_bytes(me.encode())] if self._n > 1 else [me]
+            machines = {e.rsplit("|", 1)[0] for e in everyone}
+            if any(e.rsplit("|", 1)[1] == "0" for e in everyone):
+                self._plane_blocker = "MP4J_GPU_PLANE=0"
+            elif len(machines) > 1:
+                self._plane_blocker = "the %d ranks run on %d machines and the plane is one NVLink domain" % (
+                    self._n, len(machines))
+            else:
+                self._plane_blocker = ""
+        return self._plane_blocker
+
+    def _cuda_plane(self):
+        """The GPU plane for a collective on CUDA tensors, or None when it cannot exist for this job."""
+        if self._gpu is not None:
+            return self._gpu
+        return None if self._gpu_plane_blocker() else self.init_gpu()
+
+    def _staged(self, t, fn, operator=None):
+        """Collective on a CUDA tensor without a GPU plane (ranks on several machines): device -> host copy, the
+        host-plane collective (shared memory inside a machine, TCP between machines), host -> device copy. The
+        multi-machine form of every array collective; a hierarchical form (NVLink kernels inside a machine, TCP
+        between machines) is the faster design this falls short of."""
+        if operator is not None and getattr(operator, "expr", None) and operator.code is None:
+            raise Mp4jException("device expressions need the GPU plane; use a predefined or a Python operator here")
+        h = t.detach().to("cpu")
+        fn(h)
+        t.copy_(h)
+        return t
 
     @property
     def gpu(self):
@@ -367,7 +426,10 @@ class ProcessCommSlave:
         if self._n == 1:
             return arrData
         if _is_cuda(arrData):
-            self.gpu.gather(arrData, operand, sendfroms, sendtos, rootRank)
+            plane = self._cuda_plane()
+            if plane is None:
+                return self._staged(arrData, lambda h: self.gatherArray(h, operand, sendfroms, sendtos, rootRank))
+            plane.gather(arrData, operand, sendfroms, sendtos, rootRank)
             return arrData
         a = self._native_host(arrData, operand, None)
         if a is not None:
@@ -402,7 +464,10 @@ class ProcessCommSlave:
         if self._n == 1:
             return arrData
         if _is_cuda(arrData):
-            self.gpu.allgather(arrData, operand, froms, tos)
+            plane = self._cuda_plane()
+            if plane is None:
+                return self._staged(arrData, lambda h: self.allgatherArray(h, operand, froms, tos))
+            plane.allgather(arrData, operand, froms, tos)
             return arrData
         a = self._native_host(arrData, operand, None)
         if a is not None:
@@ -435,7 +500,10 @@ class ProcessCommSlave:
         if self._n == 1:
             return arrData
         if _is_cuda(arrData):
-            self.gpu.broadcast(arrData, operand, from_, to, rootRank)
+            plane = self._cuda_plane()
+            if plane is None:
+                return self._staged(arrData, lambda h: self.broadcastArray(h, operand, from_, to, rootRank))
+            plane.broadcast(arrData, operand, from_, to, rootRank)
             return arrData
         a = self._native_host(arrData, operand, None)
         if a is not None:
@@ -477,7 +545,10 @@ class ProcessCommSlave:
         if self._n == 1:
             return arrData
         if _is_cuda(arrData):
-            self.gpu.scatter(arrData, operand, recvfroms, recvtos, rootRank)
+            plane = self._cuda_plane()
+            if plane is None:
+                return self._staged(arrData, lambda h: self.scatterArray(h, operand, recvfroms, recvtos, rootRank))
+            plane.scatter(arrData, operand, recvfroms, recvtos, rootRank)
             return arrData
         a = self._native_host(arrData, operand, None)
         if a is not None:
@@ -520,7 +591,11 @@ class ProcessCommSlave:
         if self._n == 1:
             return arrData
         if _is_cuda(arrData):
-            self.gpu.reduce_scatter(arrData, operand, operator, from_, counts)
+            plane = self._cuda_plane()
+            if plane is None:
+                return self._staged(arrData, lambda h: self.reduceScatterArray(h, operand, operator, from_, counts),
+                                    operator)
+            plane.reduce_scatter(arrData, operand, operator, from_, counts)
             return arrData
         a = self._native_host(arrData, operand, operator)
         if a is not None:
@@ -557,7 +632,11 @@ class ProcessCommSlave:
         if self._n == 1:
             return arrData
         if _is_cuda(arrData):
-            self.gpu.reduce(arrData, operand, operator, from_, to, rootRank)
+            plane = self._cuda_plane()
+            if plane is None:
+                return self._staged(arrData, lambda h: self.reduceArray(h, operand, operator, from_, to, rootRank),
+                                    operator)
+            plane.reduce(arrData, operand, operator, from_, to, rootRank)
             return arrData
         a = self._native_host(arrData, operand, operator)
         if a is not None:
@@ -594,7 +673,10 @@ class ProcessCommSlave:
         if self._n == 1:
             return arrData
         if _is_cuda(arrData):
-            self.gpu.allreduce(arrData, operand, operator, from_, to)
+            plane = self._cuda_plane()
+            if plane is None:
+                return self._staged(arrData, lambda h: self.allreduceArray(h, operand, operator, from_, to), operator)
+            plane.allreduce(arrData, operand, operator, from_, to)
             return arrData
         if self._gpu_host_ok(arrData, operand, operator):
             self._gpu.thread_allreduce_host([arrData], operand, operator, from_, to)
@@ -639,7 +721,10 @@ class ProcessCommSlave:
         if self._n == 1:
             return arrData
         if _is_cuda(arrData):
-            self.gpu.allreduce(arrData, operand, operator, 0, arrData.numel(), algo=N.ALGO_ONESHOT)
+            plane = self._cuda_plane()
+            if plane is None:
+                return self._staged(arrData, lambda h: self.allreduceArrayRpc(h, operand, operator), operator)
+            plane.allreduce(arrData, operand, operator, 0, arrData.numel(), algo=N.ALGO_ONESHOT)
             return arrData
         a = self._native_host(arrData, operand, operator)
         if a is not None:

@@ -73,6 +73,27 @@ class ThreadCommSlave:
     def init_gpu(self, *a, **kw):
         return self.processCommSlave.init_gpu(*a, **kw)
 
+    def _cuda_plane(self):
+        """The GPU plane for a thread-level collective on CUDA tensors, or None when the job cannot have one (ranks
+        on several machines: ProcessCommSlave._gpu_plane_blocker). Whether it can, and setting it up, are collective
+        over the ranks, so ONE thread does that for the process: on its first CUDA collective every thread passes
+        through this rendezvous once; afterwards it is a field read."""
+        pcs = self.processCommSlave
+        if not getattr(self._tls, "plane_known", False):
+            self.threadBarrier()
+            if self.getThreadId() == 0 and pcs._gpu is None:
+                try:
+                    pcs._cuda_plane()
+                    self._plane_exc = None
+                except BaseException as e:  # noqa: BLE001 - delivered to every thread below
+                    self._plane_exc = e
+            self.threadBarrier()
+            self._tls.plane_known = True
+            e = getattr(self, "_plane_exc", None)
+            if e is not None:
+                raise e if isinstance(e, Mp4jException) else Mp4jException(repr(e))
+        return pcs._gpu
+
     # ------------------------------------------------------------------ sync / logging
     def threadBarrier(self):
         check(N.lib.mp4j_tgroup_barrier(self._tg))
@@ -163,10 +184,11 @@ class ThreadCommSlave:
         if not _is_cuda(arrData):
             return False
         segs = [s for s in segs if s[1] > s[0]]
-        if not self.gpu.thread_segments_ok([arrData], operand, operator, len(segs)):
+        plane = self._cuda_plane()
+        if plane is None or not plane.thread_segments_ok([arrData], operand, operator, len(segs)):
             return False
 
-        self.gpu.thread_native_segments(self._tg, self.getThreadId(), root_thread, name, arrData, operand, operator, segs)
+        plane.thread_native_segments(self._tg, self.getThreadId(), root_thread, name, arrData, operand, operator, segs)
         return True
 
     def _real_root(self, rootRank, rootThreadId):
@@ -183,7 +205,11 @@ class ThreadCommSlave:
         if f >= t or len(arrs) == 1:
             return
         if _is_cuda(arrs[0]):
-            self.gpu.thread_reduce(arrs, operand, operator, f, t, dst)
+            plane = self.processCommSlave._gpu
+            if plane is not None:
+                plane.thread_reduce(arrs, operand, operator, f, t, dst)
+            else:
+                self._torch_reduce(arrs, operand, operator, f, t, dst)
             return
         order = [dst] + [i for i in range(len(arrs)) if i != dst]
         acc = self._host(arrs[dst], operand)
@@ -197,6 +223,22 @@ class ThreadCommSlave:
                                                   acc[f:t].ctypes.data, seg.ctypes.data, t - f))
             else:
                 acc[f:t] = merge(acc[f:t], src[f:t])
+
+    def _torch_reduce(self, arrs, operand, operator, f, t, dst):
+        """Thread reduce of CUDA tensors in a job without a GPU plane (ranks on several machines): torch ops for
+        the operators torch has, otherwise through host copies of the slices."""
+        import torch
+        fns = {N.SUM: torch.add, N.MAX: torch.maximum, N.MIN: torch.minimum, N.PROD: torch.mul}
+        acc = arrs[dst][f:t]
+        order = [i for i in range(len(arrs)) if i != dst]
+        fn = fns.get(operator.code) if operator.is_native else None
+        if fn is not None:
+            for i in order:
+                fn(acc, arrs[i][f:t], out=acc)
+            return
+        hs = [arrs[dst][f:t].cpu()] + [arrs[i][f:t].cpu() for i in order]
+        self._local_reduce(hs, operand, operator, 0, t - f, 0)
+        acc.copy_(hs[0])
 
     def _local_copy(self, dst, src, f, t, operand):
         if f >= t or dst is src:
@@ -389,9 +431,12 @@ class ThreadCommSlave:
 
         if _is_cuda(arrData):
             # CUDA tensors: the fused thread-reduce + inter-GPU + fan-out kernel, launched by thread 0 from the
-            # native rendezvous (every thread calls in with its own tensor)
-            self.gpu.thread_native_allreduce(self._tg, self.getThreadId(), arrData, operand, operator, from_, to)
-            return arrData
+            # native rendezvous (every thread calls in with its own tensor). Without a GPU plane (ranks on several
+            # machines) the generic composition below runs with the process step staged through the host plane.
+            plane = self._cuda_plane()
+            if plane is not None:
+                plane.thread_native_allreduce(self._tg, self.getThreadId(), arrData, operand, operator, from_, to)
+                return arrData
 
         def run(arrs):
             self._local_reduce(arrs, operand, operator, from_, to, 0)
