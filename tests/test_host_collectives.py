@@ -109,3 +109,15 @@ def test_gpu_plane_decision_is_the_same_on_every_rank():
     assert code == 0 and all(r == "" for r in res), res
     res, code, _ = run_cluster(3, workers.plane_blocker, (1,), timeout=60)
     assert code == 0 and all(r == "MP4J_GPU_PLANE=0" for r in res), res
+
+
+@pytest.mark.parametrize("p,transport,window", [(2, "shm", 64 << 10), (4, "shm", 64 << 10), (3, "shm", 64 << 20),
+                                                (3, "tcp", 0), (5, "shm", 128 << 10)])
+def test_ragged_ranges_against_numpy(p, transport, window, monkeypatch):
+    """Randomised ragged ranges (empty, unequal, with gaps) through every array collective. The small windows make
+    the shared-memory plane take many passes, each over a part of every slice."""
+    monkeypatch.setenv("MP4J_SHM", "1" if transport == "shm" else "0")
+    if window:
+        monkeypatch.setenv("MP4J_SHM_BYTES", str(window))
+    res, code, _ = run_cluster(p, workers.ragged_arrays, (1234 + p, 40_003), timeout=180)
+    assert res == [True] * p and code == 0, res

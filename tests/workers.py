@@ -445,3 +445,65 @@ def plane_blocker(comm, off_rank):
     else:
         os.environ.pop("MP4J_GPU_PLANE", None)
     return comm._gpu_plane_blocker()
+
+
+def ragged_arrays(comm, seed, n):
+    """All seven array collectives on doubles with RAGGED per-rank ranges (empty and very unequal slices, gaps between
+    them, from > 0) against numpy: what balanced splits never exercise - with a small shared-memory window the
+    multi-pass part arithmetic of the node plane, with MP4J_SHM=0 the ring's uneven segments."""
+    import numpy as np
+    from ytk_mp4j_b200 import Operands, Operators
+    p, r = comm.getSlaveNum(), comm.getRank()
+    rnd = np.random.RandomState(seed)  # the same stream on every rank
+    dop = Operands.DOUBLE_OPERAND()
+    ok = True
+    for it in range(6):
+        cuts = np.sort(rnd.randint(0, n, size=2 * p))
+        froms, tos = [int(x) for x in cuts[0::2]], [int(x) for x in cuts[1::2]]
+        k = int(rnd.randint(p))
+        tos[k] = froms[k]  # an empty slice
+        data = [rnd.randint(-50, 50, size=n).astype(np.float64) for _ in range(p)]
+        root = int(rnd.randint(p))
+        # allgather / gather / scatter
+        a = data[r].copy()
+        comm.allgatherArray(a, dop, froms, tos)
+        want = data[r].copy()
+        for q in range(p):
+            want[froms[q]:tos[q]] = data[q][froms[q]:tos[q]]
+        ok &= np.array_equal(a, want)
+        a = data[r].copy()
+        comm.gatherArray(a, dop, froms, tos, root)
+        if r == root:
+            ok &= np.array_equal(a, want)
+        a = data[r].copy()
+        comm.scatterArray(a, dop, froms, tos, root)
+        w2 = data[r].copy()
+        w2[froms[r]:tos[r]] = data[root][froms[r]:tos[r]]
+        ok &= np.array_equal(a, w2)
+        # reduce-scatter with ragged counts, allreduce / reduce / broadcast on a sub-range
+        counts = [int(x) for x in rnd.randint(0, n // p, size=p)]
+        counts[int(rnd.randint(p))] = 0
+        f0 = int(rnd.randint(0, n - sum(counts) + 1))
+        total = sum(data)
+        a = data[r].copy()
+        comm.reduceScatterArray(a, dop, Operators.Double.SUM, f0, counts)
+        lo = f0 + sum(counts[:r])
+        ok &= np.array_equal(a[lo:lo + counts[r]], total[lo:lo + counts[r]])
+        f, t = sorted(int(x) for x in rnd.randint(0, n + 1, size=2))
+        a = data[r].copy()
+        comm.allreduceArray(a, dop, Operators.Double.MAX, f, t)
+        w3 = data[r].copy()
+        w3[f:t] = np.maximum.reduce(data)[f:t]
+        ok &= np.array_equal(a, w3)
+        a = data[r].copy()
+        comm.reduceArray(a, dop, Operators.Double.SUM, f, t, root)
+        if r == root:
+            ok &= np.array_equal(a[f:t], total[f:t]) and np.array_equal(a[:f], data[r][:f]) and np.array_equal(a[t:], data[r][t:])
+        a = data[r].copy()
+        comm.broadcastArray(a, dop, f, t, root)
+        w4 = data[r].copy()
+        w4[f:t] = data[root][f:t]
+        ok &= np.array_equal(a, w4)
+        if not ok:
+            return "mismatch in iteration %d" % it
+    return True
