@@ -121,3 +121,11 @@ def test_ragged_ranges_against_numpy(p, transport, window, monkeypatch):
         monkeypatch.setenv("MP4J_SHM_BYTES", str(window))
     res, code, _ = run_cluster(p, workers.ragged_arrays, (1234 + p, 40_003), timeout=180)
     assert res == [True] * p and code == 0, res
+
+
+@pytest.mark.parametrize("p,T,transport", [(1, 3, "shm"), (2, 2, "shm"), (3, 3, "tcp"), (2, 4, "shm")])
+def test_ragged_thread_ranges_against_numpy(p, T, transport, monkeypatch):
+    monkeypatch.setenv("MP4J_SHM", "1" if transport == "shm" else "0")
+    monkeypatch.setenv("MP4J_SHM_BYTES", str(64 << 10))
+    res, code, _ = run_cluster(p, workers.ragged_thread_arrays, (77 + p * T, 20_011), threads=T, timeout=180)
+    assert code == 0 and all(all(x is True for x in row) for row in res), res

@@ -507,3 +507,67 @@ def ragged_arrays(comm, seed, n):
         if not ok:
             return "mismatch in iteration %d" % it
     return True
+
+
+def ragged_thread_arrays(comm, tid, seed, n):
+    """ThreadCommSlave's seven array collectives with ragged [slaveNum][threadNum] ranges / counts (empty slices,
+    gaps, non-zero roots) on doubles against numpy - the native mp4j::ThreadComm paths."""
+    import numpy as np
+    from ytk_mp4j_b200 import Operands, Operators
+    p, r, T = comm.getSlaveNum(), comm.getRank(), comm.getThreadNum()
+    rnd = np.random.RandomState(seed)  # the same stream on every thread of every rank
+    dop = Operands.DOUBLE_OPERAND()
+    bad = []  # never leave early: the other threads would wait for this one in the next collective
+    for it in range(5):
+        cuts = np.sort(rnd.randint(0, n, size=2 * p * T))
+        lo = [[int(cuts[2 * (q * T + t)]) for t in range(T)] for q in range(p)]
+        hi = [[int(cuts[2 * (q * T + t) + 1]) for t in range(T)] for q in range(p)]
+        eq, et = int(rnd.randint(p)), int(rnd.randint(T))
+        hi[eq][et] = lo[eq][et]  # an empty slice
+        data = [[rnd.randint(-50, 50, size=n).astype(np.float64) for _ in range(T)] for _ in range(p)]
+        root, rt = int(rnd.randint(p)), int(rnd.randint(T))
+        mine = data[r][tid]
+        gathered = mine.copy()
+        for q in range(p):
+            for t in range(T):
+                gathered[lo[q][t]:hi[q][t]] = data[q][t][lo[q][t]:hi[q][t]]
+        # only the slices are specified: between the thread slices of a process the reference ships whatever its
+        # delegate thread holds (process ranges are [lo[q][0], hi[q][T-1]), TCS:621-676), the GPU kernel ships nothing
+        def slices_ok(x):
+            return all(np.array_equal(x[lo[q][t]:hi[q][t]], gathered[lo[q][t]:hi[q][t]]) for q in range(p) for t in range(T))
+        a = mine.copy()
+        comm.allgatherArray(a, dop, lo, hi)
+        if not slices_ok(a):
+            bad.append("allgather %d" % it)
+        a = mine.copy()
+        comm.gatherArray(a, dop, lo, hi, root, rt)
+        if r == root and tid == rt and not slices_ok(a):
+            bad.append("gather %d" % it)
+        a = mine.copy()
+        comm.scatterArray(a, dop, lo, hi, root, rt)
+        if not np.array_equal(a[lo[r][tid]:hi[r][tid]], data[root][rt][lo[r][tid]:hi[r][tid]]):
+            bad.append("scatter %d" % it)
+        counts = [[int(x) for x in rnd.randint(0, n // (p * T), size=T)] for _ in range(p)]
+        counts[int(rnd.randint(p))][int(rnd.randint(T))] = 0
+        tot_cnt = sum(sum(c) for c in counts)
+        f0 = int(rnd.randint(0, n - tot_cnt + 1))
+        total = sum(sum(row) for row in data)
+        a = mine.copy()
+        comm.reduceScatterArray(a, dop, Operators.Double.SUM, f0, counts)
+        off = f0 + sum(sum(c) for c in counts[:r]) + sum(counts[r][:tid])
+        if not np.array_equal(a[off:off + counts[r][tid]], total[off:off + counts[r][tid]]):
+            bad.append("reduce-scatter %d" % it)
+        f, t = sorted(int(x) for x in rnd.randint(0, n + 1, size=2))
+        a = mine.copy()
+        comm.allreduceArray(a, dop, Operators.Double.SUM, f, t)
+        if not (np.array_equal(a[f:t], total[f:t]) and np.array_equal(a[:f], mine[:f]) and np.array_equal(a[t:], mine[t:])):
+            bad.append("allreduce %d" % it)
+        a = mine.copy()
+        comm.reduceArray(a, dop, Operators.Double.MAX, f, t, root, rt)
+        if r == root and tid == rt and not np.array_equal(a[f:t], np.maximum.reduce([x for row in data for x in row])[f:t]):
+            bad.append("reduce %d" % it)
+        a = mine.copy()
+        comm.broadcastArray(a, dop, f, t, root, rt)
+        if not np.array_equal(a[f:t], data[root][rt][f:t]):
+            bad.append("broadcast %d" % it)
+    return bad or True
