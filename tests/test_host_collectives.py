@@ -129,3 +129,12 @@ def test_ragged_thread_ranges_against_numpy(p, T, transport, monkeypatch):
     monkeypatch.setenv("MP4J_SHM_BYTES", str(64 << 10))
     res, code, _ = run_cluster(p, workers.ragged_thread_arrays, (77 + p * T, 20_011), threads=T, timeout=180)
     assert code == 0 and all(all(x is True for x in row) for row in res), res
+
+
+@pytest.mark.parametrize("p,transport", [(20, "shm"), (36, "tcp")])
+def test_many_slaves(p, transport, monkeypatch):
+    """More ranks than cores; 36 is beyond the shared-memory plane's 32-rank masks, so every rank must fall back to
+    the TCP ring together."""
+    monkeypatch.setenv("MP4J_SHM", "1")
+    res, code, _ = run_cluster(p, workers.many_slaves, (), timeout=240)
+    assert code == 0 and res == [True] * p

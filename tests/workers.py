@@ -571,3 +571,16 @@ def ragged_thread_arrays(comm, tid, seed, n):
         if not np.array_equal(a[f:t], data[root][rt][f:t]):
             bad.append("broadcast %d" % it)
     return bad or True
+
+
+def many_slaves(comm):
+    """Barrier + allreduce in a job with more ranks than cores (the reference runs on clusters of tens of slaves)."""
+    import numpy as np
+    from ytk_mp4j_b200 import Operands, Operators
+    for _ in range(5):
+        comm.barrier()
+    a = np.arange(5003, dtype=np.float64)
+    comm.allreduceArray(a, Operands.DOUBLE_OPERAND(), Operators.Double.SUM, 0, 5003)
+    m = comm.allreduceMap({"k%d" % comm.getRank(): 1, "all": 1}, Operands.INT_OPERAND(), Operators.Int.SUM)
+    return bool(np.array_equal(a, np.arange(5003) * comm.getSlaveNum())) and m["all"] == comm.getSlaveNum() \
+        and len(m) == comm.getSlaveNum() + 1
