@@ -109,6 +109,8 @@ def test_gpu_plane_decision_is_the_same_on_every_rank():
     assert code == 0 and all(r == "" for r in res), res
     res, code, _ = run_cluster(3, workers.plane_blocker, (1,), timeout=60)
     assert code == 0 and all(r == "MP4J_GPU_PLANE=0" for r in res), res
+    res, code, _ = run_cluster(9, workers.plane_blocker, (-1,), timeout=120)  # more ranks than one NVLink domain holds
+    assert code == 0 and all("at most 8" in r for r in res), res
 
 
 @pytest.mark.parametrize("p,transport,window", [(2, "shm", 64 << 10), (4, "shm", 64 << 10), (3, "shm", 64 << 20),

@@ -236,6 +236,9 @@ class ProcessCommSlave:
             machines = {e.rsplit("|", 1)[0] for e in everyone}
             if any(e.rsplit("|", 1)[1] == "0" for e in everyone):
                 self._plane_blocker = "MP4J_GPU_PLANE=0"
+            elif self._n > N.MAX_RANKS:
+                self._plane_blocker = "the job has %d ranks and the plane spans at most %d (one NVLink domain)" % (
+                    self._n, N.MAX_RANKS)
             elif len(machines) > 1:
                 self._plane_blocker = "the %d ranks run on %d machines and the plane is one NVLink domain" % (
                     self._n, len(machines))
