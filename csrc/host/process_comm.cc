@@ -1,14 +1,47 @@
 #include "process_comm.h"
 
 #include <stdlib.h>
+#include <sys/socket.h>
 #include <unistd.h>
 
 #include <algorithm>
+#include <exception>
+#include <thread>
 
 namespace mp4j {
 
 namespace {
 constexpr size_t kChunk = 1 << 20;  // pipeline granularity of reduce-on-receive
+// ring steps moving at least this much send on a helper thread (MP4J_TCP_DUPLEX_MIN_BYTES; 0 = never)
+const size_t kDuplexMin = [] {
+  const char* e = getenv("MP4J_TCP_DUPLEX_MIN_BYTES");
+  const size_t v = e ? (size_t)strtoull(e, nullptr, 10) : (size_t)(4 << 20);
+  return v ? v : (size_t)-1;
+}();
+
+// One full-duplex ring step: `send_len` bytes leave through `send_fd` on a helper thread while `receive` runs on the
+// calling thread. If either side fails the socket is shut down so that the other side wakes up (the job is over
+// anyway: any failed collective ends it), and the first error is rethrown.
+template <typename F>
+void duplex_step(int send_fd, const void* send_buf, size_t send_len, F&& receive) {
+  std::exception_ptr send_err;
+  std::thread sender([&] {
+    try {
+      if (send_len) net::send_all(send_fd, send_buf, send_len);
+    } catch (...) {
+      send_err = std::current_exception();
+    }
+  });
+  try {
+    receive();
+  } catch (...) {
+    ::shutdown(send_fd, SHUT_RDWR);
+    sender.join();
+    throw;
+  }
+  sender.join();
+  if (send_err) std::rethrow_exception(send_err);
+}
 
 int env_int(const char* name, int dflt) {
   const char* v = getenv(name);
@@ -137,6 +170,19 @@ void ProcessComm::reduce_scatter(void* arr, int dtype, int op, int64_t from, con
     char* rp = base + froms[rseg] * es;
     size_t so = 0, ro = 0;
     const size_t chunk = kChunk / es * es;
+    if (sbytes + rbytes >= kDuplexMin) {
+      // big step: the outgoing segment (reduced in the previous step, not touched in this one) leaves on a helper
+      // thread while this thread receives and reduces chunk by chunk - two cores move the bytes instead of one
+      // poll loop doing send copy, receive copy and the reduction in turn
+      duplex_step(sfd, sp, sbytes, [&] {
+        for (; ro < rbytes; ro += chunk) {
+          const size_t rl = std::min(chunk, rbytes - ro);
+          if (!net::recv_all(rfd, scratch_.data(), rl)) throw Error("peer closed during reduce-scatter");
+          host_reduce_into(dtype, op, rp + ro, scratch_.data(), rl / es);  // op(local, incoming) DOP:196
+        }
+      });
+      continue;
+    }
     while (so < sbytes || ro < rbytes) {
       size_t sl = std::min(chunk, sbytes - so), rl = std::min(chunk, rbytes - ro);
       net::sendrecv(sfd, sp + so, sl, rfd, scratch_.data(), rl);
@@ -163,8 +209,14 @@ void ProcessComm::allgather(void* arr, int dtype, const int64_t* froms, const in
   for (int s = 0; s < n_ - 1; ++s) {
     int sseg = ((rank_ - s) % n_ + n_) % n_;
     int rseg = ((rank_ - 1 - s) % n_ + n_) % n_;
-    net::sendrecv(sfd, base + froms[sseg] * es, (size_t)(tos[sseg] - froms[sseg]) * es, rfd,
-                  base + froms[rseg] * es, (size_t)(tos[rseg] - froms[rseg]) * es);
+    const size_t sbytes = (size_t)(tos[sseg] - froms[sseg]) * es, rbytes = (size_t)(tos[rseg] - froms[rseg]) * es;
+    if (sbytes + rbytes >= kDuplexMin) {
+      duplex_step(sfd, base + froms[sseg] * es, sbytes, [&] {
+        if (rbytes && !net::recv_all(rfd, base + froms[rseg] * es, rbytes)) throw Error("peer closed during allgather");
+      });
+      continue;
+    }
+    net::sendrecv(sfd, base + froms[sseg] * es, sbytes, rfd, base + froms[rseg] * es, rbytes);
   }
 }
 

@@ -13,8 +13,9 @@ import build as mp4j_build  # noqa: E402
 
 
 def _run(exe, *args, shm="1"):
+    # the TCP ring sends big steps on a helper thread: a 16 KiB threshold puts that path under the sanitizers too
     env = dict(os.environ, TSAN_OPTIONS="halt_on_error=0 exitcode=66", ASAN_OPTIONS="detect_leaks=1", MP4J_SHM=shm,
-               MP4J_SHM_BYTES=str(1 << 20))
+               MP4J_SHM_BYTES=str(1 << 20), MP4J_TCP_DUPLEX_MIN_BYTES=str(16 << 10))
     import tempfile
     with tempfile.TemporaryDirectory(prefix="mp4j-") as cwd:  # the master drops kill_<port>.sh into its cwd
         return subprocess.run([exe] + [str(a) for a in args], capture_output=True, text=True, timeout=300, env=env, cwd=cwd)
