@@ -32,6 +32,25 @@ void ThreadComm::allreduce(ProcessComm& pc, int tid, void* arr, int dtype, int o
   const int64_t n = to - from, per = (n + T - 1) / T;
   const int64_t lo = from + std::min<int64_t>(n, (int64_t)tid * per), hi = from + std::min<int64_t>(n, (int64_t)(tid + 1) * per);
   const int64_t blk = (int64_t)(32768 / es);
+  if (pc.size() == 1) {
+    // One process: there is no process step between combining and fanning out, so every thread finishes its slice
+    // in one pass - reduce a cache-sized block of the T arrays (thread-id order) into a local buffer and write it
+    // straight into all T arrays: T reads + T writes per element instead of T reads + 1 write, then T - 1 reads +
+    // T - 1 writes for the copy-out.
+    thread_local std::vector<char> blockbuf;
+    if (blockbuf.size() < 32768) blockbuf.resize(32768);
+    char* o = blockbuf.data();
+    for (int64_t b0 = lo; b0 < hi; b0 += blk) {
+      const int64_t b1 = std::min(hi, b0 + blk);
+      const size_t bb = (size_t)(b1 - b0) * es;
+      memcpy(o, acc + b0 * es, bb);
+      for (int t = 1; t < T; ++t)
+        host_reduce_into(dtype, op, o, (const char*)(uintptr_t)tg.get_slot(t, 0) + b0 * es, (size_t)(b1 - b0));
+      for (int t = 0; t < T; ++t) memcpy((char*)(uintptr_t)tg.get_slot(t, 0) + b0 * es, o, bb);
+    }
+    tg.barrier();  // nobody returns while another thread still writes into its array
+    return;
+  }
   for (int64_t b0 = lo; b0 < hi; b0 += blk) {
     const int64_t b1 = std::min(hi, b0 + blk);
     for (int t = 1; t < T; ++t)
