@@ -339,6 +339,28 @@ void ProcessComm::allreduce(void* arr, int dtype, int op, int64_t from, int64_t 
   allgather(arr, dtype, froms.data(), tos.data());
 }
 
+// allreduce as the process step of a thread-level collective: ALL T threads of the process call it with the same
+// arguments (arr = the delegate thread's array). On the shared-memory plane the T threads share the copies and the
+// reduction (ShmPlane::grs_team); on the TCP ring thread 0 runs the collective and the others return at once - the
+// caller's next thread barrier is what they wait at. Returns true if the calling thread took part in the data movement.
+bool ProcessComm::allreduce_team(void* arr, int dtype, int op, int64_t from, int64_t to, int tid, int T,
+                                 const std::function<void()>& team_sync) {
+  if (n_ == 1) return false;
+  if (!shm_ || T == 1) {
+    if (tid == 0) allreduce(arr, dtype, op, from, to);
+    return tid == 0;
+  }
+  check_from_to(from, to);
+  if (!op_valid_for(dtype, op) || op == MP4J_COPY) throw Error("invalid operator for dtype");
+  std::vector<int64_t> froms(n_), tos(n_);
+  balanced_split(from, to, n_, froms.data(), tos.data());
+  std::vector<uint32_t> sm(n_, all_mask()), dm(n_, all_mask());
+  std::unique_lock<std::mutex> lk(op_mu_, std::defer_lock);
+  if (tid == 0) lk.lock();  // one collective at a time on a communicator; the team is one collective
+  shm_->grs_team(arr, dtype, op, froms.data(), tos.data(), sm.data(), dm.data(), tid, T, &team_sync);
+  return true;
+}
+
 void ProcessComm::allreduce_rpc(void* arr, int dtype, int op, int64_t n) {
   if (n_ == 1) return;
   if (!op_valid_for(dtype, op) || op == MP4J_COPY) throw Error("invalid operator for dtype");

@@ -12,6 +12,7 @@
 // The GPU data plane (csrc/gpu) attaches to this object for handle brokerage.
 #pragma once
 #include <condition_variable>
+#include <functional>
 #include <memory>
 #include <mutex>
 #include <string>
@@ -53,6 +54,8 @@ class ProcessComm {
   void broadcast(void* arr, int dtype, int64_t from, int64_t to, int root);
   void reduce(void* arr, int dtype, int op, int64_t from, int64_t to, int root);
   void allreduce(void* arr, int dtype, int op, int64_t from, int64_t to);
+  bool allreduce_team(void* arr, int dtype, int op, int64_t from, int64_t to, int tid, int T,
+                      const std::function<void()>& team_sync);
   // small-message allreduce through the master mailbox (PCS:1776-1799, SRV:373-497)
   void allreduce_rpc(void* arr, int dtype, int op, int64_t n);
 

@@ -224,6 +224,40 @@ void ShmPlane::barrier() {
 
 void ShmPlane::grs(void* arr, int dtype, int op, const int64_t* lo, const int64_t* hi, const uint32_t* src_mask,
                    const uint32_t* dst_mask) {
+  grs_team(arr, dtype, op, lo, hi, src_mask, dst_mask, 0, 1, nullptr);
+}
+
+// The same pass executed by a TEAM of T threads of this process (ThreadCommSlave: the process step of a thread-level
+// collective, which one delegate thread used to run alone while T - 1 cores waited). All T threads call with the same
+// arguments; every copy and every reduction is cut into T parts, thread `tid` does part `tid`; thread 0 meets the
+// other processes at the barriers, bracketed by team_sync (the thread barrier). A failed process barrier is
+// delivered to all T threads.
+void ShmPlane::grs_team(void* arr, int dtype, int op, const int64_t* lo, const int64_t* hi, const uint32_t* src_mask,
+                        const uint32_t* dst_mask, int tid, int T, const std::function<void()>* team_sync) {
+  auto tsync = [&] {
+    if (T > 1) (*team_sync)();
+  };
+  auto xbarrier = [&] {
+    if (T == 1) return barrier();
+    tsync();
+    if (tid == 0) {
+      try {
+        barrier();
+        team_failed_ = false;
+      } catch (const std::exception& e) {
+        team_failed_ = true;
+        team_msg_ = e.what();
+      }
+    }
+    tsync();
+    if (team_failed_) throw Error(team_msg_);
+  };
+  // this thread's part of [l, h)
+  auto part = [&](int64_t* l, int64_t* h) {
+    const int64_t len = *h - *l, a = *l + len * tid / T, b = *l + len * (tid + 1) / T;
+    *l = a;
+    *h = b;
+  };
   const size_t es = dtype_size(dtype);
   if (es == 0) throw Error("unknown dtype");
   int64_t span_lo = INT64_MAX, span_hi = INT64_MIN;
@@ -259,6 +293,7 @@ void ShmPlane::grs(void* arr, int dtype, int op, const int64_t* lo, const int64_
   }
   std::vector<char> acc;  // private accumulator for slices whose result goes back into my window
   for (int64_t k = 0; k < passes; ++k) {
+    tsync();  // thread 0 has flipped half_ (end of the previous pass / call) before anybody reads it
     const size_t hoff = kHeaderBytes + (size_t)half_ * half_bytes_;
     // part k of slice q: [pl(q), ph(q)); its place in everybody's window: woff[q]
     auto pl = [&](int q) { return std::min(hi[q], lo[q] + k * sub[(size_t)q]); };
@@ -269,17 +304,19 @@ void ShmPlane::grs(void* arr, int dtype, int op, const int64_t* lo, const int64_
     // ---- phase 1: publish my contributions
     for (int q = 0; q < n_; ++q) {
       if (!((src_mask[q] >> rank_) & 1u)) continue;
-      const int64_t l = pl(q), h = ph(q);
+      int64_t l = pl(q), h = ph(q);
       if (l >= h) continue;
       if (op == MP4J_COPY && dst_mask[q] == (1u << rank_)) continue;  // my own slice to myself
       if (op != MP4J_COPY && q == rank_) continue;  // the slice I reduce myself: read from my array in phase 2
-      memcpy(win(rank_, q, l), base + l * es, (size_t)(h - l) * es);
+      part(&l, &h);
+      if (l < h) memcpy(win(rank_, q, l), base + l * es, (size_t)(h - l) * es);
     }
-    barrier();
+    xbarrier();
     // ---- phase 2: the owner reduces its slice over the source windows, ascending rank order
     if (op != MP4J_COPY) {
       const int q = rank_;
-      const int64_t l = pl(q), h = ph(q);
+      int64_t l = pl(q), h = ph(q);
+      part(&l, &h);
       if (l < h && src_mask[q] != 0) {
         const bool to_me = (dst_mask[q] >> q) & 1u;
         const bool to_others = (dst_mask[q] & ~(1u << q)) != 0;
@@ -304,12 +341,12 @@ void ShmPlane::grs(void* arr, int dtype, int op, const int64_t* lo, const int64_
           if (to_others) memcpy(win(rank_, q, b0), o, bb);
         }
       }
-      if (need_b2) barrier();
+      if (need_b2) xbarrier();
     }
     // ---- phase 3: fetch the slices I am a destination of
     for (int q = 0; q < n_; ++q) {
       if (!((dst_mask[q] >> rank_) & 1u)) continue;
-      const int64_t l = pl(q), h = ph(q);
+      int64_t l = pl(q), h = ph(q);
       if (l >= h || src_mask[q] == 0) continue;
       int from_rank;
       if (op != MP4J_COPY) {
@@ -319,9 +356,10 @@ void ShmPlane::grs(void* arr, int dtype, int op, const int64_t* lo, const int64_
         from_rank = __builtin_ctz(src_mask[q]);
         if (from_rank == rank_) continue;  // my own data
       }
-      memcpy(base + l * es, win(from_rank, q, l), (size_t)(h - l) * es);
+      part(&l, &h);
+      if (l < h) memcpy(base + l * es, win(from_rank, q, l), (size_t)(h - l) * es);
     }
-    half_ ^= 1;  // the other half serves the next chunk / call: no closing barrier needed
+    if (tid == 0) half_ ^= 1;  // the other half serves the next chunk / call: no closing barrier needed
   }
 }
 

@@ -17,6 +17,7 @@
 #include <stddef.h>
 #include <stdint.h>
 
+#include <functional>
 #include <memory>
 #include <string>
 #include <vector>
@@ -37,6 +38,9 @@ class ShmPlane {
   // into the arrays of the ranks in dst_mask[q]. op == MP4J_COPY: no reduction (src_mask has one bit).
   void grs(void* arr, int dtype, int op, const int64_t* lo, const int64_t* hi, const uint32_t* src_mask,
            const uint32_t* dst_mask);
+  // grs executed by a team of T threads of this process (see shm_plane.cc); team_sync = their thread barrier
+  void grs_team(void* arr, int dtype, int op, const int64_t* lo, const int64_t* hi, const uint32_t* src_mask,
+                const uint32_t* dst_mask, int tid, int T, const std::function<void()>* team_sync);
   void barrier();
   size_t window_bytes() const { return half_bytes_ * 2; }
 
@@ -49,6 +53,8 @@ class ShmPlane {
   int half_ = 0;            // which half of the windows the next chunk uses (same on every rank)
   double timeout_s_ = 600.0;
   double spin_us_ = 0.0;    // how long a barrier spins before it sleeps (0 when cores are scarce)
+  bool team_failed_ = false;  // outcome of thread 0's process barrier, read by its team after the thread barrier
+  std::string team_msg_;
 };
 
 }  // namespace mp4j

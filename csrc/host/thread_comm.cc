@@ -4,6 +4,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <functional>
 #include <vector>
 
 #include "../../include/mp4j_types.h"
@@ -57,12 +58,16 @@ void ThreadComm::allreduce(ProcessComm& pc, int tid, void* arr, int dtype, int o
       host_reduce_into(dtype, op, acc + b0 * es, (const char*)(uintptr_t)tg.get_slot(t, 0) + b0 * es, (size_t)(b1 - b0));
   }
   tg.barrier();
-  if (tid == 0) {
+  {
+    // the process step: on the shared-memory plane all T threads share it, on the TCP ring thread 0 runs it
+    const std::function<void()> sync = [&tg] { tg.barrier(); };
     try {
-      pc.allreduce(acc, dtype, op, from, to);
+      pc.allreduce_team(acc, dtype, op, from, to, tid, T, sync);
     } catch (const std::exception& e) {
-      tg.set_slot(0, 1, 1);
-      error_ = e.what();
+      if (tid == 0) {  // a team fails as one (every thread gets the same error); thread 0 records it
+        tg.set_slot(0, 1, 1);
+        error_ = e.what();
+      }
     }
   }
   tg.barrier();
