@@ -11,6 +11,24 @@
 namespace mp4j {
 
 namespace {
+// The team the calling thread belongs to while it executes the process step of a thread-level collective
+// (ProcessComm::TeamScope); null for an ordinary call.
+thread_local const ProcessComm::Team* tl_team = nullptr;
+
+// op_mu_ serialises the collectives of a communicator. A team is ONE collective: its thread 0 takes the lock, the
+// followers do not (they would wait for thread 0, which waits for them at the team's first thread barrier).
+struct OpGuard {
+  std::mutex& mu;
+  const bool own;
+  explicit OpGuard(std::mutex& m) : mu(m), own(!(tl_team && tl_team->tid != 0)) {
+    if (own) mu.lock();
+  }
+  ~OpGuard() {
+    if (own) mu.unlock();
+  }
+};
+bool team_follower() { return tl_team && tl_team->tid != 0; }
+
 constexpr size_t kChunk = 1 << 20;  // pipeline granularity of reduce-on-receive
 // ring steps moving at least this much send on a helper thread (MP4J_TCP_DUPLEX_MIN_BYTES; 0 = never)
 const size_t kDuplexMin = [] {
@@ -145,19 +163,29 @@ void ProcessComm::close(int code) {
 
 // ------------------------------------------------------------------ host collectives
 
+ProcessComm::TeamScope::TeamScope(const Team* t) { tl_team = (t && t->T > 1) ? t : nullptr; }
+ProcessComm::TeamScope::~TeamScope() { tl_team = nullptr; }
+
+void ProcessComm::shm_run(void* arr, int dtype, int op, const int64_t* lo, const int64_t* hi, const uint32_t* src_mask,
+                          const uint32_t* dst_mask) {
+  if (tl_team) shm_->grs_team(arr, dtype, op, lo, hi, src_mask, dst_mask, tl_team->tid, tl_team->T, tl_team->sync);
+  else shm_->grs(arr, dtype, op, lo, hi, src_mask, dst_mask);
+}
+
 void ProcessComm::reduce_scatter(void* arr, int dtype, int op, int64_t from, const int64_t* counts) {
   check_from_counts(from, counts, n_);
   if (n_ == 1) return;  // PCS:1179
   if (!op_valid_for(dtype, op) || op == MP4J_COPY) throw Error("invalid operator for dtype");
-  std::lock_guard<std::mutex> lk(op_mu_);
+  OpGuard lk(op_mu_);
   const size_t es = dtype_size(dtype);
   std::vector<int64_t> froms(n_), tos(n_);
   froms_tos_from_counts(from, counts, n_, froms.data(), tos.data());
   if (shm_) {
     std::vector<uint32_t> sm(n_, all_mask()), dm(n_);
     for (int q = 0; q < n_; ++q) dm[q] = 1u << q;
-    return shm_->grs(arr, dtype, op, froms.data(), tos.data(), sm.data(), dm.data());
+    return shm_run(arr, dtype, op, froms.data(), tos.data(), sm.data(), dm.data());
   }
+  if (team_follower()) return;  // the ring is thread 0's
   int next = (rank_ + 1) % n_, prev = (rank_ - 1 + n_) % n_;
   int sfd = out_fd(next), rfd = in_fd(prev);
   char* base = (char*)arr;
@@ -196,13 +224,14 @@ void ProcessComm::reduce_scatter(void* arr, int dtype, int op, int64_t from, con
 void ProcessComm::allgather(void* arr, int dtype, const int64_t* froms, const int64_t* tos) {
   check_froms_tos(froms, tos, n_);
   if (n_ == 1) return;  // PCS:630
-  std::lock_guard<std::mutex> lk(op_mu_);
+  OpGuard lk(op_mu_);
   const size_t es = dtype_size(dtype);
   if (shm_) {
     std::vector<uint32_t> sm(n_), dm(n_, all_mask());
     for (int q = 0; q < n_; ++q) sm[q] = 1u << q;
-    return shm_->grs(arr, dtype, MP4J_COPY, froms, tos, sm.data(), dm.data());
+    return shm_run(arr, dtype, MP4J_COPY, froms, tos, sm.data(), dm.data());
   }
+  if (team_follower()) return;  // the ring is thread 0's
   int next = (rank_ + 1) % n_, prev = (rank_ - 1 + n_) % n_;
   int sfd = out_fd(next), rfd = in_fd(prev);
   char* base = (char*)arr;
@@ -224,13 +253,14 @@ void ProcessComm::gather(void* arr, int dtype, const int64_t* froms, const int64
   check_froms_tos(froms, tos, n_);
   if (root < 0 || root >= n_) throw Error("root rank out of range");
   if (n_ == 1) return;  // PCS:545
-  std::lock_guard<std::mutex> lk(op_mu_);
+  OpGuard lk(op_mu_);
   const size_t es = dtype_size(dtype);
   if (shm_) {
     std::vector<uint32_t> sm(n_), dm(n_, 1u << root);
     for (int q = 0; q < n_; ++q) sm[q] = 1u << q;
-    return shm_->grs(arr, dtype, MP4J_COPY, froms, tos, sm.data(), dm.data());
+    return shm_run(arr, dtype, MP4J_COPY, froms, tos, sm.data(), dm.data());
   }
+  if (team_follower()) return;  // the tree is thread 0's
   char* base = (char*)arr;
   int vr = (rank_ - root + n_) % n_;
   auto real = [&](int v) { return (v + root) % n_; };
@@ -257,13 +287,14 @@ void ProcessComm::scatter(void* arr, int dtype, const int64_t* froms, const int6
   check_froms_tos(froms, tos, n_);
   if (root < 0 || root >= n_) throw Error("root rank out of range");
   if (n_ == 1) return;
-  std::lock_guard<std::mutex> lk(op_mu_);
+  OpGuard lk(op_mu_);
   const size_t es = dtype_size(dtype);
   if (shm_) {
     std::vector<uint32_t> sm(n_, 1u << root), dm(n_);
     for (int q = 0; q < n_; ++q) dm[q] = 1u << q;
-    return shm_->grs(arr, dtype, MP4J_COPY, froms, tos, sm.data(), dm.data());
+    return shm_run(arr, dtype, MP4J_COPY, froms, tos, sm.data(), dm.data());
   }
+  if (team_follower()) return;  // the tree is thread 0's
   char* base = (char*)arr;
   int vr = (rank_ - root + n_) % n_;
   auto real = [&](int v) { return (v + root) % n_; };
@@ -298,9 +329,9 @@ void ProcessComm::broadcast(void* arr, int dtype, int64_t from, int64_t to, int 
   balanced_split(from, to, n_, froms.data(), tos.data());  // PCS:760-767
   if (shm_) {  // one pass: everybody copies out of the root's window
     if (root < 0 || root >= n_) throw Error("root rank out of range");
-    std::lock_guard<std::mutex> lk(op_mu_);
+    OpGuard lk(op_mu_);
     std::vector<uint32_t> sm(n_, 1u << root), dm(n_, all_mask());
-    return shm_->grs(arr, dtype, MP4J_COPY, froms.data(), tos.data(), sm.data(), dm.data());
+    return shm_run(arr, dtype, MP4J_COPY, froms.data(), tos.data(), sm.data(), dm.data());
   }
   scatter(arr, dtype, froms.data(), tos.data(), root);
   allgather(arr, dtype, froms.data(), tos.data());
@@ -315,9 +346,9 @@ void ProcessComm::reduce(void* arr, int dtype, int op, int64_t from, int64_t to,
   if (shm_) {  // one pass: owners reduce, the root collects
     if (root < 0 || root >= n_) throw Error("root rank out of range");
     if (!op_valid_for(dtype, op) || op == MP4J_COPY) throw Error("invalid operator for dtype");
-    std::lock_guard<std::mutex> lk(op_mu_);
+    OpGuard lk(op_mu_);
     std::vector<uint32_t> sm(n_, all_mask()), dm(n_, 1u << root);
-    return shm_->grs(arr, dtype, op, froms.data(), tos.data(), sm.data(), dm.data());
+    return shm_run(arr, dtype, op, froms.data(), tos.data(), sm.data(), dm.data());
   }
   reduce_scatter(arr, dtype, op, from, counts.data());
   gather(arr, dtype, froms.data(), tos.data(), root);
@@ -331,34 +362,12 @@ void ProcessComm::allreduce(void* arr, int dtype, int op, int64_t from, int64_t 
   for (int i = 0; i < n_; ++i) counts[i] = tos[i] - froms[i];
   if (shm_) {  // one pass: owners reduce, everybody collects
     if (!op_valid_for(dtype, op) || op == MP4J_COPY) throw Error("invalid operator for dtype");
-    std::lock_guard<std::mutex> lk(op_mu_);
+    OpGuard lk(op_mu_);
     std::vector<uint32_t> sm(n_, all_mask()), dm(n_, all_mask());
-    return shm_->grs(arr, dtype, op, froms.data(), tos.data(), sm.data(), dm.data());
+    return shm_run(arr, dtype, op, froms.data(), tos.data(), sm.data(), dm.data());
   }
   reduce_scatter(arr, dtype, op, from, counts.data());
   allgather(arr, dtype, froms.data(), tos.data());
-}
-
-// allreduce as the process step of a thread-level collective: ALL T threads of the process call it with the same
-// arguments (arr = the delegate thread's array). On the shared-memory plane the T threads share the copies and the
-// reduction (ShmPlane::grs_team); on the TCP ring thread 0 runs the collective and the others return at once - the
-// caller's next thread barrier is what they wait at. Returns true if the calling thread took part in the data movement.
-bool ProcessComm::allreduce_team(void* arr, int dtype, int op, int64_t from, int64_t to, int tid, int T,
-                                 const std::function<void()>& team_sync) {
-  if (n_ == 1) return false;
-  if (!shm_ || T == 1) {
-    if (tid == 0) allreduce(arr, dtype, op, from, to);
-    return tid == 0;
-  }
-  check_from_to(from, to);
-  if (!op_valid_for(dtype, op) || op == MP4J_COPY) throw Error("invalid operator for dtype");
-  std::vector<int64_t> froms(n_), tos(n_);
-  balanced_split(from, to, n_, froms.data(), tos.data());
-  std::vector<uint32_t> sm(n_, all_mask()), dm(n_, all_mask());
-  std::unique_lock<std::mutex> lk(op_mu_, std::defer_lock);
-  if (tid == 0) lk.lock();  // one collective at a time on a communicator; the team is one collective
-  shm_->grs_team(arr, dtype, op, froms.data(), tos.data(), sm.data(), dm.data(), tid, T, &team_sync);
-  return true;
 }
 
 void ProcessComm::allreduce_rpc(void* arr, int dtype, int op, int64_t n) {

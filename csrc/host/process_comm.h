@@ -54,8 +54,22 @@ class ProcessComm {
   void broadcast(void* arr, int dtype, int64_t from, int64_t to, int root);
   void reduce(void* arr, int dtype, int op, int64_t from, int64_t to, int root);
   void allreduce(void* arr, int dtype, int op, int64_t from, int64_t to);
-  bool allreduce_team(void* arr, int dtype, int op, int64_t from, int64_t to, int tid, int T,
-                      const std::function<void()>& team_sync);
+  // The process step of a thread-level collective, executed by ALL T threads of the process: each thread opens a
+  // TeamScope (tid 0 = the delegate) and calls the same array collective with the same arguments. On the
+  // shared-memory plane the team shares the copies and the reduction (ShmPlane::grs_team); on the TCP paths thread
+  // 0 runs the collective and the followers return at once (the caller's next thread barrier is where they wait).
+  struct Team {
+    int tid;
+    int T;
+    const std::function<void()>* sync;  // the team's thread barrier
+  };
+  class TeamScope {
+   public:
+    explicit TeamScope(const Team* t);
+    ~TeamScope();
+    TeamScope(const TeamScope&) = delete;
+    TeamScope& operator=(const TeamScope&) = delete;
+  };
   // small-message allreduce through the master mailbox (PCS:1776-1799, SRV:373-497)
   void allreduce_rpc(void* arr, int dtype, int op, int64_t n);
 
@@ -80,6 +94,8 @@ class ProcessComm {
   std::string sendrecv_bytes(int dest, const void* data, size_t n, int src);
 
  private:
+  void shm_run(void* arr, int dtype, int op, const int64_t* lo, const int64_t* hi, const uint32_t* src_mask,
+               const uint32_t* dst_mask);
   uint32_t all_mask() const { return n_ >= 32 ? 0xffffffffu : ((1u << n_) - 1u); }
   int out_fd(int dest);
   int in_fd(int src);

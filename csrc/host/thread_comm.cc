@@ -1,6 +1,7 @@
 // ThreadComm: see thread_comm.h.
 #include "thread_comm.h"
 
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -13,6 +14,12 @@
 #include "../core/partition.h"
 
 namespace mp4j {
+
+// MP4J_THREAD_TEAM=0: the delegate thread runs the process step alone (the behaviour before teams existed)
+static bool team_enabled() {
+  static const bool on = !(getenv("MP4J_THREAD_TEAM") && atoi(getenv("MP4J_THREAD_TEAM")) == 0);
+  return on;
+}
 
 // ThreadCommSlave.allreduceArray on host arrays (TCS:1915-1963), all T threads call it:
 //   every thread reduces ITS 1/T slice of the range over the T arrays into thread 0's array
@@ -61,8 +68,10 @@ void ThreadComm::allreduce(ProcessComm& pc, int tid, void* arr, int dtype, int o
   {
     // the process step: on the shared-memory plane all T threads share it, on the TCP ring thread 0 runs it
     const std::function<void()> sync = [&tg] { tg.barrier(); };
+    const ProcessComm::Team team{tid, T, &sync};
+    ProcessComm::TeamScope scope(team_enabled() ? &team : nullptr);
     try {
-      pc.allreduce_team(acc, dtype, op, from, to, tid, T, sync);
+      if (team_enabled() || tid == 0) pc.allreduce(acc, dtype, op, from, to);
     } catch (const std::exception& e) {
       if (tid == 0) {  // a team fails as one (every thread gets the same error); thread 0 records it
         tg.set_slot(0, 1, 1);
@@ -135,10 +144,14 @@ void ThreadComm::collective(ProcessComm& pc, int tid, int kind, void* arr, int d
     copy(dst, mine, lo[(size_t)r * T + tid], hi[(size_t)r * T + tid]);
   }
   tg.barrier();
-  // ---- the delegate runs the process collective
-  if (tid == rr) {
+  // ---- the process collective: a team of all T threads whose thread 0 is the delegate (shared-memory plane: the
+  // threads share copies and reduction; TCP: the delegate runs it, the others fall through to the barrier)
+  {
+    const std::function<void()> sync = [&tg] { tg.barrier(); };
+    const ProcessComm::Team team{(tid - rr + T) % T, T, &sync};
+    ProcessComm::TeamScope scope(team_enabled() ? &team : nullptr);
     try {
-      switch (kind) {
+      if (team_enabled() || tid == rr) switch (kind) {
         case MP4J_GATHER: pc.gather(dst, dtype, pf.data(), pt.data(), root_rank); break;
         case MP4J_SCATTER: pc.scatter(dst, dtype, pf.data(), pt.data(), root_rank); break;
         case MP4J_ALL_GATHER: pc.allgather(dst, dtype, pf.data(), pt.data()); break;
@@ -148,8 +161,10 @@ void ThreadComm::collective(ProcessComm& pc, int tid, int kind, void* arr, int d
         default: throw Error("ThreadComm::collective: use allreduce() for allreduce");
       }
     } catch (const std::exception& e) {
-      tg.set_slot(rr, 1, 1);
-      error_ = e.what();
+      if (tid == rr) {
+        tg.set_slot(rr, 1, 1);
+        error_ = e.what();
+      }
     }
   }
   tg.barrier();
