@@ -125,9 +125,12 @@ def test_ragged_ranges_against_numpy(p, transport, window, monkeypatch):
     assert res == [True] * p and code == 0, res
 
 
-@pytest.mark.parametrize("p,T,transport", [(1, 3, "shm"), (2, 2, "shm"), (3, 3, "tcp"), (2, 4, "shm")])
+@pytest.mark.parametrize("p,T,transport", [(1, 3, "shm"), (2, 2, "shm"), (3, 3, "tcp"), (2, 4, "shm"), (2, 3, "shm-solo")])
 def test_ragged_thread_ranges_against_numpy(p, T, transport, monkeypatch):
-    monkeypatch.setenv("MP4J_SHM", "1" if transport == "shm" else "0")
+    # shm: the T threads run the process step as a team; shm-solo (MP4J_THREAD_TEAM=0): the delegate alone; tcp: the
+    # delegate runs the ring / tree, the other threads fall through to the barrier
+    monkeypatch.setenv("MP4J_SHM", "0" if transport == "tcp" else "1")
+    monkeypatch.setenv("MP4J_THREAD_TEAM", "0" if transport == "shm-solo" else "1")
     monkeypatch.setenv("MP4J_SHM_BYTES", str(64 << 10))
     res, code, _ = run_cluster(p, workers.ragged_thread_arrays, (77 + p * T, 20_011), threads=T, timeout=180)
     assert code == 0 and all(all(x is True for x in row) for row in res), res
