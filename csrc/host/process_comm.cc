@@ -29,6 +29,17 @@ struct OpGuard {
 };
 bool team_follower() { return tl_team && tl_team->tid != 0; }
 
+// Small messages on the TCP paths skip the ring / tree: every rank talks to every peer directly over the mesh (one
+// network latency instead of p - 1 or 2(p - 1) dependent hops), and reductions run in rank order on the receiver -
+// the TCP twin of the GPU plane's one-shot kernel. MP4J_TCP_ONESHOT_MAX_BYTES (0 = off), up to
+// MP4J_TCP_ONESHOT_MAX_RANKS ranks (a full mesh costs 2(p - 1) sockets per rank; the ring needs two).
+size_t env_sz(const char* name, size_t dflt) {
+  const char* e = getenv(name);
+  return e ? (size_t)strtoull(e, nullptr, 10) : dflt;
+}
+const size_t kOneShotMaxBytes = env_sz("MP4J_TCP_ONESHOT_MAX_BYTES", 32 << 10);
+const size_t kOneShotMaxRanks = env_sz("MP4J_TCP_ONESHOT_MAX_RANKS", 32);
+
 constexpr size_t kChunk = 1 << 20;  // pipeline granularity of reduce-on-receive
 // ring steps moving at least this much send on a helper thread (MP4J_TCP_DUPLEX_MIN_BYTES; 0 = never)
 const size_t kDuplexMin = [] {
@@ -166,6 +177,21 @@ void ProcessComm::close(int code) {
 ProcessComm::TeamScope::TeamScope(const Team* t) { tl_team = (t && t->T > 1) ? t : nullptr; }
 ProcessComm::TeamScope::~TeamScope() { tl_team = nullptr; }
 
+bool ProcessComm::tcp_oneshot(size_t bytes) const {
+  return !shm_ && kOneShotMaxBytes > 0 && bytes <= kOneShotMaxBytes && (size_t)n_ <= kOneShotMaxRanks;
+}
+
+// `bytes` of mine to every peer, every peer's `bytes` into all + q * bytes (sends first: messages this small fit
+// the socket buffers, so no send waits for a receive)
+void ProcessComm::exchange_small(const void* mine, size_t bytes, char* all) {
+  if (bytes == 0) return;
+  for (int s = 1; s < n_; ++s) net::send_all(out_fd((rank_ + s) % n_), mine, bytes);
+  for (int s = 1; s < n_; ++s) {
+    const int src = (rank_ - s + n_) % n_;
+    if (!net::recv_all(in_fd(src), all + (size_t)src * bytes, bytes)) throw Error("peer closed the data connection");
+  }
+}
+
 void ProcessComm::shm_run(void* arr, int dtype, int op, const int64_t* lo, const int64_t* hi, const uint32_t* src_mask,
                           const uint32_t* dst_mask) {
   if (tl_team) shm_->grs_team(arr, dtype, op, lo, hi, src_mask, dst_mask, tl_team->tid, tl_team->T, tl_team->sync);
@@ -186,6 +212,29 @@ void ProcessComm::reduce_scatter(void* arr, int dtype, int op, int64_t from, con
     return shm_run(arr, dtype, op, froms.data(), tos.data(), sm.data(), dm.data());
   }
   if (team_follower()) return;  // the ring is thread 0's
+  if (tcp_oneshot((size_t)(tos[n_ - 1] - froms[0]) * es)) {
+    // small: slice q goes straight to its owner q; the owner folds the p contributions in rank order
+    char* b = (char*)arr;
+    for (int s = 1; s < n_; ++s) {
+      const int q = (rank_ + s) % n_;
+      const size_t nb = (size_t)(tos[q] - froms[q]) * es;
+      if (nb) net::send_all(out_fd(q), b + froms[q] * es, nb);
+    }
+    const size_t mine = (size_t)(tos[rank_] - froms[rank_]) * es;
+    if (mine == 0) return;
+    std::vector<char> acc(mine), in(mine);
+    for (int q = 0; q < n_; ++q) {
+      const char* x = b + froms[rank_] * es;
+      if (q != rank_) {
+        if (!net::recv_all(in_fd(q), in.data(), mine)) throw Error("peer closed the data connection");
+        x = in.data();
+      }
+      if (q == 0) memcpy(acc.data(), x, mine);
+      else host_reduce_into(dtype, op, acc.data(), x, mine / es);
+    }
+    memcpy(b + froms[rank_] * es, acc.data(), mine);
+    return;
+  }
   int next = (rank_ + 1) % n_, prev = (rank_ - 1 + n_) % n_;
   int sfd = out_fd(next), rfd = in_fd(prev);
   char* base = (char*)arr;
@@ -232,6 +281,22 @@ void ProcessComm::allgather(void* arr, int dtype, const int64_t* froms, const in
     return shm_run(arr, dtype, MP4J_COPY, froms, tos, sm.data(), dm.data());
   }
   if (team_follower()) return;  // the ring is thread 0's
+  {
+    size_t total = 0;
+    for (int q = 0; q < n_; ++q) total += (size_t)(tos[q] - froms[q]) * es;
+    if (tcp_oneshot(total)) {  // small: my slice to every peer, every peer's slice straight into place
+      char* b = (char*)arr;
+      const size_t mine = (size_t)(tos[rank_] - froms[rank_]) * es;
+      if (mine)
+        for (int s = 1; s < n_; ++s) net::send_all(out_fd((rank_ + s) % n_), b + froms[rank_] * es, mine);
+      for (int s = 1; s < n_; ++s) {
+        const int q = (rank_ - s + n_) % n_;
+        const size_t nb = (size_t)(tos[q] - froms[q]) * es;
+        if (nb && !net::recv_all(in_fd(q), b + froms[q] * es, nb)) throw Error("peer closed the data connection");
+      }
+      return;
+    }
+  }
   int next = (rank_ + 1) % n_, prev = (rank_ - 1 + n_) % n_;
   int sfd = out_fd(next), rfd = in_fd(prev);
   char* base = (char*)arr;
@@ -333,6 +398,19 @@ void ProcessComm::broadcast(void* arr, int dtype, int64_t from, int64_t to, int 
     std::vector<uint32_t> sm(n_, 1u << root), dm(n_, all_mask());
     return shm_run(arr, dtype, MP4J_COPY, froms.data(), tos.data(), sm.data(), dm.data());
   }
+  const size_t es = dtype_size(dtype), bytes = (size_t)(to - from) * es;
+  if (tcp_oneshot(bytes)) {
+    if (root < 0 || root >= n_) throw Error("root rank out of range");
+    OpGuard lk(op_mu_);
+    if (team_follower() || bytes == 0) return;
+    char* mine = (char*)arr + from * es;
+    if (rank_ == root) {
+      for (int s = 1; s < n_; ++s) net::send_all(out_fd((rank_ + s) % n_), mine, bytes);
+    } else if (!net::recv_all(in_fd(root), mine, bytes)) {
+      throw Error("peer closed the data connection");
+    }
+    return;
+  }
   scatter(arr, dtype, froms.data(), tos.data(), root);
   allgather(arr, dtype, froms.data(), tos.data());
 }
@@ -350,6 +428,30 @@ void ProcessComm::reduce(void* arr, int dtype, int op, int64_t from, int64_t to,
     std::vector<uint32_t> sm(n_, all_mask()), dm(n_, 1u << root);
     return shm_run(arr, dtype, op, froms.data(), tos.data(), sm.data(), dm.data());
   }
+  const size_t es = dtype_size(dtype), bytes = (size_t)(to - from) * es;
+  if (tcp_oneshot(bytes)) {
+    if (root < 0 || root >= n_) throw Error("root rank out of range");
+    if (!op_valid_for(dtype, op) || op == MP4J_COPY) throw Error("invalid operator for dtype");
+    OpGuard lk(op_mu_);
+    if (team_follower() || bytes == 0) return;
+    char* mine = (char*)arr + from * es;
+    if (rank_ != root) {
+      net::send_all(out_fd(root), mine, bytes);
+      return;
+    }
+    std::vector<char> acc(bytes), in(bytes);
+    for (int q = 0; q < n_; ++q) {  // rank order
+      const char* x = mine;
+      if (q != root) {
+        if (!net::recv_all(in_fd(q), in.data(), bytes)) throw Error("peer closed the data connection");
+        x = in.data();
+      }
+      if (q == 0) memcpy(acc.data(), x, bytes);
+      else host_reduce_into(dtype, op, acc.data(), x, (size_t)(to - from));
+    }
+    memcpy(mine, acc.data(), bytes);
+    return;
+  }
   reduce_scatter(arr, dtype, op, from, counts.data());
   gather(arr, dtype, froms.data(), tos.data(), root);
 }
@@ -365,6 +467,19 @@ void ProcessComm::allreduce(void* arr, int dtype, int op, int64_t from, int64_t 
     OpGuard lk(op_mu_);
     std::vector<uint32_t> sm(n_, all_mask()), dm(n_, all_mask());
     return shm_run(arr, dtype, op, froms.data(), tos.data(), sm.data(), dm.data());
+  }
+  const size_t es = dtype_size(dtype), bytes = (size_t)(to - from) * es;
+  if (tcp_oneshot(bytes)) {
+    if (!op_valid_for(dtype, op) || op == MP4J_COPY) throw Error("invalid operator for dtype");
+    OpGuard lk(op_mu_);
+    if (team_follower() || bytes == 0) return;
+    char* mine = (char*)arr + from * es;
+    std::vector<char> all((size_t)n_ * bytes);
+    memcpy(all.data() + (size_t)rank_ * bytes, mine, bytes);
+    exchange_small(mine, bytes, all.data());
+    for (int q = 1; q < n_; ++q) host_reduce_into(dtype, op, all.data(), all.data() + (size_t)q * bytes, (size_t)(to - from));
+    memcpy(mine, all.data(), bytes);  // rank order on every rank: identical bits everywhere
+    return;
   }
   reduce_scatter(arr, dtype, op, from, counts.data());
   allgather(arr, dtype, froms.data(), tos.data());

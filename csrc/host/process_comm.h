@@ -94,6 +94,8 @@ class ProcessComm {
   std::string sendrecv_bytes(int dest, const void* data, size_t n, int src);
 
  private:
+  bool tcp_oneshot(size_t bytes) const;
+  void exchange_small(const void* mine, size_t bytes, char* all);
   void shm_run(void* arr, int dtype, int op, const int64_t* lo, const int64_t* hi, const uint32_t* src_mask,
                const uint32_t* dst_mask);
   uint32_t all_mask() const { return n_ >= 32 ? 0xffffffffu : ((1u << n_) - 1u); }
