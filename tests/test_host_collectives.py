@@ -113,15 +113,18 @@ def test_gpu_plane_decision_is_the_same_on_every_rank():
     assert code == 0 and all("at most 8" in r for r in res), res
 
 
-@pytest.mark.parametrize("p,transport,window", [(2, "shm", 64 << 10), (4, "shm", 64 << 10), (3, "shm", 64 << 20),
-                                                (3, "tcp", 0), (5, "shm", 128 << 10)])
-def test_ragged_ranges_against_numpy(p, transport, window, monkeypatch):
+@pytest.mark.parametrize("p,transport,window,n", [(2, "shm", 64 << 10, 40_003), (4, "shm", 64 << 10, 40_003),
+                                                  (3, "shm", 64 << 20, 40_003), (3, "tcp", 0, 40_003),
+                                                  (5, "shm", 128 << 10, 40_003),
+                                                  (4, "tcp", 0, 1_501),    # <= 32 KiB: the direct all-pairs forms
+                                                  (3, "tcp", 0, 4_099)])   # around the threshold: both forms mixed
+def test_ragged_ranges_against_numpy(p, transport, window, n, monkeypatch):
     """Randomised ragged ranges (empty, unequal, with gaps) through every array collective. The small windows make
     the shared-memory plane take many passes, each over a part of every slice."""
     monkeypatch.setenv("MP4J_SHM", "1" if transport == "shm" else "0")
     if window:
         monkeypatch.setenv("MP4J_SHM_BYTES", str(window))
-    res, code, _ = run_cluster(p, workers.ragged_arrays, (1234 + p, 40_003), timeout=180)
+    res, code, _ = run_cluster(p, workers.ragged_arrays, (1234 + p, n), timeout=180)
     assert res == [True] * p and code == 0, res
 
 
