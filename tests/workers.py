@@ -477,9 +477,9 @@ def ragged_arrays(comm, seed, n):
             ok &= np.array_equal(a, want)
         a = data[r].copy()
         comm.scatterArray(a, dop, froms, tos, root)
-        w2 = data[r].copy()
-        w2[froms[r]:tos[r]] = data[root][froms[r]:tos[r]]
-        ok &= np.array_equal(a, w2)
+        # only the own slice is specified: a rank that relays in the scatter tree holds the slices it forwards
+        # at their offsets afterwards (as in the reference)
+        ok &= np.array_equal(a[froms[r]:tos[r]], data[root][froms[r]:tos[r]])
         # reduce-scatter with ragged counts, allreduce / reduce / broadcast on a sub-range
         counts = [int(x) for x in rnd.randint(0, n // p, size=p)]
         counts[int(rnd.randint(p))] = 0
