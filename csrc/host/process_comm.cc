@@ -326,6 +326,23 @@ void ProcessComm::gather(void* arr, int dtype, const int64_t* froms, const int64
     return shm_run(arr, dtype, MP4J_COPY, froms, tos, sm.data(), dm.data());
   }
   if (team_follower()) return;  // the tree is thread 0's
+  {
+    size_t total = 0;
+    for (int q = 0; q < n_; ++q) total += (size_t)(tos[q] - froms[q]) * es;
+    if (tcp_oneshot(total)) {  // small: every rank hands its slice to the root directly (one hop, no relays)
+      char* b = (char*)arr;
+      if (rank_ != root) {
+        const size_t nb = (size_t)(tos[rank_] - froms[rank_]) * es;
+        if (nb) net::send_all(out_fd(root), b + froms[rank_] * es, nb);
+        return;
+      }
+      for (int q = 0; q < n_; ++q) {
+        const size_t nb = (size_t)(tos[q] - froms[q]) * es;
+        if (q != root && nb && !net::recv_all(in_fd(q), b + froms[q] * es, nb)) throw Error("peer closed during gather");
+      }
+      return;
+    }
+  }
   char* base = (char*)arr;
   int vr = (rank_ - root + n_) % n_;
   auto real = [&](int v) { return (v + root) % n_; };
@@ -360,6 +377,24 @@ void ProcessComm::scatter(void* arr, int dtype, const int64_t* froms, const int6
     return shm_run(arr, dtype, MP4J_COPY, froms, tos, sm.data(), dm.data());
   }
   if (team_follower()) return;  // the tree is thread 0's
+  {
+    size_t total = 0;
+    for (int q = 0; q < n_; ++q) total += (size_t)(tos[q] - froms[q]) * es;
+    if (tcp_oneshot(total)) {  // small: the root hands every rank its slice directly (one hop, no relays)
+      char* b = (char*)arr;
+      if (rank_ == root) {
+        for (int s = 1; s < n_; ++s) {
+          const int q = (rank_ + s) % n_;
+          const size_t nb = (size_t)(tos[q] - froms[q]) * es;
+          if (nb) net::send_all(out_fd(q), b + froms[q] * es, nb);
+        }
+        return;
+      }
+      const size_t nb = (size_t)(tos[rank_] - froms[rank_]) * es;
+      if (nb && !net::recv_all(in_fd(root), b + froms[rank_] * es, nb)) throw Error("peer closed during scatter");
+      return;
+    }
+  }
   char* base = (char*)arr;
   int vr = (rank_ - root + n_) % n_;
   auto real = [&](int v) { return (v + root) % n_; };
