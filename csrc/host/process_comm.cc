@@ -100,6 +100,8 @@ ProcessComm::ProcessComm(const std::string& login, const std::string& master_hos
   master_->kill_me(rank_, "ssh " + login + "@" + host + " \"kill -9 " + std::to_string((int)getpid()) + "\"");
   int period = env_int("MP4J_HEARTBEAT_MS", 15000);
   master_->start_heartbeat(rank_, std::min(period, 5000), period, 4, nullptr, nullptr);
+  everyone_.resize((size_t)n_);
+  for (int q = 0; q < n_; ++q) everyone_[(size_t)q] = q;
   shm_ = ShmPlane::create(*master_, rank_, n_);  // collective; null on every rank if unusable
 }
 
@@ -177,8 +179,9 @@ void ProcessComm::close(int code) {
 ProcessComm::TeamScope::TeamScope(const Team* t) { tl_team = (t && t->T > 1) ? t : nullptr; }
 ProcessComm::TeamScope::~TeamScope() { tl_team = nullptr; }
 
-bool ProcessComm::tcp_oneshot(size_t bytes) const {
-  return !shm_ && kOneShotMaxBytes > 0 && bytes <= kOneShotMaxBytes && (size_t)n_ <= kOneShotMaxRanks;
+bool ProcessComm::tcp_oneshot(size_t bytes, int members) const {
+  if (members < 0) members = n_;
+  return !shm_ && kOneShotMaxBytes > 0 && bytes <= kOneShotMaxBytes && (size_t)members <= kOneShotMaxRanks;
 }
 
 // `bytes` of mine to every peer, every peer's `bytes` into all + q * bytes (sends first: messages this small fit
@@ -198,53 +201,45 @@ void ProcessComm::shm_run(void* arr, int dtype, int op, const int64_t* lo, const
   else shm_->grs(arr, dtype, op, lo, hi, src_mask, dst_mask);
 }
 
-void ProcessComm::reduce_scatter(void* arr, int dtype, int op, int64_t from, const int64_t* counts) {
-  check_from_counts(from, counts, n_);
-  if (n_ == 1) return;  // PCS:1179
-  if (!op_valid_for(dtype, op) || op == MP4J_COPY) throw Error("invalid operator for dtype");
-  OpGuard lk(op_mu_);
+// The TCP reduce-scatter and allgather over a GROUP of ranks (grp[i] = global rank of member i, `me` = my index):
+// the whole job for the flat collectives, the ranks with my local index on every machine for the inter-machine step
+// of the hierarchical allreduce. froms / tos are indexed by member. Small totals go directly between all pairs,
+// otherwise the ring (big steps with the send on a helper thread).
+void ProcessComm::tcp_reduce_scatter(char* b, int dtype, int op, const int64_t* froms, const int64_t* tos,
+                                     const std::vector<int>& grp, int me) {
+  const int g = (int)grp.size();
   const size_t es = dtype_size(dtype);
-  std::vector<int64_t> froms(n_), tos(n_);
-  froms_tos_from_counts(from, counts, n_, froms.data(), tos.data());
-  if (shm_) {
-    std::vector<uint32_t> sm(n_, all_mask()), dm(n_);
-    for (int q = 0; q < n_; ++q) dm[q] = 1u << q;
-    return shm_run(arr, dtype, op, froms.data(), tos.data(), sm.data(), dm.data());
-  }
-  if (team_follower()) return;  // the ring is thread 0's
-  if (tcp_oneshot((size_t)(tos[n_ - 1] - froms[0]) * es)) {
-    // small: slice q goes straight to its owner q; the owner folds the p contributions in rank order
-    char* b = (char*)arr;
-    for (int s = 1; s < n_; ++s) {
-      const int q = (rank_ + s) % n_;
+  if (g == 1) return;
+  if (tcp_oneshot((size_t)(tos[g - 1] - froms[0]) * es, g)) {
+    // small: slice q goes straight to its owner q; the owner folds the contributions in member order
+    for (int s = 1; s < g; ++s) {
+      const int q = (me + s) % g;
       const size_t nb = (size_t)(tos[q] - froms[q]) * es;
-      if (nb) net::send_all(out_fd(q), b + froms[q] * es, nb);
+      if (nb) net::send_all(out_fd(grp[q]), b + froms[q] * es, nb);
     }
-    const size_t mine = (size_t)(tos[rank_] - froms[rank_]) * es;
+    const size_t mine = (size_t)(tos[me] - froms[me]) * es;
     if (mine == 0) return;
     std::vector<char> acc(mine), in(mine);
-    for (int q = 0; q < n_; ++q) {
-      const char* x = b + froms[rank_] * es;
-      if (q != rank_) {
-        if (!net::recv_all(in_fd(q), in.data(), mine)) throw Error("peer closed the data connection");
+    for (int q = 0; q < g; ++q) {
+      const char* x = b + froms[me] * es;
+      if (q != me) {
+        if (!net::recv_all(in_fd(grp[q]), in.data(), mine)) throw Error("peer closed the data connection");
         x = in.data();
       }
       if (q == 0) memcpy(acc.data(), x, mine);
       else host_reduce_into(dtype, op, acc.data(), x, mine / es);
     }
-    memcpy(b + froms[rank_] * es, acc.data(), mine);
+    memcpy(b + froms[me] * es, acc.data(), mine);
     return;
   }
-  int next = (rank_ + 1) % n_, prev = (rank_ - 1 + n_) % n_;
-  int sfd = out_fd(next), rfd = in_fd(prev);
-  char* base = (char*)arr;
+  const int sfd = out_fd(grp[(me + 1) % g]), rfd = in_fd(grp[(me - 1 + g) % g]);
   if (scratch_.size() < kChunk) scratch_.resize(kChunk);
-  for (int s = 0; s < n_ - 1; ++s) {
-    int sseg = ((rank_ - 1 - s) % n_ + n_) % n_;
-    int rseg = ((rank_ - 2 - s) % n_ + n_) % n_;
-    size_t sbytes = (size_t)(tos[sseg] - froms[sseg]) * es, rbytes = (size_t)(tos[rseg] - froms[rseg]) * es;
-    char* sp = base + froms[sseg] * es;
-    char* rp = base + froms[rseg] * es;
+  for (int s = 0; s < g - 1; ++s) {
+    const int sseg = ((me - 1 - s) % g + g) % g;
+    const int rseg = ((me - 2 - s) % g + g) % g;
+    const size_t sbytes = (size_t)(tos[sseg] - froms[sseg]) * es, rbytes = (size_t)(tos[rseg] - froms[rseg]) * es;
+    char* sp = b + froms[sseg] * es;
+    char* rp = b + froms[rseg] * es;
     size_t so = 0, ro = 0;
     const size_t chunk = kChunk / es * es;
     if (sbytes + rbytes >= kDuplexMin) {
@@ -261,13 +256,62 @@ void ProcessComm::reduce_scatter(void* arr, int dtype, int op, int64_t from, con
       continue;
     }
     while (so < sbytes || ro < rbytes) {
-      size_t sl = std::min(chunk, sbytes - so), rl = std::min(chunk, rbytes - ro);
+      const size_t sl = std::min(chunk, sbytes - so), rl = std::min(chunk, rbytes - ro);
       net::sendrecv(sfd, sp + so, sl, rfd, scratch_.data(), rl);
       if (rl) host_reduce_into(dtype, op, rp + ro, scratch_.data(), rl / es);  // op(local, incoming) DOP:196
       so += sl;
       ro += rl;
     }
   }
+}
+
+void ProcessComm::tcp_allgather(char* b, size_t es, const int64_t* froms, const int64_t* tos,
+                                const std::vector<int>& grp, int me) {
+  const int g = (int)grp.size();
+  if (g == 1) return;
+  size_t total = 0;
+  for (int q = 0; q < g; ++q) total += (size_t)(tos[q] - froms[q]) * es;
+  if (tcp_oneshot(total, g)) {  // small: my slice to every peer, every peer's slice straight into place
+    const size_t mine = (size_t)(tos[me] - froms[me]) * es;
+    if (mine)
+      for (int s = 1; s < g; ++s) net::send_all(out_fd(grp[(me + s) % g]), b + froms[me] * es, mine);
+    for (int s = 1; s < g; ++s) {
+      const int q = (me - s + g) % g;
+      const size_t nb = (size_t)(tos[q] - froms[q]) * es;
+      if (nb && !net::recv_all(in_fd(grp[q]), b + froms[q] * es, nb)) throw Error("peer closed the data connection");
+    }
+    return;
+  }
+  const int sfd = out_fd(grp[(me + 1) % g]), rfd = in_fd(grp[(me - 1 + g) % g]);
+  for (int s = 0; s < g - 1; ++s) {
+    const int sseg = ((me - s) % g + g) % g;
+    const int rseg = ((me - 1 - s) % g + g) % g;
+    const size_t sbytes = (size_t)(tos[sseg] - froms[sseg]) * es, rbytes = (size_t)(tos[rseg] - froms[rseg]) * es;
+    if (sbytes + rbytes >= kDuplexMin) {
+      duplex_step(sfd, b + froms[sseg] * es, sbytes, [&] {
+        if (rbytes && !net::recv_all(rfd, b + froms[rseg] * es, rbytes)) throw Error("peer closed during allgather");
+      });
+      continue;
+    }
+    net::sendrecv(sfd, b + froms[sseg] * es, sbytes, rfd, b + froms[rseg] * es, rbytes);
+  }
+}
+
+void ProcessComm::reduce_scatter(void* arr, int dtype, int op, int64_t from, const int64_t* counts) {
+  check_from_counts(from, counts, n_);
+  if (n_ == 1) return;  // PCS:1179
+  if (!op_valid_for(dtype, op) || op == MP4J_COPY) throw Error("invalid operator for dtype");
+  OpGuard lk(op_mu_);
+  const size_t es = dtype_size(dtype);
+  std::vector<int64_t> froms(n_), tos(n_);
+  froms_tos_from_counts(from, counts, n_, froms.data(), tos.data());
+  if (shm_) {
+    std::vector<uint32_t> sm(n_, all_mask()), dm(n_);
+    for (int q = 0; q < n_; ++q) dm[q] = 1u << q;
+    return shm_run(arr, dtype, op, froms.data(), tos.data(), sm.data(), dm.data());
+  }
+  if (team_follower()) return;  // the ring is thread 0's
+  tcp_reduce_scatter((char*)arr, dtype, op, froms.data(), tos.data(), everyone_, rank_);
 }
 
 void ProcessComm::allgather(void* arr, int dtype, const int64_t* froms, const int64_t* tos) {
@@ -281,37 +325,7 @@ void ProcessComm::allgather(void* arr, int dtype, const int64_t* froms, const in
     return shm_run(arr, dtype, MP4J_COPY, froms, tos, sm.data(), dm.data());
   }
   if (team_follower()) return;  // the ring is thread 0's
-  {
-    size_t total = 0;
-    for (int q = 0; q < n_; ++q) total += (size_t)(tos[q] - froms[q]) * es;
-    if (tcp_oneshot(total)) {  // small: my slice to every peer, every peer's slice straight into place
-      char* b = (char*)arr;
-      const size_t mine = (size_t)(tos[rank_] - froms[rank_]) * es;
-      if (mine)
-        for (int s = 1; s < n_; ++s) net::send_all(out_fd((rank_ + s) % n_), b + froms[rank_] * es, mine);
-      for (int s = 1; s < n_; ++s) {
-        const int q = (rank_ - s + n_) % n_;
-        const size_t nb = (size_t)(tos[q] - froms[q]) * es;
-        if (nb && !net::recv_all(in_fd(q), b + froms[q] * es, nb)) throw Error("peer closed the data connection");
-      }
-      return;
-    }
-  }
-  int next = (rank_ + 1) % n_, prev = (rank_ - 1 + n_) % n_;
-  int sfd = out_fd(next), rfd = in_fd(prev);
-  char* base = (char*)arr;
-  for (int s = 0; s < n_ - 1; ++s) {
-    int sseg = ((rank_ - s) % n_ + n_) % n_;
-    int rseg = ((rank_ - 1 - s) % n_ + n_) % n_;
-    const size_t sbytes = (size_t)(tos[sseg] - froms[sseg]) * es, rbytes = (size_t)(tos[rseg] - froms[rseg]) * es;
-    if (sbytes + rbytes >= kDuplexMin) {
-      duplex_step(sfd, base + froms[sseg] * es, sbytes, [&] {
-        if (rbytes && !net::recv_all(rfd, base + froms[rseg] * es, rbytes)) throw Error("peer closed during allgather");
-      });
-      continue;
-    }
-    net::sendrecv(sfd, base + froms[sseg] * es, sbytes, rfd, base + froms[rseg] * es, rbytes);
-  }
+  tcp_allgather((char*)arr, es, froms, tos, everyone_, rank_);
 }
 
 void ProcessComm::gather(void* arr, int dtype, const int64_t* froms, const int64_t* tos, int root) {

@@ -94,7 +94,11 @@ class ProcessComm {
   std::string sendrecv_bytes(int dest, const void* data, size_t n, int src);
 
  private:
-  bool tcp_oneshot(size_t bytes) const;
+  bool tcp_oneshot(size_t bytes, int members = -1) const;
+  void tcp_reduce_scatter(char* b, int dtype, int op, const int64_t* froms, const int64_t* tos,
+                          const std::vector<int>& grp, int me);
+  void tcp_allgather(char* b, size_t es, const int64_t* froms, const int64_t* tos, const std::vector<int>& grp, int me);
+  std::vector<int> everyone_;  // 0 .. n-1: the group of the flat collectives
   void exchange_small(const void* mine, size_t bytes, char* all);
   void shm_run(void* arr, int dtype, int op, const int64_t* lo, const int64_t* hi, const uint32_t* src_mask,
                const uint32_t* dst_mask);
