@@ -103,6 +103,46 @@ ProcessComm::ProcessComm(const std::string& login, const std::string& master_hos
   everyone_.resize((size_t)n_);
   for (int q = 0; q < n_; ++q) everyone_[(size_t)q] = q;
   shm_ = ShmPlane::create(*master_, rank_, n_);  // collective; null on every rank if unusable
+  if (!shm_) setup_node_plane();
+}
+
+// Several machines with several ranks each (8 GPUs per node, one process per GPU): no job-wide shared-memory plane,
+// but every machine can have its own. Used by the hierarchical allreduce: reduce-scatter inside the machine, TCP
+// between the ranks that hold the same shard on every machine, allgather inside the machine. Needs the same number
+// (>= 2) of ranks on every machine; MP4J_HIER=0 turns it off. Collective; every rank reaches the same verdict.
+void ProcessComm::setup_node_plane() {
+  if (n_ < 4 || env_int("MP4J_HIER", 1) == 0 || env_int("MP4J_SHM", 1) == 0) return;  // same env on every rank
+  const std::string key = ShmPlane::machine_key();
+  const std::vector<std::string> keys = master_->gather_all(rank_, key.data(), key.size());
+  if ((int)keys.size() != n_) return;
+  // machines in the order of their lowest rank; members ascending
+  std::vector<std::string> order;
+  std::vector<std::vector<int>> nodes;
+  for (int q = 0; q < n_; ++q) {
+    size_t j = 0;
+    while (j < order.size() && order[j] != keys[(size_t)q]) ++j;
+    if (j == order.size()) {
+      order.push_back(keys[(size_t)q]);
+      nodes.emplace_back();
+    }
+    nodes[j].push_back(q);
+  }
+  const size_t L = nodes[0].size();
+  if (nodes.size() < 2 || L < 2 || L > 32) return;
+  for (const auto& nd : nodes)
+    if (nd.size() != L) return;
+  int ni = -1, li = -1;
+  for (size_t j = 0; j < nodes.size(); ++j)
+    for (size_t i = 0; i < L; ++i)
+      if (nodes[j][i] == rank_) ni = (int)j, li = (int)i;
+  std::vector<int> group = nodes[(size_t)ni], rail;
+  for (const auto& nd : nodes) rail.push_back(nd[(size_t)li]);
+  node_shm_ = ShmPlane::create(*master_, rank_, n_, &group);  // collective over the job
+  if (node_shm_) {
+    node_group_ = group;
+    rail_group_ = rail;
+    node_index_ = ni;
+  }
 }
 
 ProcessComm::~ProcessComm() {
@@ -518,6 +558,25 @@ void ProcessComm::allreduce(void* arr, int dtype, int op, int64_t from, int64_t 
     return shm_run(arr, dtype, op, froms.data(), tos.data(), sm.data(), dm.data());
   }
   const size_t es = dtype_size(dtype), bytes = (size_t)(to - from) * es;
+  if (node_shm_ && !tcp_oneshot(bytes)) {
+    // hierarchical: shared memory inside the machine, TCP only between the ranks that own the same shard
+    if (!op_valid_for(dtype, op) || op == MP4J_COPY) throw Error("invalid operator for dtype");
+    OpGuard lk(op_mu_);
+    if (team_follower()) return;
+    const int L = node_shm_->members(), li = node_shm_->index(), m = (int)rail_group_.size();
+    const uint32_t all_l = L >= 32 ? 0xffffffffu : ((1u << L) - 1u);
+    std::vector<int64_t> lf(L), lt(L), rf(m), rt(m);
+    balanced_split(from, to, L, lf.data(), lt.data());
+    std::vector<uint32_t> sm(L, all_l), dm(L);
+    for (int q = 0; q < L; ++q) dm[q] = 1u << q;
+    node_shm_->grs(arr, dtype, op, lf.data(), lt.data(), sm.data(), dm.data());  // reduce-scatter inside the machine
+    balanced_split(lf[li], lt[li], m, rf.data(), rt.data());
+    tcp_reduce_scatter((char*)arr, dtype, op, rf.data(), rt.data(), rail_group_, node_index_);  // my shard, across
+    tcp_allgather((char*)arr, es, rf.data(), rt.data(), rail_group_, node_index_);               // the machines
+    for (int q = 0; q < L; ++q) sm[q] = 1u << q, dm[q] = all_l;
+    node_shm_->grs(arr, dtype, MP4J_COPY, lf.data(), lt.data(), sm.data(), dm.data());  // allgather inside the machine
+    return;
+  }
   if (tcp_oneshot(bytes)) {
     if (!op_valid_for(dtype, op) || op == MP4J_COPY) throw Error("invalid operator for dtype");
     OpGuard lk(op_mu_);

@@ -40,7 +40,7 @@ class ProcessComm {
   bool closed() const { return closed_; }
   // "shm" when the ranks share a machine and exchange host arrays through shared-memory windows
   // (shm_plane.h), "tcp" for the ring / tree algorithms over the socket mesh.
-  const char* host_transport() const { return shm_ ? "shm" : "tcp"; }
+  const char* host_transport() const { return shm_ ? "shm" : (node_shm_ ? "tcp+shm" : "tcp"); }
 
   void barrier();
   void log(LogLevel lvl, const std::string& msg);  // forwards verbatim; prefixes are the binding's job
@@ -99,6 +99,12 @@ class ProcessComm {
                           const std::vector<int>& grp, int me);
   void tcp_allgather(char* b, size_t es, const int64_t* froms, const int64_t* tos, const std::vector<int>& grp, int me);
   std::vector<int> everyone_;  // 0 .. n-1: the group of the flat collectives
+  // hierarchical allreduce (several machines, several ranks on each): the plane of my machine, its members, and the
+  // ranks with my local index on every machine (in machine order; node_index_ = my place among them)
+  void setup_node_plane();
+  std::unique_ptr<ShmPlane> node_shm_;
+  std::vector<int> node_group_, rail_group_;
+  int node_index_ = 0;
   void exchange_small(const void* mine, size_t bytes, char* all);
   void shm_run(void* arr, int dtype, int op, const int64_t* lo, const int64_t* hi, const uint32_t* src_mask,
                const uint32_t* dst_mask);

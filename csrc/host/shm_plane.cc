@@ -101,8 +101,26 @@ struct ShmPlane::Header {
   std::atomic<int32_t> pid;  // owner of this segment: lets waiting peers notice a dead process
 };
 
-std::unique_ptr<ShmPlane> ShmPlane::create(MasterClient& master, int rank, int n) {
-  if (n < 2 || n > 32) return nullptr;  // masks are 32-bit; identical decision on every rank
+// boot id of the machine, plus MP4J_NODE_ID when set (tests: several "machines" on one box)
+std::string ShmPlane::machine_key() {
+  std::string k = boot_id();
+  if (const char* e = getenv("MP4J_NODE_ID")) k += std::string("#") + e;
+  return k;
+}
+
+std::unique_ptr<ShmPlane> ShmPlane::create(MasterClient& master, int job_rank, int job_n, const std::vector<int>* group) {
+  // members of this plane: the whole job, or the ranks of one machine (hierarchical collectives). Every rank of the
+  // job calls this together (the exchanges below go through the master and involve everybody); the early returns
+  // depend only on numbers that are the same on every rank.
+  std::vector<int> members;
+  if (group) members = *group;
+  else
+    for (int q = 0; q < job_n; ++q) members.push_back(q);
+  const int n = (int)members.size();
+  int rank = -1;
+  for (int i = 0; i < n; ++i)
+    if (members[(size_t)i] == job_rank) rank = i;
+  if (n < 2 || n > 32 || rank < 0) return nullptr;  // masks are 32-bit
   bool enabled = env_size("MP4J_SHM", 1) != 0;
   size_t window = env_size("MP4J_SHM_BYTES", 64ull << 20);
   window = std::max<size_t>(window, 1 << 16) / 8192 * 8192;  // two page-aligned halves
@@ -152,12 +170,12 @@ std::unique_ptr<ShmPlane> ShmPlane::create(MasterClient& master, int rank, int n
     }
   }
   // ---- exchange (boot id, name, window) and map the peers
-  const std::string mine = boot_id() + "\n" + name + "\n" + std::to_string(window);
-  std::vector<std::string> parts = master.gather_all(rank, mine.data(), mine.size());
-  bool ok = enabled && !name.empty() && (int)parts.size() == n;
+  const std::string mine = machine_key() + "\n" + name + "\n" + std::to_string(window);
+  std::vector<std::string> parts = master.gather_all(job_rank, mine.data(), mine.size());
+  bool ok = enabled && !name.empty() && (int)parts.size() == job_n;
   std::vector<std::string> names(n);
   for (int q = 0; ok && q < n; ++q) {
-    std::vector<std::string> f = split_lines(parts[q]);
+    std::vector<std::string> f = split_lines(parts[(size_t)members[(size_t)q]]);
     if (f.size() != 3 || f[1].empty() || f[0] != split_lines(mine)[0] || f[2] != std::to_string(window)) ok = false;
     else names[q] = f[1];
   }
@@ -175,8 +193,8 @@ std::unique_ptr<ShmPlane> ShmPlane::create(MasterClient& master, int rank, int n
   }
   // ---- everybody must agree, otherwise ranks would run different algorithms
   const char verdict = ok ? '1' : '0';
-  parts = master.gather_all(rank, &verdict, 1);
-  bool all_ok = (int)parts.size() == n;
+  parts = master.gather_all(job_rank, &verdict, 1);
+  bool all_ok = (int)parts.size() == job_n;
   for (const auto& v : parts)
     if (v.size() != 1 || v[0] != '1') all_ok = false;
   if (!name.empty()) shm_unlink(name.c_str());  // everyone who could map it has done so: no leftovers on exit

@@ -30,7 +30,13 @@ class ShmPlane {
  public:
   // Collective over all ranks. Returns nullptr (on every rank alike) if shared memory cannot be
   // used: different machines, MP4J_SHM=0 on any rank, or a mapping failure anywhere.
-  static std::unique_ptr<ShmPlane> create(MasterClient& master, int rank, int n);
+  // group = the job ranks that form this plane (ascending), null = the whole job. With a group the call is still
+  // collective over the WHOLE job (every rank builds the plane of its own group at the same time), and the verdict
+  // is global: one group that cannot map its members turns the planes of all groups off.
+  static std::unique_ptr<ShmPlane> create(MasterClient& master, int rank, int n, const std::vector<int>* group = nullptr);
+  static std::string machine_key();
+  int members() const { return n_; }
+  int index() const { return rank_; }
   ~ShmPlane();
 
   // One gather-reduce-scatter pass. Element ranges [lo[q], hi[q]) are owned by rank q; the owner

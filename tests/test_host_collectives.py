@@ -146,3 +146,20 @@ def test_many_slaves(p, transport, monkeypatch):
     monkeypatch.setenv("MP4J_SHM", "1")
     res, code, _ = run_cluster(p, workers.many_slaves, (), timeout=240)
     assert code == 0 and res == [True] * p
+
+
+@pytest.mark.parametrize("ids,n", [("0,0,1,1", 100_003), ("0,0,0,1,1,1", 20_011), ("a,b,a,b,a,b,a,b", 300_007),
+                                   ("0,0,1,1,2,2", 5_000)])
+def test_hierarchical_allreduce_across_virtual_machines(ids, n, monkeypatch):
+    """No job-wide shared memory (the ranks sit on different 'machines'), but one plane per machine: allreduce =
+    shared-memory reduce-scatter + TCP between the machines + shared-memory allgather. Interleaved rank placement
+    (a,b,a,b,...) checks that groups come from the machine ids, not from rank ranges."""
+    p = len(ids.split(","))
+    monkeypatch.setenv("MP4J_SHM_BYTES", str(256 << 10))  # several passes per plane
+    res, code, _ = run_cluster(p, workers.hierarchical, (n,), timeout=180, env={"MP4J_NODE_IDS": ids})
+    assert code == 0 and res == [True] * p, res
+
+
+def test_uneven_machines_fall_back_to_the_flat_tcp_paths():
+    res, code, _ = run_cluster(5, workers.plane_blocker, (-1,), timeout=60, env={"MP4J_NODE_IDS": "0,0,0,1,1"})
+    assert code == 0  # 3 + 2 ranks: no hierarchy, and nothing hangs while deciding so

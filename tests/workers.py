@@ -584,3 +584,38 @@ def many_slaves(comm):
     m = comm.allreduceMap({"k%d" % comm.getRank(): 1, "all": 1}, Operands.INT_OPERAND(), Operators.Int.SUM)
     return bool(np.array_equal(a, np.arange(5003) * comm.getSlaveNum())) and m["all"] == comm.getSlaveNum() \
         and len(m) == comm.getSlaveNum() + 1
+
+
+def hierarchical(comm, n):
+    """Several "machines" (MP4J_NODE_IDS) with several ranks each: allreduce runs reduce-scatter in shared memory,
+    TCP between the machines, allgather in shared memory; everything else stays on the TCP mesh."""
+    import numpy as np
+    from ytk_mp4j_b200 import Operands, Operators, CommUtils
+    p, r = comm.getSlaveNum(), comm.getRank()
+    assert comm.host_transport == "tcp+shm", comm.host_transport
+    dop = Operands.DOUBLE_OPERAND()
+    rnd = np.random.RandomState(99)
+    data = [rnd.randint(-50, 50, size=n).astype(np.float64) for _ in range(p)]
+    ok = True
+    for f, t in ((0, n), (3, n - 5), (7, 9), (n // 2, n // 2)):
+        a = data[r].copy()
+        comm.allreduceArray(a, dop, Operators.Double.SUM, f, t)
+        want = data[r].copy()
+        want[f:t] = sum(data)[f:t]
+        ok &= bool(np.array_equal(a, want))
+        a = data[r].copy()
+        comm.allreduceArray(a, dop, Operators.Double.MIN, f, t)
+        want = data[r].copy()
+        want[f:t] = np.minimum.reduce(data)[f:t]
+        ok &= bool(np.array_equal(a, want))
+    # the other collectives still work (flat TCP)
+    froms, tos = CommUtils.createProcessArrayFroms(n, p), CommUtils.createProcessArrayTos(n, p)
+    a = data[r].copy()
+    comm.allgatherArray(a, dop, froms, tos)
+    want = np.concatenate([data[q][froms[q]:tos[q]] for q in range(p)])
+    ok &= bool(np.array_equal(a, want))
+    a = data[r].copy()
+    comm.reduceScatterArray(a, dop, Operators.Double.SUM, 0, [t - f for f, t in zip(froms, tos)])
+    ok &= bool(np.array_equal(a[froms[r]:tos[r]], sum(data)[froms[r]:tos[r]]))
+    comm.barrier()
+    return ok

@@ -134,7 +134,9 @@ class ProcessCommSlave:
 
     @property
     def host_transport(self):
-        """"shm" (ranks share a machine: host arrays move through shared-memory windows) or "tcp"."""
+        """"shm" (ranks share a machine: host arrays move through shared-memory windows), "tcp", or "tcp+shm"
+        (several machines with several ranks each: allreduce is hierarchical - shared memory inside a machine,
+        TCP between the machines)."""
         return N.lib.mp4j_comm_host_transport(self._h).decode()
 
     def barrier(self):

@@ -13,6 +13,9 @@ import traceback
 
 def _worker(fn, rank_hint, n, port, threads, args, q, env):
     os.environ.update(env or {})
+    # tests of the multi-machine paths on one box: MP4J_NODE_IDS="0,0,1,1" gives rank i the machine id of entry i
+    if env and env.get("MP4J_NODE_IDS") and rank_hint is not None:
+        os.environ["MP4J_NODE_ID"] = env["MP4J_NODE_IDS"].split(",")[rank_hint]
     try:
         from ytk_mp4j_b200 import ProcessCommSlave, ThreadCommSlave
         if not threads or threads < 1:
