@@ -163,3 +163,4 @@ def test_hierarchical_allreduce_across_virtual_machines(ids, n, monkeypatch):
 def test_uneven_machines_fall_back_to_the_flat_tcp_paths():
     res, code, _ = run_cluster(5, workers.plane_blocker, (-1,), timeout=60, env={"MP4J_NODE_IDS": "0,0,0,1,1"})
     assert code == 0  # 3 + 2 ranks: no hierarchy, and nothing hangs while deciding so
+    assert all("2 machines" in r for r in res), res  # and no GPU plane across "machines" either

@@ -233,7 +233,9 @@ class ProcessCommSlave:
                     boot = f.read().strip()
             except OSError:
                 boot = ""
-            me = "%s|%s|%s" % (socket.gethostname(), boot, os.environ.get("MP4J_GPU_PLANE", "1"))
+            # MP4J_NODE_ID (tests: several "machines" on one box) is part of the machine identity, as in the host plane
+            me = "%s|%s#%s|%s" % (socket.gethostname(), boot, os.environ.get("MP4J_NODE_ID", ""),
+                                  os.environ.get("MP4J_GPU_PLANE", "1"))
             everyone = [b.decode() for b in self._gather_all_bytes(me.encode())] if self._n > 1 else [me]
             machines = {e.rsplit("|", 1)[0] for e in everyone}
             if any(e.rsplit("|", 1)[1] == "0" for e in everyone):
