@@ -142,6 +142,7 @@ void ProcessComm::setup_node_plane() {
     node_group_ = group;
     rail_group_ = rail;
     node_index_ = ni;
+    nodes_ = nodes;
   }
 }
 
@@ -250,7 +251,9 @@ void ProcessComm::tcp_reduce_scatter(char* b, int dtype, int op, const int64_t* 
   const int g = (int)grp.size();
   const size_t es = dtype_size(dtype);
   if (g == 1) return;
-  if (tcp_oneshot((size_t)(tos[g - 1] - froms[0]) * es, g)) {
+  size_t total_bytes = 0;
+  for (int q = 0; q < g; ++q) total_bytes += (size_t)(tos[q] - froms[q]) * es;
+  if (tcp_oneshot(total_bytes, g)) {
     // small: slice q goes straight to its owner q; the owner folds the contributions in member order
     for (int s = 1; s < g; ++s) {
       const int q = (me + s) % g;
@@ -351,6 +354,24 @@ void ProcessComm::reduce_scatter(void* arr, int dtype, int op, int64_t from, con
     return shm_run(arr, dtype, op, froms.data(), tos.data(), sm.data(), dm.data());
   }
   if (team_follower()) return;  // the ring is thread 0's
+  if (node_shm_ && !tcp_oneshot((size_t)(tos[n_ - 1] - froms[0]) * es)) {
+    // hierarchical: for every machine j, its ranks' slices are reduced over MY machine in shared memory (local rank i
+    // takes the slice of machine j's local rank i); then the partial sums travel between the machines: on the rail
+    // of local index i, member j owns the slice of machine j's local rank i
+    const int L = node_shm_->members(), li = node_shm_->index(), m = (int)nodes_.size();
+    const uint32_t all_l = L >= 32 ? 0xffffffffu : ((1u << L) - 1u);
+    std::vector<int64_t> lf(L), lt(L), rf(m), rt(m);
+    std::vector<uint32_t> sm(L, all_l), dm(L);
+    for (int q = 0; q < L; ++q) dm[q] = 1u << q;
+    for (int j = 0; j < m; ++j) {
+      for (int i = 0; i < L; ++i) lf[i] = froms[nodes_[j][i]], lt[i] = tos[nodes_[j][i]];
+      node_shm_->grs(arr, dtype, op, lf.data(), lt.data(), sm.data(), dm.data());
+      rf[j] = froms[nodes_[j][li]];
+      rt[j] = tos[nodes_[j][li]];
+    }
+    tcp_reduce_scatter((char*)arr, dtype, op, rf.data(), rt.data(), rail_group_, node_index_);
+    return;
+  }
   tcp_reduce_scatter((char*)arr, dtype, op, froms.data(), tos.data(), everyone_, rank_);
 }
 
@@ -365,6 +386,26 @@ void ProcessComm::allgather(void* arr, int dtype, const int64_t* froms, const in
     return shm_run(arr, dtype, MP4J_COPY, froms, tos, sm.data(), dm.data());
   }
   if (team_follower()) return;  // the ring is thread 0's
+  {
+    size_t total = 0;
+    for (int q = 0; q < n_; ++q) total += (size_t)(tos[q] - froms[q]) * es;
+    if (node_shm_ && !tcp_oneshot(total)) {
+      // hierarchical: first between the machines (on my rail I collect the slices of every machine's local rank
+      // li), then inside the machine in shared memory, one pass per source machine
+      const int L = node_shm_->members(), li = node_shm_->index(), m = (int)nodes_.size();
+      const uint32_t all_l = L >= 32 ? 0xffffffffu : ((1u << L) - 1u);
+      std::vector<int64_t> lf(L), lt(L), rf(m), rt(m);
+      for (int j = 0; j < m; ++j) rf[j] = froms[nodes_[j][li]], rt[j] = tos[nodes_[j][li]];
+      tcp_allgather((char*)arr, es, rf.data(), rt.data(), rail_group_, node_index_);
+      std::vector<uint32_t> sm(L), dm(L, all_l);
+      for (int q = 0; q < L; ++q) sm[q] = 1u << q;
+      for (int j = 0; j < m; ++j) {
+        for (int i = 0; i < L; ++i) lf[i] = froms[nodes_[j][i]], lt[i] = tos[nodes_[j][i]];
+        node_shm_->grs(arr, dtype, MP4J_COPY, lf.data(), lt.data(), sm.data(), dm.data());
+      }
+      return;
+    }
+  }
   tcp_allgather((char*)arr, es, froms, tos, everyone_, rank_);
 }
 

@@ -104,6 +104,7 @@ class ProcessComm {
   void setup_node_plane();
   std::unique_ptr<ShmPlane> node_shm_;
   std::vector<int> node_group_, rail_group_;
+  std::vector<std::vector<int>> nodes_;  // members of every machine, machines in the order of their lowest rank
   int node_index_ = 0;
   void exchange_small(const void* mine, size_t bytes, char* all);
   void shm_run(void* arr, int dtype, int op, const int64_t* lo, const int64_t* hi, const uint32_t* src_mask,

@@ -164,3 +164,13 @@ def test_uneven_machines_fall_back_to_the_flat_tcp_paths():
     res, code, _ = run_cluster(5, workers.plane_blocker, (-1,), timeout=60, env={"MP4J_NODE_IDS": "0,0,0,1,1"})
     assert code == 0  # 3 + 2 ranks: no hierarchy, and nothing hangs while deciding so
     assert all("2 machines" in r for r in res), res  # and no GPU plane across "machines" either
+
+
+@pytest.mark.parametrize("ids", ["0,0,1,1", "a,b,a,b,a,b", "0,0,0,1,1,1,2,2,2"])
+def test_ragged_ranges_on_virtual_machines(ids, monkeypatch):
+    """Ragged ranges through every array collective when allreduce, reduce-scatter and allgather are hierarchical
+    (per-machine shared memory + TCP rails) and the rooted ones run on the flat mesh."""
+    p = len(ids.split(","))
+    monkeypatch.setenv("MP4J_SHM_BYTES", str(64 << 10))
+    res, code, _ = run_cluster(p, workers.ragged_arrays, (4321 + p, 40_003), timeout=240, env={"MP4J_NODE_IDS": ids})
+    assert code == 0 and res == [True] * p, res
