@@ -363,11 +363,10 @@ def failing_slave(comm):
     return "ok"
 
 
-def dying_peer(comm):
+def dying_peer(comm, n=1000):
     """Rank 1 vanishes without closing; rank 0's next collective must fail instead of hanging."""
     import os
     import time
-    n = 1000
     arr = np.ones(n)
     comm.allreduceArray(arr, Operands.DOUBLE_OPERAND(), Operators.Double.SUM, 0, n)  # everybody is set up
     if comm.getRank() == 1:
